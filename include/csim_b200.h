@@ -1,0 +1,234 @@
+/* csim_b200.h — C ABI of the B200-native batched Newton/MNA hot path.
+ *
+ * Drop-in boundary for ONE path of ZyuRao/CircuitSimulator: the damped
+ * Newton-Raphson / modified-nodal-analysis inner loop (device stamps, dense-
+ * semantics LU with partial pivoting, DC source ramp, fixed-step backward-Euler
+ * transient), run batched over B independent instances of one netlist
+ * topology.  The reference has no FFI: its boundary is the in-process C++
+ * surface listed per entry point below (file:line into the reference tree).
+ * The C++ host layer in include/csim/ (same class and function names as the
+ * reference) lowers a parsed Circuit into `csim_topology` and calls this ABI.
+ *
+ * Conventions
+ *   - every call returns 0 on success, a negative CSIM_E_* code on failure and
+ *     never throws; csim_last_error() returns a thread-local message.
+ *   - all per-instance arrays are INSTANCE-MINOR ("SoA"): element (k, b) of a
+ *     [K][B] array lives at k*B + b.  A shard of the batch is therefore a
+ *     contiguous slice of every row.
+ *   - arithmetic is IEEE-754 binary64, round-to-nearest, NO fused multiply-add
+ *     on the reference's expressions, operations in the reference's order.
+ *   - `csim_dev_*` take DEVICE pointers and a CUDA stream (cudaStream_t passed
+ *     as void*) and only enqueue work; `csim_batch_*` take HOST pointers and
+ *     include the host<->device copies.
+ *   - there is no CPU fallback: without a CUDA device every compute entry point
+ *     fails with CSIM_E_CUDA.
+ */
+#ifndef CSIM_B200_H
+#define CSIM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CSIM_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------- */
+#define CSIM_OK 0
+#define CSIM_E_INVALID (-1)     /* bad argument / inconsistent topology        */
+#define CSIM_E_UNSUPPORTED (-2) /* topology outside what the kernels cover     */
+#define CSIM_E_CUDA (-3)        /* CUDA runtime error or no device             */
+#define CSIM_E_NOMEM (-4)
+
+/* ---- per-instance status word (bit mask) -------------------------------- *
+ * Reference behaviour mirrored per instance:                 */
+#define CSIM_ST_LU_SINGULAR 0x1u     /* pivot < lu_eps seen: that solve returned the ZERO vector (include/solver.hpp:58-61,94-97) */
+#define CSIM_ST_NONFINITE 0x2u       /* raw LU solution had NaN/Inf. DC: gmin*=10 and retry (src/dcanalysis.cpp:135-138); TRAN: the reference throws (src/tanalisis.cpp:360-362) -> instance is frozen at its last accepted x */
+#define CSIM_ST_DC_UNCONVERGED 0x4u  /* some ramp step hit dc_max_iters (src/dcanalysis.cpp:153-158) */
+#define CSIM_ST_TRAN_UNCONVERGED 0x8u/* some timestep hit tran_max_iters; step accepted anyway (src/tanalisis.cpp:372-376) */
+
+/* ---- element kinds (reference classes, include/element.hpp) ------------- */
+enum csim_elem_type {
+    CSIM_ELEM_R = 0,   /* Resistor          element.hpp:41-52  params: R                        */
+    CSIM_ELEM_C = 1,   /* CapacitorElement  element.hpp:93-109 params: C                        */
+    CSIM_ELEM_L = 2,   /* Inductor          element.hpp:112-131 params: L ; owns a branch row   */
+    CSIM_ELEM_V = 3,   /* VoltageSource     element.hpp:71-90  params: dc v0 va freq td phi ; owns a branch row */
+    CSIM_ELEM_I = 4,   /* CurrentSource     element.hpp:55-69  params: dc v0 va freq td phi     */
+    CSIM_ELEM_MOS = 5  /* MosfetBase        element.hpp:134-171 params: Vth K lambda Cj0 ; nodes D G S B */
+};
+/* elem_flags */
+#define CSIM_FLAG_PMOS 0x1       /* MOS: isP (sign of .MODEL VT, src/parser.cpp:755-761) */
+#define CSIM_FLAG_SRC_SIN 0x1    /* V/I: tran.type == SIN -> evalDC adds v0 (include/sim.hpp:152-158) */
+
+#define CSIM_PARAMS_R 1
+#define CSIM_PARAMS_C 1
+#define CSIM_PARAMS_L 1
+#define CSIM_PARAMS_SRC 6 /* dc, v0, va, freq, td, phi  (SourceSpec / SinSpec, include/sim.hpp:56-62,145-149) */
+#define CSIM_PARAMS_MOS 4 /* Vth, K, lambda, Cj0        (MosfetBase, include/element.hpp:134-140)             */
+
+/* How the transient value of an independent source is obtained at step s
+ * (t = (s+1)*dt, src/tanalisis.cpp:256).  glibc sin() and CUDA sin() are not
+ * bit-identical, so the parity path tabulates on the HOST with the host libm:
+ *   CSIM_SRC_CONST      value = dc + 0.0                      (WaveformType::NONE, sim.hpp:77-78,160-162)
+ *   CSIM_SRC_SIN_TABLE  value = dc + (t < td ? v0 : v0 + va * S[group][s])
+ *                       with S = sin(2*pi*freq*(t-td)+phi) tabulated per group (sim.hpp:117-122)
+ *   CSIM_SRC_VAL_TABLE  value = dc + S[group][s]              (S = TranWaveform::eval(t): PULSE / PWL, sim.hpp:80-138)
+ */
+enum csim_src_mode { CSIM_SRC_CONST = 0, CSIM_SRC_SIN_TABLE = 1, CSIM_SRC_VAL_TABLE = 2 };
+
+/* ---- constants block: every literal of the reference loops -------------- */
+typedef struct csim_constants {
+    int32_t dc_ramp_steps;   /* 10     src/dcanalysis.cpp:104 */
+    int32_t dc_max_iters;    /* 50     src/dcanalysis.cpp:105 */
+    double dc_tol;           /* 1e-9   src/dcanalysis.cpp:106 */
+    double dc_alpha;         /* 0.35 = clamp(0.35, 0.1, 0.5)  src/dcanalysis.cpp:274 (alphaNext is dead) */
+    double gmin_high_base;   /* 1e-6   src/dcanalysis.cpp:264 */
+    double gmin_low_base;    /* 3.35e-7 */
+    double gmin_abs_max;     /* 1e-4   */
+    double fast_conv_ratio;  /* 0.7    */
+    double slow_conv_ratio;  /* 1.05   */
+    double dc_nonfinite_mul; /* 10.0   src/dcanalysis.cpp:136 */
+    double dc_nonfinite_cap; /* 1e-2   */
+    int32_t tran_max_iters;  /* 50     src/tanalisis.cpp:241 */
+    int32_t _pad0;
+    double tran_tol;         /* 1e-6   src/tanalisis.cpp:242 */
+    double tran_gmin;        /* 1e-6   src/tanalisis.cpp:243 */
+    double tran_alpha;       /* 0.45   src/tanalisis.cpp:244 */
+    double lu_eps;           /* 1e-15  include/solver.hpp:31  */
+    double mos_off_gds;      /* 1e-12  src/element.cpp:246    */
+} csim_constants;
+
+/* Fills *c with the reference's literals. */
+void csim_default_constants(csim_constants* c);
+
+/* ---- flat topology: what Circuit + assignEquationIndices() define ------- *
+ * (include/circuit.hpp:33-66, src/circuit.cpp:42-61).  Elements are listed in
+ * NETLIST ORDER: with the equation numbering it fixes the MNA sparsity pattern
+ * AND the order in which contributions are accumulated into each G(i,j)/I(i)
+ * (src/dcanalysis.cpp:126-130, src/tanalisis.cpp:268-356).                    */
+typedef struct csim_topology {
+    int32_t n_unknowns;         /* N = node equations + branch equations (Circuit::numUnknowns)       */
+    int32_t n_node_eq;          /* rows 0..n_node_eq-1 are node rows (receive gmin, dcanalysis.cpp:36-43) */
+    int32_t n_elems;
+    int32_t n_params;           /* P = parameter doubles per instance                                  */
+    const int32_t* elem_type;   /* [n_elems] csim_elem_type                                            */
+    const int32_t* elem_flags;  /* [n_elems]                                                           */
+    const int32_t* elem_nodes;  /* [n_elems][4] equation index of each terminal, -1 = ground/unused    */
+    const int32_t* elem_branch; /* [n_elems] branch equation index (V, L) or -1                        */
+    const int32_t* elem_param;  /* [n_elems] offset of the element's first parameter in [0,P)          */
+} csim_topology;
+
+typedef struct csim_plan csim_plan;   /* topology lowered to device tables; immutable, shareable   */
+typedef struct csim_batch csim_batch; /* B instances on one device: owns device buffers + a stream */
+
+const char* csim_last_error(void);
+int csim_abi_version(void);
+/* Number of visible CUDA devices, or CSIM_E_CUDA. */
+int csim_device_count(void);
+
+/* Builds the stamp programs (ordered per-slot contribution lists for the DC
+ * and the TRAN assembly), the CSR patterns and uploads them to `device`.
+ * consts == NULL -> reference defaults.                                        */
+int csim_plan_create(const csim_topology* topo, const csim_constants* consts, int device, csim_plan** out);
+void csim_plan_destroy(csim_plan* plan);
+
+/* Host-side introspection (no device work).  mode: 0 = DC assembly, 1 = TRAN
+ * assembly.  Structural pattern of G in CSR, rows ascending, columns ascending
+ * within a row.  Pass NULL arrays to query *nnz only.                          */
+#define CSIM_MODE_DC 0
+#define CSIM_MODE_TRAN 1
+int csim_plan_pattern(const csim_plan* plan, int mode, int32_t* nnz, int32_t* rowptr /*[N+1]*/, int32_t* colidx /*[nnz]*/);
+int csim_plan_dims(const csim_plan* plan, int32_t* n_unknowns, int32_t* n_params, int32_t* n_sources);
+
+/* ===================== device-pointer entry points ======================== */
+
+/* Standalone assembly (the HBM-roofline kernel; also the parity probe for the
+ * stamp programs).  Replaces one pass of the assembly blocks
+ *   DC  : src/dcanalysis.cpp:120-130   (elements in netlist order, then gmin)
+ *   TRAN: src/tanalisis.cpp:259-356    (R/V/I, MOS channel, C, L, MOS caps, gmin)
+ * for every instance.  params [P][B]; x [N][B] = current Newton iterate;
+ * x_prev [N][B] = last accepted timepoint (TRAN only, may be NULL for DC);
+ * src_val [n_sources][B] = value of each independent source (already scaled
+ * for DC, evaluated at t for TRAN), or NULL to use evalDC(scale) from params;
+ * vals [nnz(mode)][B], rhs [N][B].                                             */
+int csim_dev_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double* params, const double* x,
+                       const double* x_prev, const double* src_val, double dt, double source_scale,
+                       double gmin, double* vals, double* rhs, void* stream);
+
+/* Batched Solver::solveLinearSystemLU (include/solver.hpp:83-131) on dense
+ * N x N systems, N <= 32: A [N*N][B] row-major over (i,j), b [N][B] ->
+ * x [N][B], perm [N][B] (perm[i] = original row now at position i,
+ * solver.hpp:41-44,66), singular [B] (1 -> x is the zero vector).              */
+int csim_dev_lu_solve(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                      int32_t* singular, double lu_eps, void* stream);
+
+/* DC operating point for every instance (dcSolveLU, src/dcanalysis.cpp:242-248:
+ * Newton ramp 95-163 when the netlist has MOSFETs, direct solve 46-68 otherwise).
+ * x [N][B] out; iters [dc_ramp_steps][B] Newton iterations spent per ramp step
+ * (may be NULL); pivot_hash [B] in/out running hash of every pivot permutation
+ * (may be NULL; see csim_pivot_hash_* below); status [B] OR-ed in.              */
+int csim_dev_dc(const csim_plan* plan, int64_t B, const double* params, double* x, int32_t* iters,
+                uint64_t* pivot_hash, uint32_t* status, void* stream);
+
+typedef struct csim_tran_args {
+    double dt;              /* .TRAN tstep                                                   */
+    int32_t step_begin;     /* first step of this launch; t = (step+1)*dt                    */
+    int32_t step_end;       /* one past the last step: the reference runs [0, nSteps)        */
+    /* source tables (see csim_src_mode) */
+    int32_t n_groups;       /* rows of src_table                                             */
+    int32_t table_steps;    /* columns of src_table (>= step_end)                            */
+    const double* src_table;    /* [n_groups][table_steps] device                            */
+    const int32_t* src_mode;    /* [n_sources] host array, csim_src_mode                     */
+    const int32_t* src_group;   /* [n_sources] host array: group used by every instance, or  */
+    const int32_t* src_group_b; /* [n_sources][B] DEVICE array: per-instance group (overrides src_group when non-NULL) */
+    /* outputs */
+    int32_t n_probes;       /* probed unknowns                                               */
+    const int32_t* probes;  /* [n_probes] host array of equation indices                     */
+    int32_t out_stride;     /* record step s when (s+1) % out_stride == 0                    */
+    int32_t out_begin_step; /* and s >= out_begin_step (the reference's t >= tstart filter, src/tanalisis.cpp:209) */
+    int64_t wave_ld;        /* timepoints allocated per (instance, probe) row of wave        */
+} csim_tran_args;
+
+/* Fixed-step backward-Euler transient for every instance, steps
+ * [step_begin, step_end) of runTransientAnalysisBackwardEuler
+ * (src/tanalisis.cpp:255-420).  x [N][B] in: state at step_begin (the DC
+ * operating point for step_begin == 0), out: state after step_end-1.
+ * wave [B][n_probes][wave_ld] TIME-MINOR: the value of probe p of instance b at
+ * recorded point r (r counts recorded steps from step 0) is
+ * wave[(b*n_probes + p)*wave_ld + r]; row 0 of the reference CSV (t = 0, the DC
+ * point) is NOT written here.  iters_total [B] += Newton iterations;
+ * iters_step [nSteps][B] uint8 per-step counts (may be NULL).                   */
+int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const csim_tran_args* args,
+                  double* x, double* wave, int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash,
+                  uint32_t* status, void* stream);
+
+/* ======================= host-pointer entry points ======================== */
+int csim_batch_create(const csim_plan* plan, int64_t B, csim_batch** out);
+void csim_batch_destroy(csim_batch* batch);
+int csim_batch_set_params(csim_batch* batch, const double* params /*[P][B] host*/);
+/* DC operating point; x [N][B], iters [ramp][B] (NULL ok), status [B] (NULL ok). */
+int csim_batch_dc(csim_batch* batch, double* x, int32_t* iters, uint64_t* pivot_hash, uint32_t* status);
+/* DC operating point followed by the whole transient, as
+ * runTransientAnalysisBackwardEuler does (src/tanalisis.cpp:112 then 255-420).
+ * args->src_table / src_group_b are HOST pointers here.  wave as above but
+ * host; x_dc [N][B] and x_final [N][B] may be NULL.                             */
+int csim_batch_tran(csim_batch* batch, const csim_tran_args* args, double* x_dc, double* x_final, double* wave,
+                    int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status);
+/* Milliseconds of the kernels of the last csim_batch_* call, measured with CUDA
+ * events on the batch's stream (copies excluded).                               */
+float csim_batch_last_kernel_ms(const csim_batch* batch);
+
+/* ---- pivot-sequence hash (shared definition, host-callable) ------------- *
+ * Every factorisation contributes f = sum_i mix(i, perm[i]) (mod 2^64) and the
+ * running hash becomes h' = (h XOR f) * 0x100000001B3.  h starts at
+ * CSIM_PIVOT_HASH_INIT.  Two instances have equal hashes iff (with
+ * overwhelming probability) they chose the same pivot rows in the same order
+ * in every factorisation.                                                       */
+#define CSIM_PIVOT_HASH_INIT 0xCBF29CE484222325ull
+uint64_t csim_pivot_hash_update(uint64_t h, const int32_t* perm, int32_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CSIM_B200_H */

@@ -1,0 +1,200 @@
+#!/usr/bin/env python
+"""Pins the oracle and writes the golden fixtures.  RUN IN THE BUILD CONTAINER ONLY
+(needs /root/reference):   python tests/golden/make_golden.py
+
+1. Compiles the UNMODIFIED reference (oracle/_ref) and the C restatement (oracle/).
+2. Pins the restatement against the unmodified reference drivers, bit for bit:
+   raw LU solution + pivot permutation of EVERY Newton iteration (DC ramp and
+   transient), every Newton step norm, the CSV the reference writes, plus
+   Element::stamp and Solver::solveLinearSystemLU on random inputs, for the
+   shipped netlists and for parameter-perturbed instances.
+3. Writes small raw-double fixtures (tests/golden/*.npz) that the CPU and GPU
+   test-suites check against on machines where /root/reference does not exist.
+The reference has NO golden vectors of its own; these are generated
+from its own code.
+"""
+import hashlib
+import json
+import os
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import oraclelib as O  # noqa: E402
+
+REF_TESTS = "/root/reference/tests"
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float64).view(np.uint64)
+
+
+def same_bits(a, b):
+    return a.shape == b.shape and np.array_equal(bits(a), bits(b))
+
+
+def perturb(nominal, topo, n, seed):
+    """SURVEY.md §8(d) recipe: instance 0 nominal, others nominal*(1+0.05u), u~U(-1,1),
+    PCG64(seed); applied to R, C, L and the MOS Vth, K, lambda, Cj0; sources nominal."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    P = nominal.size
+    mask = np.zeros(P, bool)
+    for e in range(topo.n_elems):
+        ty = int(topo.elem_type[e])
+        if ty in (O.ELEM_R, O.ELEM_C, O.ELEM_L, O.ELEM_MOS):
+            mask[topo.elem_param[e]: topo.elem_param[e] + O.PARAM_COUNT[ty]] = True
+    u = rng.uniform(-1.0, 1.0, size=(n, P))
+    out = np.repeat(nominal[None, :], n, 0)
+    out[1:, mask] = nominal[mask] * (1.0 + 0.05 * u[1:, mask])
+    return out
+
+
+def csv_from_wave(topo, x_dc, wave, dt):
+    """Re-creates the reference's CSV text (src/tanalisis.cpp:183-231) from raw doubles."""
+    hdr = ["time"] + [f"V({n})" for n in topo.node_names]
+    for e in range(topo.n_elems):
+        if topo.elem_type[e] in (O.ELEM_V, O.ELEM_L):
+            hdr.append(f"I({topo.elem_names[e]})")
+    cols = list(range(topo.n_node_eq)) + [int(topo.elem_branch[e]) for e in range(topo.n_elems)
+                                            if topo.elem_type[e] in (O.ELEM_V, O.ELEM_L)]
+    lines = [",".join(hdr)]
+
+    def row(t, x):
+        return ",".join(["%.9e" % t] + ["%.9e" % x[c] for c in cols])
+
+    lines.append(row(0.0, x_dc))
+    for s in range(wave.shape[0]):
+        lines.append(row((s + 1) * dt, wave[s]))
+    return "\n".join(lines) + "\n"
+
+
+def pin_netlist(name, text, expect_sha16=None, cap=600_000):
+    print(f"== {name}")
+    ref = O.Ref(text)
+    topo = ref.topology()
+    cfg = ref.tran_cfg()
+    dt = cfg["tstep"]
+    n_steps = int(np.floor(cfg["tstop"] / dt + 1e-12))
+    N = topo.n_unknowns
+    print(f"   N={N} elems={topo.n_elems} P={topo.n_params} steps={n_steps}")
+
+    # --- unmodified reference: DC alone (raw doubles) and the full transient driver with trace
+    x_ref_dc, tr_dc = ref.dc(trace_cap=2000)
+    with tempfile.TemporaryDirectory() as td:
+        csv = os.path.join(td, "ref.csv")
+        rc, tr = ref.tran(csv, trace_cap=cap)
+        assert rc == 0
+        ref_csv = open(csv).read()
+    sha = hashlib.sha256(ref_csv.encode()).hexdigest()
+    print(f"   reference CSV sha256 {sha[:16]}  newton solves (DC+TRAN) {tr.n_iters}")
+    if expect_sha16:
+        assert sha.startswith(expect_sha16), "reference CSV differs from SURVEY.md §4 known answer"
+
+    # --- restatement
+    o_dc = O.dc(topo, topo.params, trace_cap=2000)
+    mode, group, table = O.make_source_tables(topo, topo.params, dt, n_steps)
+    for s in range(len(mode)):  # table convention reproduces SourceSpec::evalTran bit for bit
+        for st in (0, 1, n_steps // 3, n_steps - 1):
+            v = O.src_tran(topo, topo.params, mode, group, table, st, dt)[s]
+            assert bits(np.array(v)) == bits(np.array(ref.source_tran(s, (st + 1) * dt))), (s, st)
+    o_tr = O.tran(topo, topo.params, dt, 0, n_steps, mode, group, table, o_dc["x"], trace_cap=cap,
+                  pivot_hash=o_dc["hash"])
+
+    # DC: raw solution, every iteration
+    assert same_bits(o_dc["x"], x_ref_dc), "DC operating point differs"
+    assert o_dc["trace"].n_iters == tr_dc.n_iters
+    assert same_bits(o_dc["trace"].xraw, tr_dc.xraw) and np.array_equal(o_dc["trace"].perm, tr_dc.perm)
+    assert same_bits(o_dc["trace"].err, tr_dc.err)
+    # transient driver = DC (again) followed by the step loop
+    nd = o_dc["trace"].n_iters
+    assert tr.n_iters == nd + o_tr["trace"].n_iters == nd + o_tr["total"], (tr.n_iters, nd, o_tr["total"])
+    assert same_bits(tr.xraw[:nd], o_dc["trace"].xraw)
+    assert same_bits(tr.xraw[nd:], o_tr["trace"].xraw), "raw LU solutions differ in the transient"
+    assert np.array_equal(tr.perm[nd:], o_tr["trace"].perm), "pivot permutations differ"
+    assert same_bits(tr.err[o_dc["trace"].n_err:], o_tr["trace"].err), "Newton step norms differ"
+    my_csv = csv_from_wave(topo, o_dc["x"], o_tr["wave"], dt)
+    assert my_csv == ref_csv, "CSV text differs"
+    margin = min(o_dc["trace"].min_margin, o_tr["trace"].min_margin)
+    print(f"   PINNED: {tr.n_iters} raw solutions, permutations and norms bit-identical; CSV identical;"
+          f" min threshold margin {margin:.3e}")
+
+    # distinct permutations
+    allperm = np.concatenate([o_dc["trace"].perm, o_tr["trace"].perm])
+    uniq = np.unique(allperm, axis=0)
+    print(f"   distinct pivot permutations: {len(uniq)}")
+
+    # Element::stamp / solveLinearSystemLU on random iterates
+    rng = np.random.default_rng(7)
+    for k in range(25):
+        x = rng.uniform(-1, 4, N)
+        scale = (k % 10 + 1) / 10.0
+        Gr, Ir = ref.stamp(False, x, scale=scale)
+        Go, Io = O.stamp(topo, O.MODE_DC, topo.params, x, None, O.src_dc(topo, topo.params, scale), gmin=0.0)
+        assert same_bits(Gr, Go) and same_bits(Ir, Io), "DC stamp differs"
+        A = Go + np.diag(np.r_[np.full(topo.n_node_eq, 1e-6), np.zeros(N - topo.n_node_eq)])
+        xr, pr = O.ref_lu_solve(A, Io)
+        xo, po, failed = O.lu_solve(A, Io)
+        assert same_bits(xr, xo) and np.array_equal(pr, po) and not failed
+    return topo, cfg, o_dc, o_tr, dict(sha=sha, margin=margin, n_perm=len(uniq), n_steps=n_steps)
+
+
+def main():
+    O.build(force=True)
+    summary = {}
+
+    # ---- buffer.sp (config 1): full raw waveform
+    text = open(os.path.join(REF_TESTS, "buffer.sp")).read()
+    topo, cfg, dc, tr, info = pin_netlist("buffer.sp", text, "32dfdc4364637c7a")
+    summary["buffer"] = info
+    np.savez_compressed(os.path.join(OUT, "buffer_nominal.npz"), netlist=text, x_dc=dc["x"], dc_iters=dc["iters"],
+                        dc_hash=np.uint64(dc["hash"]), wave=tr["wave"], iters_step=tr["iters_step"],
+                        hash=np.uint64(tr["hash"]), status=np.uint32(dc["status"] | tr["status"]),
+                        params=topo.params, elem_type=topo.elem_type, elem_flags=topo.elem_flags,
+                        elem_nodes=topo.elem_nodes, elem_branch=topo.elem_branch, elem_param=topo.elem_param,
+                        n_node_eq=topo.n_node_eq, dt=cfg["tstep"], tstop=cfg["tstop"])
+
+    # perturbed buffer instances through the reference's own parser + drivers
+    pert = perturb(topo.params, topo, 6, 20261104 + 3)
+    n_steps = info["n_steps"]
+    rows = []
+    for b in range(1, 6):
+        t2 = O.netlist_from_params(topo, pert[b], tran=cfg)
+        r2 = O.Ref(t2)
+        tp2 = r2.topology()
+        assert same_bits(tp2.params, pert[b]), "netlist round trip is not bit exact"
+        assert np.array_equal(tp2.elem_nodes, topo.elem_nodes) and np.array_equal(tp2.elem_type, topo.elem_type)
+        _, trc = r2.tran("/dev/null", trace_cap=20000)
+        d2 = O.dc(topo, pert[b], trace_cap=2000)
+        m, g, tab = O.make_source_tables(topo, pert[b], cfg["tstep"], n_steps)
+        o2 = O.tran(topo, pert[b], cfg["tstep"], 0, n_steps, m, g, tab, d2["x"], trace_cap=20000, pivot_hash=d2["hash"])
+        nd = d2["trace"].n_iters
+        assert trc.n_iters == nd + o2["total"]
+        assert same_bits(trc.xraw[nd:], o2["trace"].xraw) and np.array_equal(trc.perm[nd:], o2["trace"].perm)
+        rows.append(dict(params=pert[b], x_dc=d2["x"], x_final=o2["x"], iters=o2["iters_step"], hash=o2["hash"]))
+    print(f"   perturbed buffer instances 1..5 pinned against the reference")
+    np.savez_compressed(os.path.join(OUT, "buffer_perturbed.npz"), params=np.stack([r["params"] for r in rows]),
+                        x_dc=np.stack([r["x_dc"] for r in rows]), x_final=np.stack([r["x_final"] for r in rows]),
+                        iters_step=np.stack([r["iters"] for r in rows]),
+                        hash=np.array([r["hash"] for r in rows], np.uint64))
+
+    # ---- dbmixer.sp (config 2): DC point, per-step Newton counts, decimated waveform
+    text = open(os.path.join(REF_TESTS, "dbmixer.sp")).read()
+    topo, cfg, dc, tr, info = pin_netlist("dbmixer.sp", text, "46fcdf8fa4a14bf7")
+    summary["dbmixer"] = info
+    np.savez_compressed(os.path.join(OUT, "dbmixer_nominal.npz"), netlist=text, x_dc=dc["x"], dc_iters=dc["iters"],
+                        dc_hash=np.uint64(dc["hash"]), wave_first=tr["wave"][:400], wave_dec100=tr["wave"][99::100],
+                        x_final=tr["x"], iters_step=tr["iters_step"], hash=np.uint64(tr["hash"]),
+                        status=np.uint32(dc["status"] | tr["status"]), params=topo.params,
+                        elem_type=topo.elem_type, elem_flags=topo.elem_flags, elem_nodes=topo.elem_nodes,
+                        elem_branch=topo.elem_branch, elem_param=topo.elem_param, n_node_eq=topo.n_node_eq,
+                        dt=cfg["tstep"], tstop=cfg["tstop"])
+    json.dump(summary, open(os.path.join(OUT, "pinning_summary.json"), "w"), indent=1)
+    print("golden fixtures written to", OUT)
+
+
+if __name__ == "__main__":
+    main()
