@@ -1,0 +1,459 @@
+// capi.cpp — the extern "C" boundary declared in include/csim_b200.h.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/csim_b200.h"
+#include "kernels.hpp"
+#include "plan.hpp"
+
+using namespace csim;
+
+namespace {
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+int cuda_fail(cudaError_t e, const char* what) {
+    return fail(CSIM_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(call)                                            \
+    do {                                                    \
+        cudaError_t e__ = (call);                           \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+    } while (0)
+
+template <typename T>
+cudaError_t upload(const std::vector<T>& v, const T** out, std::vector<void*>& owned) {
+    *out = nullptr;
+    if (v.empty()) return cudaSuccess;
+    void* d = nullptr;
+    cudaError_t e = cudaMalloc(&d, v.size() * sizeof(T));
+    if (e != cudaSuccess) return e;
+    owned.push_back(d);
+    e = cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+    *out = static_cast<const T*>(d);
+    return e;
+}
+}  // namespace
+
+struct csim_plan {
+    HostPlan host;
+    DevPlan dev{};
+    int device = -1;
+    int sm_count = 0;
+    std::vector<void*> owned;
+};
+
+struct csim_batch {
+    const csim_plan* plan = nullptr;
+    int64_t B = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double* d_params = nullptr;
+    double* d_x = nullptr;
+    uint64_t* d_hash = nullptr;
+    uint32_t* d_status = nullptr;
+    int32_t* d_iters = nullptr;  // [max(ramp,1)][B], also reused for iters_total
+    float last_ms = 0.f;
+};
+
+extern "C" {
+
+const char* csim_last_error(void) { return g_err.c_str(); }
+int csim_abi_version(void) { return CSIM_ABI_VERSION; }
+
+void csim_default_constants(csim_constants* c) {
+    if (!c) return;
+    std::memset(c, 0, sizeof(*c));
+    c->dc_ramp_steps = 10;
+    c->dc_max_iters = 50;
+    c->dc_tol = 1e-9;
+    c->dc_alpha = 0.35;
+    c->gmin_high_base = 1e-6;
+    c->gmin_low_base = 3.35e-7;
+    c->gmin_abs_max = 1e-4;
+    c->fast_conv_ratio = 0.7;
+    c->slow_conv_ratio = 1.05;
+    c->dc_nonfinite_mul = 10.0;
+    c->dc_nonfinite_cap = 1e-2;
+    c->tran_max_iters = 50;
+    c->tran_tol = 1e-6;
+    c->tran_gmin = 1e-6;
+    c->tran_alpha = 0.45;
+    c->lu_eps = 1e-15;
+    c->mos_off_gds = 1e-12;
+}
+
+int csim_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    return n;
+}
+
+uint64_t csim_pivot_hash_update(uint64_t h, const int32_t* perm, int32_t n) {
+    uint32_t flo = 0, fhi = 0;
+    for (int32_t i = 0; i < n; ++i) {
+        uint32_t key = (uint32_t)i * 1024u + (uint32_t)perm[i] + 1u;
+        uint32_t lo = key * 0x9E3779B1u;
+        lo ^= lo >> 15;
+        uint32_t hi = key * 0x85EBCA77u;
+        hi ^= hi >> 13;
+        flo += lo;
+        fhi += hi;
+    }
+    return (h ^ (((uint64_t)fhi << 32) | flo)) * 0x100000001B3ull;
+}
+
+int csim_plan_create(const csim_topology* topo, const csim_constants* consts, int device, csim_plan** out) {
+    if (!topo || !out) return fail(CSIM_E_INVALID, "csim_plan_create: null argument");
+    *out = nullptr;
+    std::unique_ptr<csim_plan> p(new csim_plan());
+    try {
+        p->host = build_host_plan(*topo, consts);
+    } catch (const std::exception& e) {
+        return fail(CSIM_E_INVALID, std::string("csim_plan_create: ") + e.what());
+    }
+    p->device = device;
+    if (device >= 0) {
+        CU(cudaSetDevice(device));
+        cudaDeviceProp prop;
+        CU(cudaGetDeviceProperties(&prop, device));
+        p->sm_count = prop.multiProcessorCount;
+        DevPlan& d = p->dev;
+        d.N = p->host.N;
+        d.n_node_eq = p->host.n_node_eq;
+        d.n_params = p->host.n_params;
+        d.n_sources = p->host.n_sources;
+        d.has_mos = p->host.has_mos ? 1 : 0;
+        d.c = p->host.consts;
+        for (int m = 0; m < 2; ++m) {
+            const ModeProgram& mp = p->host.mode[m];
+            DevMode& dm = d.m[m];
+            dm.n_values = mp.n_values;
+            dm.n_static = (int)mp.static_ops.size();
+            dm.n_step = (int)mp.step_ops.size();
+            dm.n_src = (int)mp.src_ops.size();
+            dm.n_mos = (int)mp.mos_ops.size();
+            dm.row_len = mp.row_len_max;
+            dm.nnz = (int)mp.colidx.size();
+            dm.n_slots = (int)mp.slot_ptr.size() - 1;
+            CU(upload(mp.static_ops, &dm.static_ops, p->owned));
+            CU(upload(mp.step_ops, &dm.step_ops, p->owned));
+            CU(upload(mp.src_ops, &dm.src_ops, p->owned));
+            CU(upload(mp.mos_ops, &dm.mos_ops, p->owned));
+            CU(upload(mp.row_prog, &dm.row_prog, p->owned));
+            CU(upload(mp.slot_ptr, &dm.slot_ptr, p->owned));
+            CU(upload(mp.slot_entries, &dm.slot_entries, p->owned));
+        }
+    }
+    *out = p.release();
+    return CSIM_OK;
+}
+
+void csim_plan_destroy(csim_plan* plan) {
+    if (!plan) return;
+    if (plan->device >= 0) {
+        cudaSetDevice(plan->device);
+        for (void* d : plan->owned) cudaFree(d);
+    }
+    delete plan;
+}
+
+int csim_plan_pattern(const csim_plan* plan, int mode, int32_t* nnz, int32_t* rowptr, int32_t* colidx) {
+    if (!plan || mode < 0 || mode > 1) return fail(CSIM_E_INVALID, "csim_plan_pattern: bad argument");
+    const ModeProgram& mp = plan->host.mode[mode];
+    if (nnz) *nnz = (int32_t)mp.colidx.size();
+    if (rowptr) std::memcpy(rowptr, mp.rowptr.data(), mp.rowptr.size() * sizeof(int32_t));
+    if (colidx) std::memcpy(colidx, mp.colidx.data(), mp.colidx.size() * sizeof(int32_t));
+    return CSIM_OK;
+}
+
+int csim_plan_dims(const csim_plan* plan, int32_t* n_unknowns, int32_t* n_params, int32_t* n_sources) {
+    if (!plan) return fail(CSIM_E_INVALID, "csim_plan_dims: null plan");
+    if (n_unknowns) *n_unknowns = plan->host.N;
+    if (n_params) *n_params = plan->host.n_params;
+    if (n_sources) *n_sources = plan->host.n_sources;
+    return CSIM_OK;
+}
+
+// ------------------------------------------------------------------ device API
+static int need_device(const csim_plan* plan, const char* who) {
+    if (!plan) return fail(CSIM_E_INVALID, std::string(who) + ": null plan");
+    if (plan->device < 0) return fail(CSIM_E_CUDA, std::string(who) + ": plan was created without a CUDA device (no CPU fallback)");
+    cudaError_t e = cudaSetDevice(plan->device);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
+    return CSIM_OK;
+}
+static int need_small(const csim_plan* plan, const char* who) {
+    if (plan->host.N > 32)
+        return fail(CSIM_E_UNSUPPORTED, std::string(who) + ": N > 32 needs the large-matrix path (not in this build)");
+    return CSIM_OK;
+}
+
+int csim_dev_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double* params, const double* x,
+                       const double* x_prev, const double* src_val, double dt, double source_scale, double gmin,
+                       double* vals, double* rhs, void* stream) {
+    int rc = need_device(plan, "csim_dev_stamp_csr");
+    if (rc) return rc;
+    if (mode < 0 || mode > 1 || B <= 0 || !params || !x || !vals || !rhs || (mode == CSIM_MODE_TRAN && !x_prev))
+        return fail(CSIM_E_INVALID, "csim_dev_stamp_csr: bad argument");
+    CU(launch_stamp_csr(plan->dev, mode, B, params, x, x_prev, src_val, dt, source_scale, gmin, vals, rhs,
+                        plan->sm_count, (cudaStream_t)stream));
+    return CSIM_OK;
+}
+
+int csim_dev_lu_solve(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                      int32_t* singular, double lu_eps, void* stream) {
+    if (n <= 0 || n > 32) return fail(CSIM_E_UNSUPPORTED, "csim_dev_lu_solve: 1 <= n <= 32 required");
+    if (B <= 0 || !A || !b || !x) return fail(CSIM_E_INVALID, "csim_dev_lu_solve: bad argument");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(CSIM_E_CUDA, "csim_dev_lu_solve: no CUDA device (no CPU fallback)");
+    CU(launch_lu_solve(n, B, A, b, x, perm, singular, lu_eps, (cudaStream_t)stream));
+    return CSIM_OK;
+}
+
+int csim_dev_dc(const csim_plan* plan, int64_t B, const double* params, double* x, int32_t* iters,
+                uint64_t* pivot_hash, uint32_t* status, void* stream) {
+    int rc = need_device(plan, "csim_dev_dc");
+    if (rc) return rc;
+    if ((rc = need_small(plan, "csim_dev_dc"))) return rc;
+    if (B <= 0 || !params || !x) return fail(CSIM_E_INVALID, "csim_dev_dc: bad argument");
+    CU(launch_dc(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
+    return CSIM_OK;
+}
+
+int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const csim_tran_args* a, double* x,
+                  double* wave, int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status,
+                  void* stream_v) {
+    int rc = need_device(plan, "csim_dev_tran");
+    if (rc) return rc;
+    if ((rc = need_small(plan, "csim_dev_tran"))) return rc;
+    if (B <= 0 || !params || !a || !x) return fail(CSIM_E_INVALID, "csim_dev_tran: bad argument");
+    const int ns = plan->host.n_sources;
+    if (a->dt <= 0.0 || a->step_begin < 0 || a->step_end < a->step_begin)
+        return fail(CSIM_E_INVALID, "csim_dev_tran: bad step range or dt");
+    if (a->n_probes < 0 || a->n_probes > 32 || (a->n_probes > 0 && (!a->probes || !wave || a->out_stride <= 0)))
+        return fail(CSIM_E_INVALID, "csim_dev_tran: bad probe specification (at most 32 probes)");
+    if (ns > 0 && (!a->src_mode || (!a->src_group && !a->src_group_b)))
+        return fail(CSIM_E_INVALID, "csim_dev_tran: source modes/groups missing");
+    bool uses_table = false;
+    for (int s = 0; s < ns; ++s) {
+        if (a->src_mode[s] < 0 || a->src_mode[s] > CSIM_SRC_VAL_TABLE)
+            return fail(CSIM_E_INVALID, "csim_dev_tran: bad src_mode");
+        if (a->src_mode[s] != CSIM_SRC_CONST) {
+            uses_table = true;
+            if (a->src_group && (a->src_group[s] < 0 || a->src_group[s] >= a->n_groups))
+                return fail(CSIM_E_INVALID, "csim_dev_tran: src_group out of range");
+        }
+    }
+    if (uses_table && (!a->src_table || a->table_steps < a->step_end))
+        return fail(CSIM_E_INVALID, "csim_dev_tran: source table missing or shorter than step_end");
+    for (int p = 0; p < a->n_probes; ++p)
+        if (a->probes[p] < 0 || a->probes[p] >= plan->host.N) return fail(CSIM_E_INVALID, "csim_dev_tran: probe out of range");
+    if (a->n_probes > 0) {
+        int64_t recorded = (int64_t)a->step_end / a->out_stride - (int64_t)a->out_begin_step / a->out_stride;
+        if (recorded > a->wave_ld) return fail(CSIM_E_INVALID, "csim_dev_tran: wave_ld too small");
+    }
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    // small host-side descriptors -> stream-ordered device scratch
+    std::vector<int32_t> pack((size_t)2 * ns + 32, 0);
+    for (int s = 0; s < ns; ++s) {
+        pack[s] = a->src_mode[s];
+        pack[ns + s] = a->src_group ? a->src_group[s] : 0;
+    }
+    for (int p = 0; p < a->n_probes; ++p) pack[2 * ns + p] = a->probes[p];
+    int32_t* d_pack = nullptr;
+    CU(cudaMallocAsync((void**)&d_pack, pack.size() * sizeof(int32_t), stream));
+    CU(cudaMemcpyAsync(d_pack, pack.data(), pack.size() * sizeof(int32_t), cudaMemcpyHostToDevice, stream));
+    CU(cudaStreamSynchronize(stream));  // `pack` is a pageable temporary
+    DevTran T{};
+    T.dt = a->dt;
+    T.step_begin = a->step_begin;
+    T.step_end = a->step_end;
+    T.table_steps = a->table_steps;
+    T.n_probes = a->n_probes;
+    T.out_stride = a->out_stride > 0 ? a->out_stride : 1;
+    T.out_begin_step = a->out_begin_step;
+    T.wave_ld = a->wave_ld;
+    T.src_table = a->src_table;
+    T.src_mode = d_pack;
+    T.src_group = d_pack + ns;
+    T.src_group_b = a->src_group_b;
+    T.probes = d_pack + 2 * ns;
+    cudaError_t e = launch_tran(plan->dev, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
+    cudaFreeAsync(d_pack, stream);
+    if (e != cudaSuccess) return cuda_fail(e, "tran_kernel launch");
+    return CSIM_OK;
+}
+
+// -------------------------------------------------------------------- host API
+int csim_batch_create(const csim_plan* plan, int64_t B, csim_batch** out) {
+    if (!out) return fail(CSIM_E_INVALID, "csim_batch_create: null out");
+    *out = nullptr;
+    int rc = need_device(plan, "csim_batch_create");
+    if (rc) return rc;
+    if (B <= 0) return fail(CSIM_E_INVALID, "csim_batch_create: B <= 0");
+    std::unique_ptr<csim_batch> b(new csim_batch());
+    b->plan = plan;
+    b->B = B;
+    const int N = plan->host.N, P = plan->host.n_params;
+    const int ramp = plan->host.consts.dc_ramp_steps > 0 ? plan->host.consts.dc_ramp_steps : 1;
+    CU(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&b->ev0));
+    CU(cudaEventCreate(&b->ev1));
+    CU(cudaMalloc((void**)&b->d_params, sizeof(double) * (size_t)(P > 0 ? P : 1) * B));
+    CU(cudaMalloc((void**)&b->d_x, sizeof(double) * (size_t)N * B));
+    CU(cudaMalloc((void**)&b->d_hash, sizeof(uint64_t) * B));
+    CU(cudaMalloc((void**)&b->d_status, sizeof(uint32_t) * B));
+    CU(cudaMalloc((void**)&b->d_iters, sizeof(int32_t) * (size_t)ramp * B));
+    *out = b.release();
+    return CSIM_OK;
+}
+
+void csim_batch_destroy(csim_batch* b) {
+    if (!b) return;
+    cudaSetDevice(b->plan->device);
+    cudaFree(b->d_params);
+    cudaFree(b->d_x);
+    cudaFree(b->d_hash);
+    cudaFree(b->d_status);
+    cudaFree(b->d_iters);
+    if (b->ev0) cudaEventDestroy(b->ev0);
+    if (b->ev1) cudaEventDestroy(b->ev1);
+    if (b->stream) cudaStreamDestroy(b->stream);
+    delete b;
+}
+
+int csim_batch_set_params(csim_batch* b, const double* params) {
+    if (!b || !params) return fail(CSIM_E_INVALID, "csim_batch_set_params: null argument");
+    CU(cudaSetDevice(b->plan->device));
+    CU(cudaMemcpyAsync(b->d_params, params, sizeof(double) * (size_t)b->plan->host.n_params * b->B,
+                       cudaMemcpyHostToDevice, b->stream));
+    CU(cudaStreamSynchronize(b->stream));
+    return CSIM_OK;
+}
+
+static int batch_reset_diag(csim_batch* b) {
+    std::vector<uint64_t> h0((size_t)b->B, CSIM_PIVOT_HASH_INIT);
+    CU(cudaMemcpyAsync(b->d_hash, h0.data(), sizeof(uint64_t) * b->B, cudaMemcpyHostToDevice, b->stream));
+    CU(cudaMemsetAsync(b->d_status, 0, sizeof(uint32_t) * b->B, b->stream));
+    CU(cudaStreamSynchronize(b->stream));
+    return CSIM_OK;
+}
+
+int csim_batch_dc(csim_batch* b, double* x, int32_t* iters, uint64_t* pivot_hash, uint32_t* status) {
+    if (!b) return fail(CSIM_E_INVALID, "csim_batch_dc: null batch");
+    CU(cudaSetDevice(b->plan->device));
+    int rc = batch_reset_diag(b);
+    if (rc) return rc;
+    const int N = b->plan->host.N, ramp = b->plan->host.consts.dc_ramp_steps;
+    CU(cudaEventRecord(b->ev0, b->stream));
+    rc = csim_dev_dc(b->plan, b->B, b->d_params, b->d_x, b->d_iters, b->d_hash, b->d_status, b->stream);
+    if (rc) return rc;
+    CU(cudaEventRecord(b->ev1, b->stream));
+    if (x) CU(cudaMemcpyAsync(x, b->d_x, sizeof(double) * (size_t)N * b->B, cudaMemcpyDeviceToHost, b->stream));
+    if (iters) CU(cudaMemcpyAsync(iters, b->d_iters, sizeof(int32_t) * (size_t)ramp * b->B, cudaMemcpyDeviceToHost, b->stream));
+    if (pivot_hash) CU(cudaMemcpyAsync(pivot_hash, b->d_hash, sizeof(uint64_t) * b->B, cudaMemcpyDeviceToHost, b->stream));
+    if (status) CU(cudaMemcpyAsync(status, b->d_status, sizeof(uint32_t) * b->B, cudaMemcpyDeviceToHost, b->stream));
+    CU(cudaStreamSynchronize(b->stream));
+    CU(cudaEventElapsedTime(&b->last_ms, b->ev0, b->ev1));
+    return CSIM_OK;
+}
+
+int csim_batch_tran(csim_batch* b, const csim_tran_args* a, double* x_dc, double* x_final, double* wave,
+                    int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status) {
+    if (!b || !a) return fail(CSIM_E_INVALID, "csim_batch_tran: null argument");
+    const csim_plan* plan = b->plan;
+    CU(cudaSetDevice(plan->device));
+    const int N = plan->host.N;
+    const int64_t B = b->B;
+    int rc = batch_reset_diag(b);
+    if (rc) return rc;
+    const int nsteps = a->step_end;
+    // device copies of the host-side tables / outputs
+    double* d_table = nullptr;
+    int32_t* d_group_b = nullptr;
+    double* d_wave = nullptr;
+    uint8_t* d_its = nullptr;
+    int32_t* d_total = nullptr;
+    size_t wave_elems = (size_t)B * (a->n_probes > 0 ? a->n_probes : 0) * (size_t)(a->wave_ld > 0 ? a->wave_ld : 0);
+    auto cleanup = [&]() {
+        cudaFree(d_table);
+        cudaFree(d_group_b);
+        cudaFree(d_wave);
+        cudaFree(d_its);
+        cudaFree(d_total);
+    };
+#define CUC(call)                                    \
+    do {                                             \
+        cudaError_t e__ = (call);                    \
+        if (e__ != cudaSuccess) {                    \
+            cleanup();                               \
+            return cuda_fail(e__, #call);            \
+        }                                            \
+    } while (0)
+    if (a->src_table && a->n_groups > 0 && a->table_steps > 0) {
+        size_t bytes = sizeof(double) * (size_t)a->n_groups * a->table_steps;
+        CUC(cudaMalloc((void**)&d_table, bytes));
+        CUC(cudaMemcpyAsync(d_table, a->src_table, bytes, cudaMemcpyHostToDevice, b->stream));
+    }
+    if (a->src_group_b) {
+        size_t bytes = sizeof(int32_t) * (size_t)plan->host.n_sources * B;
+        CUC(cudaMalloc((void**)&d_group_b, bytes));
+        CUC(cudaMemcpyAsync(d_group_b, a->src_group_b, bytes, cudaMemcpyHostToDevice, b->stream));
+    }
+    if (wave_elems) {
+        CUC(cudaMalloc((void**)&d_wave, sizeof(double) * wave_elems));
+        CUC(cudaMemsetAsync(d_wave, 0xFF, sizeof(double) * wave_elems, b->stream));  // NaN = "never written"
+    }
+    if (iters_step) {
+        CUC(cudaMalloc((void**)&d_its, (size_t)nsteps * B));
+        CUC(cudaMemsetAsync(d_its, 0, (size_t)nsteps * B, b->stream));
+    }
+    CUC(cudaMalloc((void**)&d_total, sizeof(int32_t) * B));
+    CUC(cudaMemsetAsync(d_total, 0, sizeof(int32_t) * B, b->stream));
+
+    csim_tran_args da = *a;
+    da.src_table = d_table;
+    da.src_group_b = d_group_b;
+    CUC(cudaEventRecord(b->ev0, b->stream));
+    // runTransientAnalysisBackwardEuler: DC operating point first (src/tanalisis.cpp:112) ...
+    rc = csim_dev_dc(plan, B, b->d_params, b->d_x, nullptr, b->d_hash, b->d_status, b->stream);
+    if (rc) {
+        cleanup();
+        return rc;
+    }
+    if (x_dc) CUC(cudaMemcpyAsync(x_dc, b->d_x, sizeof(double) * (size_t)N * B, cudaMemcpyDeviceToHost, b->stream));
+    // ... then the step loop (255-420)
+    rc = csim_dev_tran(plan, B, b->d_params, &da, b->d_x, d_wave, d_total, d_its, b->d_hash, b->d_status, b->stream);
+    if (rc) {
+        cleanup();
+        return rc;
+    }
+    CUC(cudaEventRecord(b->ev1, b->stream));
+    if (x_final) CUC(cudaMemcpyAsync(x_final, b->d_x, sizeof(double) * (size_t)N * B, cudaMemcpyDeviceToHost, b->stream));
+    if (wave && wave_elems) CUC(cudaMemcpyAsync(wave, d_wave, sizeof(double) * wave_elems, cudaMemcpyDeviceToHost, b->stream));
+    if (iters_total) CUC(cudaMemcpyAsync(iters_total, d_total, sizeof(int32_t) * B, cudaMemcpyDeviceToHost, b->stream));
+    if (iters_step) CUC(cudaMemcpyAsync(iters_step, d_its, (size_t)nsteps * B, cudaMemcpyDeviceToHost, b->stream));
+    if (pivot_hash) CUC(cudaMemcpyAsync(pivot_hash, b->d_hash, sizeof(uint64_t) * B, cudaMemcpyDeviceToHost, b->stream));
+    if (status) CUC(cudaMemcpyAsync(status, b->d_status, sizeof(uint32_t) * B, cudaMemcpyDeviceToHost, b->stream));
+    CUC(cudaStreamSynchronize(b->stream));
+    CUC(cudaEventElapsedTime(&b->last_ms, b->ev0, b->ev1));
+    cleanup();
+#undef CUC
+    return CSIM_OK;
+}
+
+float csim_batch_last_kernel_ms(const csim_batch* b) { return b ? b->last_ms : 0.f; }
+
+}  // extern "C"

@@ -1,0 +1,40 @@
+// device_plan.cuh — device-side view of a csim_plan (POD, passed to kernels by value).
+#pragma once
+#include <cstdint>
+
+#include "plan.hpp"
+
+namespace csim {
+
+struct DevMode {
+    int32_t n_values, n_static, n_step, n_src, n_mos, row_len, nnz, n_slots;
+    const StaticOp* static_ops;
+    const StepOp* step_ops;
+    const SrcOp* src_ops;
+    const MosOp* mos_ops;
+    const uint32_t* row_prog;      // [row_len][32]
+    const int32_t* slot_ptr;       // [n_slots+1]
+    const uint32_t* slot_entries;  // contribution words per slot, reference order
+};
+
+struct DevPlan {
+    int32_t N, n_node_eq, n_params, n_sources, has_mos, _pad;
+    csim_constants c;
+    DevMode m[2];
+};
+
+// transient launch description (device pointers)
+struct DevTran {
+    double dt;
+    int32_t step_begin, step_end;
+    int32_t table_steps, n_probes;
+    int32_t out_stride, out_begin_step;
+    int64_t wave_ld;
+    const double* src_table;     // [n_groups][table_steps]
+    const int32_t* src_mode;     // [n_sources]
+    const int32_t* src_group;    // [n_sources]
+    const int32_t* src_group_b;  // [n_sources][B] or nullptr
+    const int32_t* probes;       // [n_probes]
+};
+
+}  // namespace csim

@@ -1,0 +1,378 @@
+// kernels.cu — sm_100a kernels of the batched Newton/MNA path.
+//
+//   stamp_csr_kernel : standalone assembly, thread-per-instance, HBM-bound
+//   lu_solve_kernel  : batched Solver::solveLinearSystemLU, warp-per-system
+//   dc_kernel        : DC operating point (source ramp + damped Newton), warp-per-instance
+//   tran_kernel      : backward-Euler step loop + damped Newton, warp-per-instance
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "kernels.hpp"
+#include "newton_warp.cuh"
+
+namespace csim {
+
+// =============================================================================
+// standalone assembly
+// =============================================================================
+// One thread per instance; the value table of a thread lives in shared memory as
+// vt[v][threadIdx.x] (conflict-free).  Inputs are read once, coalesced across the
+// warp (instance-minor layout); every output slot is written once, coalesced.
+template <int MODE>
+__global__ void __launch_bounds__(kStampThreads)
+stamp_csr_kernel(DevPlan P, int64_t B, const double* __restrict__ params, const double* __restrict__ x,
+                 const double* __restrict__ x_prev, const double* __restrict__ src_val, double dt, double scale,
+                 double gmin, double* __restrict__ vals, double* __restrict__ rhs) {
+    extern __shared__ double smem[];
+    const DevMode& m = P.m[MODE];
+    const int tid = threadIdx.x;
+    double* vt = smem + tid;  // stride blockDim.x
+    const int TS = blockDim.x;
+    for (int64_t b = (int64_t)blockIdx.x * blockDim.x + tid; b < B; b += (int64_t)gridDim.x * blockDim.x) {
+        for (int i = 0; i < m.n_static; ++i) {
+            StaticOp op = m.static_ops[i];
+            double p = op.param >= 0 ? __ldg(params + (int64_t)op.param * B + b) : 0.0;
+            double v;
+            switch (op.kind) {
+                case SK_ONE: v = 1.0; break;
+                case SK_GMIN: v = gmin; break;
+                case SK_RES: v = (p == 0.0) ? 0.0 : 1.0 / p; break;
+                case SK_CAP: v = (p <= 0.0 || dt <= 0.0) ? 0.0 : p / dt; break;
+                case SK_CAPHALF: {
+                    double c = dmul(0.5, p);
+                    v = (c <= 0.0 || dt <= 0.0) ? 0.0 : c / dt;
+                } break;
+                case SK_IND_ONE: v = (p <= 0.0) ? 0.0 : 1.0; break;
+                case SK_IND_NREQ: v = (p <= 0.0) ? 0.0 : -(p / dt); break;
+                default: v = 0.0;
+            }
+            vt[op.out * TS] = v;
+        }
+        if (MODE == CSIM_MODE_TRAN) {
+            for (int i = 0; i < m.n_step; ++i) {
+                StepOp op = m.step_ops[i];
+                double va = op.a >= 0 ? __ldg(x_prev + (int64_t)op.a * B + b) : 0.0;
+                double v;
+                if (op.kind == TK_CAP_HIST) {
+                    double vb = op.b >= 0 ? __ldg(x_prev + (int64_t)op.b * B + b) : 0.0;
+                    v = dmul(-vt[op.g * TS], dsub(va, vb));
+                } else {
+                    v = dmul(vt[op.g * TS], va);
+                }
+                vt[op.out * TS] = v;
+            }
+        }
+        for (int i = 0; i < m.n_src; ++i) {
+            SrcOp op = m.src_ops[i];
+            double v;
+            if (src_val) {
+                v = __ldg(src_val + (int64_t)op.index * B + b);
+            } else {
+                double base = __ldg(params + (int64_t)op.param * B + b);
+                if (op.is_sin) base = dadd(base, __ldg(params + (int64_t)(op.param + 1) * B + b));
+                v = dmul(base, scale);
+            }
+            vt[op.out * TS] = v;
+        }
+        for (int i = 0; i < m.n_mos; ++i) {
+            MosOp op = m.mos_ops[i];
+            double Vth = __ldg(params + (int64_t)op.param * B + b);
+            double K = __ldg(params + (int64_t)(op.param + 1) * B + b);
+            double lambda = __ldg(params + (int64_t)(op.param + 2) * B + b);
+            double Vd = op.d >= 0 ? __ldg(x + (int64_t)op.d * B + b) : 0.0;
+            double Vg = op.g >= 0 ? __ldg(x + (int64_t)op.g * B + b) : 0.0;
+            double Vs = op.s >= 0 ? __ldg(x + (int64_t)op.s * B + b) : 0.0;
+            double gd, gg, gs, cst;
+            mos_eval(Vth, K, lambda, op.is_p != 0, P.c.mos_off_gds, Vd, Vg, Vs, gd, gg, gs, cst);
+            vt[op.out * TS] = gd;
+            vt[(op.out + 1) * TS] = gg;
+            vt[(op.out + 2) * TS] = gs;
+            vt[(op.out + 3) * TS] = cst;
+        }
+        // ordered gather per slot
+        int e = m.slot_ptr[0];
+        for (int s = 0; s < m.n_slots; ++s) {
+            const int e1 = m.slot_ptr[s + 1];
+            double acc = 0.0;
+            for (; e < e1; ++e) {
+                uint32_t w = m.slot_entries[e];
+                double v = vt[(w >> 8) * TS];
+                acc = (w & 64u) ? dsub(acc, v) : dadd(acc, v);
+            }
+            if (s < m.nnz) vals[(int64_t)s * B + b] = acc;
+            else rhs[(int64_t)(s - m.nnz) * B + b] = acc;
+        }
+    }
+}
+
+// =============================================================================
+// batched dense LU solve (parity probe for the solver)
+// =============================================================================
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+lu_solve_kernel(int N, int64_t B, const double* __restrict__ A, const double* __restrict__ bvec,
+                double* __restrict__ xout, int32_t* __restrict__ perm_out, int32_t* __restrict__ singular,
+                double eps) {
+    extern __shared__ double smem[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    double* S = smem + (size_t)wib * (32 * kLD + 32);
+    double* bs = S + 32 * kLD;
+    const int64_t b = (int64_t)blockIdx.x * kWarpsPerBlock + wib;
+    if (b >= B) return;
+    for (int idx = lane; idx < N * N; idx += 32) {
+        int i = idx / N, j = idx - i * N;
+        S[i * kLD + j] = A[(int64_t)idx * B + b];
+    }
+    bs[lane] = lane < N ? bvec[(int64_t)lane * B + b] : 0.0;
+    __syncwarp();
+    int perm;
+    bool sing = lu_solve_warp(S, bs, N, lane, eps, perm);
+    if (lane < N) {
+        xout[(int64_t)lane * B + b] = bs[lane];
+        if (perm_out) perm_out[(int64_t)lane * B + b] = perm;
+    }
+    if (lane == 0 && singular) singular[b] = sing ? 1 : 0;
+}
+
+// =============================================================================
+// fused Newton kernels
+// =============================================================================
+struct BlockProg {  // block-shared copy of the row program
+    uint32_t* words;
+};
+
+__device__ __forceinline__ const uint32_t* load_prog(const DevMode& m, uint32_t* dst) {
+    for (int i = threadIdx.x; i < m.row_len * 32; i += blockDim.x) dst[i] = m.row_prog[i];
+    __syncthreads();
+    return dst;
+}
+
+// ConvController::baseGmin (include/dcanalysis.hpp:45-48)
+__device__ __forceinline__ double base_gmin(const csim_constants& c, double s) {
+    if (s < 0.0) s = 0.0;
+    if (s > 1.0) s = 1.0;
+    return dadd(dmul(c.gmin_high_base, dsub(1.0, s)), dmul(c.gmin_low_base, s));
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+dc_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double* __restrict__ xout,
+          int32_t* __restrict__ iters, uint64_t* __restrict__ pivot_hash, uint32_t* __restrict__ status) {
+    extern __shared__ double smem[];
+    const DevMode& m = P.m[CSIM_MODE_DC];
+    const csim_constants& c = P.c;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int N = P.N;
+    const size_t wd = warp_mem_doubles(m.n_values);
+    uint32_t* progbuf = reinterpret_cast<uint32_t*>(smem + wd * kWarpsPerBlock);
+    const uint32_t* prog = load_prog(m, progbuf);
+    const int64_t b = (int64_t)blockIdx.x * kWarpsPerBlock + wib;
+    if (b >= B) return;
+    WarpMem w = carve(smem + wd * wib, m.n_values);
+
+    uint64_t h = pivot_hash ? pivot_hash[b] : CSIM_PIVOT_HASH_INIT;
+    uint32_t st = 0;
+    double x = 0.0;  // lane i holds x(i)
+    w.xs[lane] = 0.0;
+    eval_static(m, params, B, b, 0.0, 0.0, w.vt, lane);
+    __syncwarp();
+    int gmin_slot = -1;
+    for (int i = 0; i < m.n_static; ++i)
+        if (m.static_ops[i].kind == SK_GMIN) gmin_slot = m.static_ops[i].out;
+
+    if (!P.has_mos) {
+        // dcSolveDirectLU (src/dcanalysis.cpp:46-68): one solve at scale 1, no gmin, no damping
+        eval_src_dc(m, params, B, b, 1.0, w.vt, lane);
+        __syncwarp();
+        assemble(m, prog, w, N, lane);
+        int perm;
+        if (lu_solve_warp(w.S, w.bs, N, lane, c.lu_eps, perm)) st |= CSIM_ST_LU_SINGULAR;
+        h = hash_update(h, perm, N, lane);
+        x = w.bs[lane];
+        if (iters && lane < c.dc_ramp_steps) iters[(int64_t)lane * B + b] = lane == 0 ? 1 : 0;
+    } else {
+        // dcSolveNewtonLU (src/dcanalysis.cpp:95-163)
+        for (int step = 1; step <= c.dc_ramp_steps; ++step) {
+            const double scale = (double)step / (double)c.dc_ramp_steps;
+            double gmin = base_gmin(c, scale);
+            double prevErr = CUDART_INF;
+            eval_src_dc(m, params, B, b, scale, w.vt, lane);
+            int count = 0;
+            for (int iter = 0; iter < c.dc_max_iters; ++iter) {
+                ++count;
+                if (lane == 0) w.vt[gmin_slot] = gmin;
+                eval_mos(m, params, B, b, c.mos_off_gds, w.xs, w.vt, lane);
+                __syncwarp();
+                assemble(m, prog, w, N, lane);
+                int perm;
+                if (lu_solve_warp(w.S, w.bs, N, lane, c.lu_eps, perm)) st |= CSIM_ST_LU_SINGULAR;
+                h = hash_update(h, perm, N, lane);
+                const double xr = lane < N ? w.bs[lane] : 0.0;
+                if (__any_sync(kFull, !lane_finite(xr))) {  // dcanalysis.cpp:135-138
+                    st |= CSIM_ST_NONFINITE;
+                    double g10 = dmul(gmin, c.dc_nonfinite_mul);
+                    gmin = g10 < c.dc_nonfinite_cap ? g10 : c.dc_nonfinite_cap;
+                    continue;
+                }
+                // ConvController::update (src/dcanalysis.cpp:268-307)
+                const double xn = dadd(x, dmul(c.dc_alpha, dsub(xr, x)));
+                const double err = warp_norm2(dsub(xn, x));
+                const double gbase = base_gmin(c, scale);
+                double gnext = gbase;
+                if (!(iter == 0 || !lane_finite(prevErr))) {
+                    if (err > dmul(prevErr, c.slow_conv_ratio)) {
+                        double g2 = dmul(gmin, 2.0);
+                        gnext = g2 < c.gmin_abs_max ? g2 : c.gmin_abs_max;
+                    } else if (err < dmul(prevErr, c.fast_conv_ratio)) {
+                        gnext = dadd(dmul(0.5, gmin), dmul(0.5, gbase));
+                    } else {
+                        gnext = dadd(dmul(0.7, gmin), dmul(0.3, gbase));
+                    }
+                }
+                x = xn;
+                __syncwarp();
+                w.xs[lane] = x;
+                __syncwarp();
+                gmin = gnext;
+                prevErr = err;
+                if (err < c.dc_tol) break;
+                if (iter == c.dc_max_iters - 1) st |= CSIM_ST_DC_UNCONVERGED;
+            }
+            if (iters && lane == 0) iters[(int64_t)(step - 1) * B + b] = count;
+        }
+    }
+    if (lane < N) xout[(int64_t)lane * B + b] = x;
+    if (lane == 0) {
+        if (pivot_hash) pivot_hash[b] = h;
+        if (status) status[b] |= st;
+    }
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+tran_kernel(DevPlan P, DevTran T, int64_t B, const double* __restrict__ params, double* __restrict__ xio,
+            double* __restrict__ wave, int32_t* __restrict__ iters_total, uint8_t* __restrict__ iters_step,
+            uint64_t* __restrict__ pivot_hash, uint32_t* __restrict__ status) {
+    extern __shared__ double smem[];
+    const DevMode& m = P.m[CSIM_MODE_TRAN];
+    const csim_constants& c = P.c;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int N = P.N;
+    const size_t wd = warp_mem_doubles(m.n_values);
+    uint32_t* progbuf = reinterpret_cast<uint32_t*>(smem + wd * kWarpsPerBlock);
+    const uint32_t* prog = load_prog(m, progbuf);
+    const int64_t b = (int64_t)blockIdx.x * kWarpsPerBlock + wib;
+    if (b >= B) return;
+    WarpMem w = carve(smem + wd * wib, m.n_values);
+
+    uint64_t h = pivot_hash ? pivot_hash[b] : CSIM_PIVOT_HASH_INIT;
+    uint32_t st = 0;
+    int total = 0;
+    double x = lane < N ? xio[(int64_t)lane * B + b] : 0.0;
+    w.xs[lane] = x;
+    eval_static(m, params, B, b, T.dt, c.tran_gmin, w.vt, lane);
+    __syncwarp();
+    const int r0 = T.out_begin_step / T.out_stride;
+    const int probe = lane < T.n_probes ? T.probes[lane] : 0;
+
+    for (int step = T.step_begin; step < T.step_end; ++step) {
+        // companion-model state = functions of the last accepted x (tanalisis.cpp:139-180, 381-417)
+        w.xp[lane] = x;
+        __syncwarp();
+        eval_step(m, w.xp, w.vt, lane);
+        eval_src_tran(m, T, params, B, b, step, w.vt, lane);
+        int count = 0;
+        bool dead = false;
+        for (int iter = 0; iter < c.tran_max_iters; ++iter) {  // tanalisis.cpp:258
+            ++count;
+            eval_mos(m, params, B, b, c.mos_off_gds, w.xs, w.vt, lane);
+            __syncwarp();
+            assemble(m, prog, w, N, lane);
+            int perm;
+            if (lu_solve_warp(w.S, w.bs, N, lane, c.lu_eps, perm)) st |= CSIM_ST_LU_SINGULAR;
+            h = hash_update(h, perm, N, lane);
+            const double xr = lane < N ? w.bs[lane] : 0.0;
+            if (__any_sync(kFull, !lane_finite(xr))) {  // tanalisis.cpp:360-362 (the reference throws)
+                st |= CSIM_ST_NONFINITE;
+                dead = true;
+                break;
+            }
+            const double xn = dadd(x, dmul(c.tran_alpha, dsub(xr, x)));  // tanalisis.cpp:365
+            const double err = warp_norm2(dsub(xn, x));                   // tanalisis.cpp:366
+            x = xn;
+            __syncwarp();
+            w.xs[lane] = x;
+            __syncwarp();
+            if (err < c.tran_tol) break;
+            if (iter == c.tran_max_iters - 1) st |= CSIM_ST_TRAN_UNCONVERGED;
+        }
+        total += count;
+        if (iters_step && lane == 0) iters_step[(int64_t)step * B + b] = (uint8_t)count;
+        if (dead) break;
+        if ((step + 1) % T.out_stride == 0 && step >= T.out_begin_step && lane < T.n_probes) {
+            const int64_t r = (step + 1) / T.out_stride - 1 - r0;
+            wave[((int64_t)b * T.n_probes + lane) * T.wave_ld + r] = w.xs[probe];
+        }
+    }
+    if (lane < N) xio[(int64_t)lane * B + b] = x;
+    if (lane == 0) {
+        if (iters_total) iters_total[b] += total;
+        if (pivot_hash) pivot_hash[b] = h;
+        if (status) status[b] |= st;
+    }
+}
+
+// =============================================================================
+// launch wrappers
+// =============================================================================
+static size_t newton_smem_bytes(const DevMode& m) {
+    return (warp_mem_doubles(m.n_values) * kWarpsPerBlock) * sizeof(double) + (size_t)m.row_len * 32 * sizeof(uint32_t);
+}
+
+cudaError_t launch_stamp_csr(const DevPlan& P, int mode, int64_t B, const double* params, const double* x,
+                             const double* x_prev, const double* src_val, double dt, double scale, double gmin,
+                             double* vals, double* rhs, int sm_count, cudaStream_t stream) {
+    const DevMode& m = P.m[mode];
+    size_t smem = (size_t)m.n_values * kStampThreads * sizeof(double);
+    int64_t blocks = (B + kStampThreads - 1) / kStampThreads;
+    (void)sm_count;
+    if (mode == CSIM_MODE_DC) {
+        cudaFuncSetAttribute(stamp_csr_kernel<CSIM_MODE_DC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        stamp_csr_kernel<CSIM_MODE_DC><<<(unsigned)blocks, kStampThreads, smem, stream>>>(
+            P, B, params, x, x_prev, src_val, dt, scale, gmin, vals, rhs);
+    } else {
+        cudaFuncSetAttribute(stamp_csr_kernel<CSIM_MODE_TRAN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        stamp_csr_kernel<CSIM_MODE_TRAN><<<(unsigned)blocks, kStampThreads, smem, stream>>>(
+            P, B, params, x, x_prev, src_val, dt, scale, gmin, vals, rhs);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_lu_solve(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                            int32_t* singular, double eps, cudaStream_t stream) {
+    size_t smem = (size_t)kWarpsPerBlock * (32 * kLD + 32) * sizeof(double);
+    cudaFuncSetAttribute(lu_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int64_t blocks = (B + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    lu_solve_kernel<<<(unsigned)blocks, kWarpsPerBlock * 32, smem, stream>>>(N, B, A, b, x, perm, singular, eps);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_dc(const DevPlan& P, int64_t B, const double* params, double* x, int32_t* iters,
+                      uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream) {
+    size_t smem = newton_smem_bytes(P.m[CSIM_MODE_DC]);
+    cudaFuncSetAttribute(dc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int64_t blocks = (B + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    dc_kernel<<<(unsigned)blocks, kWarpsPerBlock * 32, smem, stream>>>(P, B, params, x, iters, pivot_hash, status);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tran(const DevPlan& P, const DevTran& T, int64_t B, const double* params, double* x, double* wave,
+                        int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status,
+                        cudaStream_t stream) {
+    size_t smem = newton_smem_bytes(P.m[CSIM_MODE_TRAN]);
+    cudaFuncSetAttribute(tran_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int64_t blocks = (B + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    tran_kernel<<<(unsigned)blocks, kWarpsPerBlock * 32, smem, stream>>>(P, T, B, params, x, wave, iters_total,
+                                                                         iters_step, pivot_hash, status);
+    return cudaGetLastError();
+}
+
+}  // namespace csim

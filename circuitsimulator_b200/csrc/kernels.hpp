@@ -1,0 +1,25 @@
+// kernels.hpp — launch wrappers implemented in kernels.cu (callable from plain C++).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "device_plan.cuh"
+
+namespace csim {
+
+constexpr int kWarpsPerBlock = 4;   // fused Newton kernels: 4 instances per CTA
+constexpr int kStampThreads = 128;  // standalone assembly: instances per CTA
+
+cudaError_t launch_stamp_csr(const DevPlan& P, int mode, int64_t B, const double* params, const double* x,
+                             const double* x_prev, const double* src_val, double dt, double scale, double gmin,
+                             double* vals, double* rhs, int sm_count, cudaStream_t stream);
+cudaError_t launch_lu_solve(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                            int32_t* singular, double eps, cudaStream_t stream);
+cudaError_t launch_dc(const DevPlan& P, int64_t B, const double* params, double* x, int32_t* iters,
+                      uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream);
+cudaError_t launch_tran(const DevPlan& P, const DevTran& T, int64_t B, const double* params, double* x, double* wave,
+                        int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status,
+                        cudaStream_t stream);
+
+}  // namespace csim

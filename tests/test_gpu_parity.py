@@ -1,0 +1,266 @@
+"""GPU parity: the CUDA path (through the C ABI) against the oracle on the same seeded inputs.
+Bar: bit-identical doubles, identical Newton-iteration counts and pivot sequences."""
+import numpy as np
+import pytest
+
+from oracle import oraclelib as O
+from support import GOLDEN, assert_same_bits, load_golden, make_plan, n_steps_of, perturb
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch
+
+
+def u64(t):
+    return t.cpu().numpy().view(np.uint64)
+
+
+def dev(torch, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+@pytest.mark.parametrize("name,mode", [("buffer", 0), ("buffer", 1), ("dbmixer", 0), ("dbmixer", 1)])
+def test_stamp_csr_bit_exact(torch, name, mode):
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden(name)
+    plan = make_plan(topo)
+    B, N, dt = 96, topo.n_unknowns, float(g["dt"])
+    P = perturb(topo.params, topo, B, 42)
+    rng = np.random.default_rng(5)
+    X = np.stack([g["x_dc"] + rng.normal(scale=0.3, size=N) for _ in range(B)])
+    XP = np.stack([g["x_dc"] + rng.normal(scale=0.3, size=N) for _ in range(B)])
+    ns = len(topo.source_elems())
+    SV = rng.uniform(-1, 3, size=(B, ns))
+    gmin = 1e-6 if mode else 4.2e-7
+    vals, rhs = capi.stamp_csr(plan, mode, dev(torch, P.T), dev(torch, X.T), dev(torch, XP.T), dev(torch, SV.T),
+                               dt=dt, gmin=gmin)
+    torch.cuda.synchronize()
+    vals, rhs = vals.cpu().numpy(), rhs.cpu().numpy()
+    rowptr, colidx = plan.pattern(mode)
+    rows = np.repeat(np.arange(N), np.diff(rowptr))
+    for b in range(B):
+        G, I = O.stamp(topo, mode, P[b], X[b], XP[b], SV[b], dt=dt, gmin=gmin)
+        assert_same_bits(vals[:, b], G[rows, colidx], f"{name} vals inst {b}")
+        assert_same_bits(rhs[:, b], I, f"{name} rhs inst {b}")
+        G2 = G.copy()
+        G2[rows, colidx] = 0.0
+        assert not G2.any(), "oracle has a non-zero outside the structural pattern"
+    # DC sources from parameters (src_val = NULL -> evalDC(scale))
+    if mode == 0:
+        vals2, rhs2 = capi.stamp_csr(plan, 0, dev(torch, P.T), dev(torch, X.T), None, None, scale=0.7, gmin=gmin)
+        for b in (0, 5):
+            G, I = O.stamp(topo, 0, P[b], X[b], None, O.src_dc(topo, P[b], 0.7), gmin=gmin)
+            assert_same_bits(rhs2[:, b].cpu().numpy(), I, "evalDC rhs")
+
+
+@pytest.mark.parametrize("n", [1, 2, 7, 13, 31, 32])
+def test_lu_solve_bit_exact(torch, n):
+    from circuitsimulator_b200 import capi
+    rng = np.random.default_rng(n)
+    B = 64
+    A = rng.normal(size=(B, n, n))
+    A[rng.random(size=A.shape) < 0.6] = 0.0  # sparse-ish, exercises zero skipping
+    A += np.eye(n)[None] * rng.normal(size=(B, n, 1))
+    if n >= 2:
+        A[3, :, :] = 1.0  # singular
+        A[4, 0, 0], A[4, 1, 0] = 1.0, -1.0  # tie in |.|: first max wins
+        A[5] = 0.0
+    b = rng.normal(size=(B, n))
+    x, perm, sing = capi.lu_solve(dev(torch, A.reshape(B, n * n).T), dev(torch, b.T))
+    torch.cuda.synchronize()
+    x, perm, sing = x.cpu().numpy(), perm.cpu().numpy(), sing.cpu().numpy()
+    for k in range(B):
+        xo, po, failed = O.lu_solve(A[k], b[k])
+        assert sing[k] == failed
+        assert_same_bits(x[:, k], xo, f"x of system {k}")
+        assert np.array_equal(perm[:, k], po), (k, perm[:, k], po)
+
+
+@pytest.mark.parametrize("name,B", [("buffer", 40), ("dbmixer", 24)])
+def test_dc_bit_exact(torch, name, B):
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden(name)
+    plan = make_plan(topo)
+    P = perturb(topo.params, topo, B, 20261104)
+    d = capi.dc(plan, dev(torch, P.T))
+    torch.cuda.synchronize()
+    x, iters, h, st = d["x"].cpu().numpy(), d["iters"].cpu().numpy(), u64(d["hash"]), d["status"].cpu().numpy()
+    assert_same_bits(x[:, 0], g["x_dc"], "nominal DC vs golden")
+    assert np.array_equal(iters[:, 0], g["dc_iters"]) and h[0] == np.uint64(g["dc_hash"])
+    for b in range(B):
+        o = O.dc(topo, P[b])
+        assert_same_bits(x[:, b], o["x"], f"{name} DC inst {b}")
+        assert np.array_equal(iters[:, b], o["iters"]), (b, iters[:, b], o["iters"])
+        assert h[b] == np.uint64(o["hash"]) and int(st[b]) == o["status"]
+
+
+def test_dc_linear_circuit_direct_path(torch):
+    """No MOSFET -> dcSolveDirectLU: one solve, no gmin (src/dcanalysis.cpp:46-68)."""
+    from circuitsimulator_b200 import capi
+    # V1 1 0 DC 5 ; R1 1 2 1k ; R2 2 0 2k ; L1 2 3 1u ; R3 3 0 500 ; C1 3 0 1n ; I1 0 2 DC 1m
+    ty = np.array([O.ELEM_V, O.ELEM_R, O.ELEM_R, O.ELEM_L, O.ELEM_R, O.ELEM_C, O.ELEM_I], np.int32)
+    nodes = np.array([[0, -1, -1, -1], [0, 1, -1, -1], [1, -1, -1, -1], [1, 2, -1, -1], [2, -1, -1, -1],
+                      [2, -1, -1, -1], [-1, 1, -1, -1]], np.int32)
+    branch = np.array([3, -1, -1, 4, -1, -1, -1], np.int32)
+    off = np.array([0, 6, 7, 8, 9, 10, 11], np.int32)
+    nominal = np.array([5, 0, 0, 0, 0, 0, 1e3, 2e3, 1e-6, 500, 1e-9, 1e-3, 0, 0, 0, 0, 0], np.float64)
+    topo = O.Topology(5, 3, ty, np.zeros(7, np.int32), nodes, branch, off, 17, nominal)
+    plan = make_plan(topo)
+    B = 9
+    P = perturb(nominal, topo, B, 3)
+    d = capi.dc(plan, dev(torch, P.T))
+    torch.cuda.synchronize()
+    for b in range(B):
+        o = O.dc(topo, P[b])
+        assert_same_bits(d["x"][:, b].cpu().numpy(), o["x"], f"linear DC {b}")
+        assert u64(d["hash"])[b] == np.uint64(o["hash"])
+        assert list(d["iters"][:, b].cpu().numpy()) == list(o["iters"])
+
+
+def test_tran_buffer_full_bit_exact(torch):
+    """Config 1 + perturbed instances: every unknown at every one of the 300 steps, Newton counts per step,
+    pivot-sequence hash."""
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    plan = make_plan(topo)
+    B, dt, ns, N = 12, float(g["dt"]), n_steps_of(g), topo.n_unknowns
+    P = perturb(topo.params, topo, B, 20261104 + 3)
+    params = dev(torch, P.T)
+    d = capi.dc(plan, params)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    setup = capi.TranSetup(dt, ns, m, grp, tab, probes=np.arange(N))
+    x = d["x"].clone()
+    t = capi.tran(plan, params, x, setup, pivot_hash=d["hash"], status=d["status"], want_iters_step=True)
+    torch.cuda.synchronize()
+    wave = t["wave"].cpu().numpy()  # [B, N, ns]
+    assert_same_bits(wave[0].T, g["wave"], "nominal buffer waveform vs golden")
+    assert np.array_equal(t["iters_step"][:, 0].cpu().numpy(), g["iters_step"])
+    assert u64(t["hash"])[0] == np.uint64(g["hash"])
+    pg = np.load(f"{GOLDEN}/buffer_perturbed.npz")
+    for k in range(5):  # instances 1..5 of this recipe are pinned against the reference itself
+        assert_same_bits(P[k + 1], pg["params"][k], "perturbation recipe")
+        assert_same_bits(t["x"][:, k + 1].cpu().numpy(), pg["x_final"][k], f"final state inst {k+1} vs golden")
+        assert u64(t["hash"])[k + 1] == pg["hash"][k]
+    for b in range(B):
+        od = O.dc(topo, P[b])
+        ot = O.tran(topo, P[b], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(wave[b].T, ot["wave"], f"waveform inst {b}")
+        assert np.array_equal(t["iters_step"][:, b].cpu().numpy(), ot["iters_step"])
+        assert int(t["iters_total"][b]) == ot["total"]
+        assert u64(t["hash"])[b] == np.uint64(ot["hash"])
+        assert int(t["status"][b]) == (od["status"] | ot["status"])
+
+
+def test_tran_dbmixer_bit_exact(torch):
+    """Config 2 (reduced length for the per-instance oracle): DC + 1500 steps, 10 instances; chunked launches
+    (resume from state) must equal one launch."""
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("dbmixer")
+    plan = make_plan(topo)
+    B, dt, ns, N = 10, float(g["dt"]), 1500, topo.n_unknowns
+    P = perturb(topo.params, topo, B, 20261104)
+    params = dev(torch, P.T)
+    d = capi.dc(plan, params)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    setup = capi.TranSetup(dt, ns, m, grp, tab, probes=np.arange(N))
+    x = d["x"].clone()
+    t = capi.tran(plan, params, x, setup, pivot_hash=d["hash"].clone(), status=d["status"].clone(),
+                  want_iters_step=True)
+    torch.cuda.synchronize()
+    wave = t["wave"].cpu().numpy()
+    assert_same_bits(wave[0].T[:400], g["wave_first"], "nominal dbmixer first 400 steps vs golden")
+    assert np.array_equal(t["iters_step"][:, 0].cpu().numpy(), g["iters_step"][:ns])
+    for b in range(B):
+        od = O.dc(topo, P[b])
+        ot = O.tran(topo, P[b], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(wave[b].T, ot["wave"], f"dbmixer waveform inst {b}")
+        assert np.array_equal(t["iters_step"][:, b].cpu().numpy(), ot["iters_step"])
+        assert u64(t["hash"])[b] == np.uint64(ot["hash"])
+    # chunked: 3 launches with host-visible state in between
+    x2 = d["x"].clone()
+    h2, s2 = d["hash"].clone(), d["status"].clone()
+    wave2, tot2 = None, None
+    for lo, hi in ((0, 500), (500, 501), (501, ns)):
+        r = capi.tran(plan, params, x2, setup, step_begin=lo, step_end=hi, wave=wave2, iters_total=tot2,
+                      pivot_hash=h2, status=s2)
+        wave2, tot2 = r["wave"], r["iters_total"]
+    torch.cuda.synchronize()
+    assert_same_bits(wave2.cpu().numpy(), wave, "chunked == single launch")
+    assert np.array_equal(u64(h2), u64(t["hash"])) and np.array_equal(tot2.cpu().numpy(), t["iters_total"].cpu().numpy())
+
+
+def test_tran_output_decimation_and_tstart(torch):
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    plan = make_plan(topo)
+    dt, ns = float(g["dt"]), 120
+    params = dev(torch, topo.params[:, None])
+    d = capi.dc(plan, params)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    probes = np.array([8, 1], np.int32)  # V(118), V(101)
+    setup = capi.TranSetup(dt, ns, m, grp, tab, probes=probes, out_stride=7, out_begin_step=30)
+    t = capi.tran(plan, params, d["x"].clone(), setup)
+    torch.cuda.synchronize()
+    steps = [s for s in range(ns) if (s + 1) % 7 == 0 and s >= 30]
+    w = t["wave"].cpu().numpy()[0]
+    assert w.shape[1] == setup.n_out == len(steps)
+    assert_same_bits(w.T, g["wave"][steps][:, probes], "decimated probes")
+
+
+def test_host_buffer_api_equals_device_api(torch):
+    """csim_batch_* (host pointers, copies inside) == csim_dev_* ; nominal dbmixer DC vs golden."""
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("dbmixer")
+    plan = make_plan(topo)
+    B, dt, ns = 6, float(g["dt"]), 300
+    P = perturb(topo.params, topo, B, 99)
+    batch = capi.Batch(plan, B)
+    batch.set_params(P.T)
+    d = batch.dc()
+    assert_same_bits(d["x"][:, 0], g["x_dc"], "host API DC")
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    setup = capi.TranSetup(dt, ns, m, grp, tab, probes=np.array([1, 2], np.int32))
+    out = batch.tran(setup, want_iters_step=True)
+    assert batch.last_kernel_ms > 0
+    assert_same_bits(out["x_dc"], d["x"], "x_dc")
+    assert_same_bits(out["wave"][0].T, g["wave_first"][:ns][:, [1, 2]], "host API waveform vs golden")
+    assert np.array_equal(out["iters_step"][:, 0], g["iters_step"][:ns])
+    for b in range(B):
+        od = O.dc(topo, P[b])
+        ot = O.tran(topo, P[b], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(out["x_final"][:, b], ot["x"], f"x_final {b}")
+        assert out["hash"][b] == np.uint64(ot["hash"]) and out["iters_total"][b] == ot["total"]
+
+
+def test_degenerate_parameters_follow_reference_rules(torch):
+    """R == 0 skips the stamp, C <= 0 skips the companion, L <= 0 leaves an empty branch row -> singular LU ->
+    zero vector (src/element.cpp:20-23, src/tanalisis.cpp:65,296, include/solver.hpp:58-61,94-97)."""
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    plan = make_plan(topo)
+    dt, ns = float(g["dt"]), 6
+    P = np.repeat(topo.params[None], 4, 0)
+    e_c = [e for e in range(topo.n_elems) if topo.elem_type[e] == O.ELEM_C]
+    e_l = [e for e in range(topo.n_elems) if topo.elem_type[e] == O.ELEM_L]
+    e_r = [e for e in range(topo.n_elems) if topo.elem_type[e] == O.ELEM_R]
+    P[1, topo.elem_param[e_c[0]]] = -1e-12
+    P[2, topo.elem_param[e_l[0]]] = 0.0
+    P[3, topo.elem_param[e_r[1]]] = 0.0
+    params = dev(torch, P.T)
+    d = capi.dc(plan, params)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    setup = capi.TranSetup(dt, ns, m, grp, tab, probes=np.arange(topo.n_unknowns))
+    t = capi.tran(plan, params, d["x"].clone(), setup, pivot_hash=d["hash"], status=d["status"], want_iters_step=True)
+    torch.cuda.synchronize()
+    for b in range(4):
+        od = O.dc(topo, P[b])
+        ot = O.tran(topo, P[b], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(t["wave"][b].cpu().numpy().T, ot["wave"], f"degenerate inst {b}")
+        assert int(t["status"][b]) == (od["status"] | ot["status"]), b
+        assert np.array_equal(t["iters_step"][:, b].cpu().numpy(), ot["iters_step"])
+    assert int(t["status"][2]) & capi.ST_LU_SINGULAR
