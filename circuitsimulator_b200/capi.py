@@ -30,6 +30,7 @@ EXPORTS = [
     "csim_dev_stamp_csr", "csim_dev_lu_solve", "csim_dev_dc", "csim_dev_tran",
     "csim_batch_create", "csim_batch_destroy", "csim_batch_set_params", "csim_batch_dc",
     "csim_batch_tran", "csim_batch_last_kernel_ms", "csim_pivot_hash_update",
+    "csim_host_stamp_csr", "csim_host_lu_solve",
 ]
 
 

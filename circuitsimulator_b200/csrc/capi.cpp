@@ -65,6 +65,19 @@ struct csim_batch {
     float last_ms = 0.f;
 };
 
+namespace {
+struct DevBuf {  // RAII scratch for the host-pointer convenience calls
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t put(const void* src, size_t bytes) {
+        cudaError_t e = cudaMalloc(&p, bytes ? bytes : 8);
+        if (e == cudaSuccess && src && bytes) e = cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice);
+        return e;
+    }
+    template <typename T> T* as() { return static_cast<T*>(p); }
+};
+}  // namespace
+
 extern "C" {
 
 const char* csim_last_error(void) { return g_err.c_str(); }
@@ -451,6 +464,54 @@ int csim_batch_tran(csim_batch* b, const csim_tran_args* a, double* x_dc, double
     CUC(cudaEventElapsedTime(&b->last_ms, b->ev0, b->ev1));
     cleanup();
 #undef CUC
+    return CSIM_OK;
+}
+
+
+int csim_host_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double* params, const double* x,
+                        const double* x_prev, const double* src_val, double dt, double source_scale, double gmin,
+                        double* vals, double* rhs) {
+    int rc = need_device(plan, "csim_host_stamp_csr");
+    if (rc) return rc;
+    if (mode < 0 || mode > 1 || B <= 0 || !params || !x || !vals || !rhs)
+        return fail(CSIM_E_INVALID, "csim_host_stamp_csr: bad argument");
+    const size_t N = plan->host.N, P = plan->host.n_params, S = plan->host.n_sources;
+    const size_t nnz = plan->host.mode[mode].colidx.size();
+    DevBuf dp, dx, dxp, dsv, dv, dr;
+    CU(dp.put(params, sizeof(double) * P * B));
+    CU(dx.put(x, sizeof(double) * N * B));
+    if (x_prev) CU(dxp.put(x_prev, sizeof(double) * N * B));
+    if (src_val) CU(dsv.put(src_val, sizeof(double) * S * B));
+    CU(dv.put(nullptr, sizeof(double) * nnz * B));
+    CU(dr.put(nullptr, sizeof(double) * N * B));
+    rc = csim_dev_stamp_csr(plan, mode, B, dp.as<double>(), dx.as<double>(), x_prev ? dxp.as<double>() : nullptr,
+                            src_val ? dsv.as<double>() : nullptr, dt, source_scale, gmin, dv.as<double>(),
+                            dr.as<double>(), nullptr);
+    if (rc) return rc;
+    CU(cudaMemcpy(vals, dv.p, sizeof(double) * nnz * B, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(rhs, dr.p, sizeof(double) * N * B, cudaMemcpyDeviceToHost));
+    return CSIM_OK;
+}
+
+int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                       int32_t* singular, double lu_eps) {
+    if (n <= 0 || n > 32) return fail(CSIM_E_UNSUPPORTED, "csim_host_lu_solve: 1 <= n <= 32 required");
+    if (B <= 0 || !A || !b || !x) return fail(CSIM_E_INVALID, "csim_host_lu_solve: bad argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(CSIM_E_CUDA, "csim_host_lu_solve: no CUDA device (no CPU fallback)");
+    DevBuf dA, db, dx, dp, ds;
+    CU(dA.put(A, sizeof(double) * (size_t)n * n * B));
+    CU(db.put(b, sizeof(double) * (size_t)n * B));
+    CU(dx.put(nullptr, sizeof(double) * (size_t)n * B));
+    CU(dp.put(nullptr, sizeof(int32_t) * (size_t)n * B));
+    CU(ds.put(nullptr, sizeof(int32_t) * (size_t)B));
+    int rc = csim_dev_lu_solve(n, B, dA.as<double>(), db.as<double>(), dx.as<double>(), dp.as<int32_t>(),
+                               ds.as<int32_t>(), lu_eps, nullptr);
+    if (rc) return rc;
+    CU(cudaMemcpy(x, dx.p, sizeof(double) * (size_t)n * B, cudaMemcpyDeviceToHost));
+    if (perm) CU(cudaMemcpy(perm, dp.p, sizeof(int32_t) * (size_t)n * B, cudaMemcpyDeviceToHost));
+    if (singular) CU(cudaMemcpy(singular, ds.p, sizeof(int32_t) * (size_t)B, cudaMemcpyDeviceToHost));
     return CSIM_OK;
 }
 

@@ -1,0 +1,163 @@
+// facade.cpp — extern "C" window onto the C++ host layer for Python (ctypes): parse a netlist
+// with the product's own parser, lower it, tabulate sources.  Declared in include/csim_host.h.
+#include <cmath>
+#include <cstring>
+#include <sstream>
+#include <string>
+
+#include "../../include/csim_host.h"
+#include "csim/lower.hpp"
+#include "csim/parser.hpp"
+#include "csim/tanalisis.hpp"
+
+struct csimh_netlist {
+    Circuit ckt;
+    SimulationConfig sim;
+    csim::Lowered low;
+    std::string header;
+};
+
+namespace {
+thread_local std::string g_herr;
+void copy_str(const std::string& s, char* out, int cap) {
+    if (!out || cap <= 0) return;
+    std::snprintf(out, static_cast<std::size_t>(cap), "%s", s.c_str());
+}
+}  // namespace
+
+extern "C" {
+
+const char* csimh_last_error(void) { return g_herr.c_str(); }
+
+csimh_netlist* csimh_parse(const char* text) {
+    if (!text) return nullptr;
+    try {
+        auto* h = new csimh_netlist();
+        std::istringstream in(text);
+        NetlistParser parser(h->ckt, h->sim);
+        parser.parseStream(in, "<memory>");
+        h->sim.ensureDefaultOp();
+        h->ckt.assignEquationIndices();
+        h->low = csim::lower(h->ckt);
+        h->header = h->low.csv_header();
+        return h;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return nullptr;
+    }
+}
+
+void csimh_free(csimh_netlist* h) { delete h; }
+
+int csimh_dims(const csimh_netlist* h, int32_t* n_unknowns, int32_t* n_node_eq, int32_t* n_elems, int32_t* n_params,
+               int32_t* n_sources) {
+    if (!h) return -1;
+    if (n_unknowns) *n_unknowns = h->low.n_unknowns;
+    if (n_node_eq) *n_node_eq = h->low.n_node_eq;
+    if (n_elems) *n_elems = static_cast<int32_t>(h->low.elem_type.size());
+    if (n_params) *n_params = h->low.n_params;
+    if (n_sources) *n_sources = static_cast<int32_t>(h->low.source_elems.size());
+    return 0;
+}
+
+int csimh_topology(const csimh_netlist* h, int32_t* type, int32_t* flags, int32_t* nodes, int32_t* branch,
+                   int32_t* param_off, double* nominal) {
+    if (!h) return -1;
+    const csim::Lowered& L = h->low;
+    const std::size_t ne = L.elem_type.size();
+    std::memcpy(type, L.elem_type.data(), ne * 4);
+    std::memcpy(flags, L.elem_flags.data(), ne * 4);
+    std::memcpy(nodes, L.elem_nodes.data(), ne * 16);
+    std::memcpy(branch, L.elem_branch.data(), ne * 4);
+    std::memcpy(param_off, L.elem_param.data(), ne * 4);
+    std::memcpy(nominal, L.nominal.data(), L.nominal.size() * 8);
+    return 0;
+}
+
+int csimh_node_name(const csimh_netlist* h, int32_t eq, char* out, int32_t cap) {
+    if (!h || eq < 0 || eq >= h->low.n_node_eq) return -1;
+    copy_str(h->low.node_names[eq], out, cap);
+    return 0;
+}
+int csimh_elem_name(const csimh_netlist* h, int32_t idx, char* out, int32_t cap) {
+    if (!h || idx < 0 || idx >= static_cast<int32_t>(h->low.elem_names.size())) return -1;
+    copy_str(h->low.elem_names[idx], out, cap);
+    return 0;
+}
+int csimh_csv_header(const csimh_netlist* h, char* out, int32_t cap) {
+    if (!h) return -1;
+    copy_str(h->header, out, cap);
+    return static_cast<int>(h->header.size());
+}
+
+int csimh_tran_cfg(const csimh_netlist* h, double* tstep, double* tstop, double* tstart, int32_t* enabled) {
+    if (!h) return -1;
+    *tstep = h->sim.tran.tstep;
+    *tstop = h->sim.tran.tstop;
+    *tstart = h->sim.tran.tstart;
+    *enabled = h->sim.tran.enabled ? 1 : 0;
+    return 0;
+}
+int csimh_hb_cfg(const csimh_netlist* h, double* f0, int32_t* n_harm, int32_t* enabled) {
+    if (!h) return -1;
+    *f0 = h->sim.hb.f0;
+    *n_harm = h->sim.hb.nHarm;
+    *enabled = h->sim.hb.enabled ? 1 : 0;
+    return 0;
+}
+
+// equation indices of the .PLOTNV / .PRINT V(node) probes, in card order; returns the count
+int csimh_plot_probes(const csimh_netlist* h, int32_t* out, int32_t cap) {
+    if (!h) return -1;
+    int n = 0;
+    for (const PrintCommand& pc : h->sim.printCommands)
+        for (const ProbeSpec& p : pc.probes) {
+            if (p.kind != ProbeKind::NodeVoltage) continue;
+            auto it = h->ckt.nodeNameToId.find(p.node1);
+            if (it == h->ckt.nodeNameToId.end()) continue;
+            const int eq = h->ckt.nodes[it->second].eqIndex;
+            if (eq < 0) continue;
+            if (out && n < cap) out[n] = eq;
+            ++n;
+        }
+    return n;
+}
+
+// Host tabulation of the independent sources (host libm), csim_src_mode convention.
+// mode/group: [n_sources]; table: [n_sources][n_steps] capacity (n_groups <= n_sources rows used).
+int csimh_tabulate_sources(const csimh_netlist* h, double dt, int32_t n_steps, int32_t* mode, int32_t* group,
+                           double* table, int32_t* n_groups) {
+    if (!h) return -1;
+    csim::SourceTables T = csim::tabulate_sources(h->ckt, dt, n_steps);
+    std::memcpy(mode, T.mode.data(), T.mode.size() * 4);
+    std::memcpy(group, T.group.data(), T.group.size() * 4);
+    std::memcpy(table, T.table.data(), T.table.size() * 8);
+    *n_groups = T.n_groups;
+    return 0;
+}
+
+// S[s] = sin(2*pi*freq*(t-td)+phi), t=(s+1)*dt — one table row for a swept source
+int csimh_sin_table(double freq, double td, double phi, double dt, int32_t n_steps, double* out) {
+    for (int32_t s = 0; s < n_steps; ++s) {
+        const double t = (s + 1) * dt;
+        const double tau = t - td;
+        const double w = 2.0 * M_PI * freq;
+        out[s] = std::sin(w * tau + phi);
+    }
+    return 0;
+}
+
+// The reference's own driver signature, for drop-in checks from Python: DC + transient of the
+// nominal circuit, CSV written to `path`.  Returns 0, or -1 with csimh_last_error().
+int csimh_run_tran_csv(const csimh_netlist* h, const char* path) {
+    if (!h || !path) return -1;
+    try {
+        runTransientAnalysisBackwardEuler(h->ckt, h->sim, path);
+        return 0;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return -1;
+    }
+}
+
+}  // extern "C"

@@ -1,0 +1,156 @@
+"""Host side above the C ABI: the product's own .sp parser + lowering (C++: include/csim/*.hpp,
+circuitsimulator_b200/host/*.cpp) seen from Python, plus batch parameter generation."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+
+
+def _hlib():
+    L = capi.lib()
+    if not getattr(L, "_csimh_ready", False):
+        L.csimh_last_error.restype = C.c_char_p
+        L.csimh_parse.restype = C.c_void_p
+        L.csimh_parse.argtypes = [C.c_char_p]
+        L.csimh_free.argtypes = [C.c_void_p]
+        for name in ("csimh_dims", "csimh_topology", "csimh_node_name", "csimh_elem_name", "csimh_csv_header",
+                     "csimh_tran_cfg", "csimh_hb_cfg", "csimh_plot_probes", "csimh_run_tran_csv"):
+            getattr(L, name).restype = C.c_int
+        L.csimh_tabulate_sources.argtypes = [C.c_void_p, C.c_double, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p]
+        L.csimh_sin_table.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, C.c_void_p]
+        L._csimh_ready = True
+    return L
+
+
+class Netlist:
+    """A parsed netlist lowered to the flat topology of include/csim_b200.h."""
+
+    def __init__(self, text: str):
+        L = _hlib()
+        self.text = text
+        self._h = L.csimh_parse(text.encode())
+        if not self._h:
+            raise capi.CsimError("csimh_parse: " + L.csimh_last_error().decode(errors="replace"))
+        h = C.c_void_p(self._h)
+        d = [C.c_int32() for _ in range(5)]
+        L.csimh_dims(h, *[C.byref(v) for v in d])
+        self.n_unknowns, self.n_node_eq, self.n_elems, self.n_params, self.n_sources = [int(v.value) for v in d]
+        ne = self.n_elems
+        self.elem_type = np.zeros(ne, np.int32)
+        self.elem_flags = np.zeros(ne, np.int32)
+        self.elem_nodes = np.zeros((ne, 4), np.int32)
+        self.elem_branch = np.zeros(ne, np.int32)
+        self.elem_param = np.zeros(ne, np.int32)
+        self.params = np.zeros(max(self.n_params, 1), np.float64)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        L.csimh_topology(h, vp(self.elem_type), vp(self.elem_flags), vp(self.elem_nodes), vp(self.elem_branch),
+                         vp(self.elem_param), vp(self.params))
+        self.params = self.params[: self.n_params].copy()
+        buf = C.create_string_buffer(1 << 16)
+        self.node_names, self.elem_names = [], []
+        for eq in range(self.n_node_eq):
+            L.csimh_node_name(h, eq, buf, len(buf))
+            self.node_names.append(buf.value.decode())
+        for e in range(ne):
+            L.csimh_elem_name(h, e, buf, len(buf))
+            self.elem_names.append(buf.value.decode())
+        L.csimh_csv_header(h, buf, len(buf))
+        self.csv_header = buf.value.decode()
+        a, b, c_, en = C.c_double(), C.c_double(), C.c_double(), C.c_int32()
+        L.csimh_tran_cfg(h, C.byref(a), C.byref(b), C.byref(c_), C.byref(en))
+        self.tran = dict(tstep=a.value, tstop=b.value, tstart=c_.value, enabled=bool(en.value))
+        f0, nh = C.c_double(), C.c_int32()
+        L.csimh_hb_cfg(h, C.byref(f0), C.byref(nh), C.byref(en))
+        self.hb = dict(f0=f0.value, n_harm=int(nh.value), enabled=bool(en.value))
+        n = L.csimh_plot_probes(h, None, 0)
+        pr = np.zeros(max(n, 1), np.int32)
+        L.csimh_plot_probes(h, vp(pr), n)
+        self.plot_probes = pr[:n].copy()
+
+    @classmethod
+    def from_file(cls, path: str) -> "Netlist":
+        with open(path) as f:
+            return cls(f.read())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _hlib().csimh_free(C.c_void_p(self._h))
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def n_steps(self) -> int:
+        """nSteps = floor(tstop/dt + 1e-12) (reference: src/tanalisis.cpp:238)."""
+        return int(np.floor(self.tran["tstop"] / self.tran["tstep"] + 1e-12))
+
+    def source_elems(self):
+        return [e for e in range(self.n_elems) if self.elem_type[e] in (capi.ELEM_V, capi.ELEM_I)]
+
+    def plan(self, device: int = 0, consts=None) -> capi.Plan:
+        return capi.Plan(self.n_unknowns, self.n_node_eq, self.elem_type, self.elem_flags, self.elem_nodes,
+                         self.elem_branch, self.elem_param, self.n_params, device=device, consts=consts)
+
+    def source_tables(self, dt: float | None = None, n_steps: int | None = None):
+        """(src_mode, src_group, table[n_groups, n_steps]) tabulated with the host libm."""
+        dt = self.tran["tstep"] if dt is None else dt
+        n_steps = self.n_steps if n_steps is None else n_steps
+        ns = max(self.n_sources, 1)
+        mode = np.zeros(ns, np.int32)
+        group = np.zeros(ns, np.int32)
+        table = np.zeros((ns, max(n_steps, 1)), np.float64)
+        ng = C.c_int32()
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        _hlib().csimh_tabulate_sources(C.c_void_p(self._h), float(dt), int(n_steps), vp(mode), vp(group), vp(table),
+                                       C.byref(ng))
+        return mode[: self.n_sources], group[: self.n_sources], np.ascontiguousarray(table[: max(ng.value, 1)])
+
+    def tran_setup(self, probes=None, out_stride: int = 1, n_steps: int | None = None) -> capi.TranSetup:
+        n_steps = self.n_steps if n_steps is None else n_steps
+        dt = self.tran["tstep"]
+        mode, group, table = self.source_tables(dt, n_steps)
+        first = 0
+        while first < n_steps and (first + 1) * dt < self.tran["tstart"]:
+            first += 1
+        probes = self.plot_probes if probes is None else probes
+        return capi.TranSetup(dt, n_steps, mode, group, table, probes, out_stride=out_stride, out_begin_step=first)
+
+    def monte_carlo(self, B: int, seed: int, rel: float = 0.05, first: int = 0) -> np.ndarray:
+        """Instance parameters [P, B] (instance-minor): global instance 0 is nominal, instance i>0 is
+        nominal*(1+rel*u_i), u_i~U(-1,1) drawn row-wise from PCG64(seed); applied to R, C, L and the MOS
+        Vth/K/lambda/Cj0; sources stay nominal (SURVEY.md §8(d) recipe).  `first` selects a shard
+        [first, first+B) of one global batch, so ranks draw disjoint, reproducible slices."""
+        P = self.n_params
+        mask = np.zeros(P, bool)
+        for e in range(self.n_elems):
+            ty = int(self.elem_type[e])
+            if ty in (capi.ELEM_R, capi.ELEM_C, capi.ELEM_L, capi.ELEM_MOS):
+                mask[self.elem_param[e]: self.elem_param[e] + capi.PARAM_COUNT[ty]] = True
+        rng = np.random.Generator(np.random.PCG64(seed))
+        if first:
+            rng.bit_generator.advance(first * P)
+        u = rng.uniform(-1.0, 1.0, size=(B, P))
+        out = np.repeat(self.params[None, :], B, 0)
+        lo = 1 if first == 0 else 0
+        out[lo:, mask] = self.params[mask] * (1.0 + rel * u[lo:, mask])
+        return np.ascontiguousarray(out.T)
+
+    def run_reference_style_csv(self, path: str):
+        """runTransientAnalysisBackwardEuler(ckt, sim, path) of the C++ host layer (B = 1 on the GPU)."""
+        L = _hlib()
+        if L.csimh_run_tran_csv(C.c_void_p(self._h), path.encode()) != 0:
+            raise capi.CsimError(L.csimh_last_error().decode(errors="replace"))
+
+
+def sin_table(freq, td, phi, dt, n_steps) -> np.ndarray:
+    out = np.zeros(n_steps, np.float64)
+    _hlib().csimh_sin_table(float(freq), float(td), float(phi), float(dt), int(n_steps), out.ctypes.data_as(C.c_void_p))
+    return out

@@ -1,0 +1,26 @@
+// solver.hpp — namespace Solver of the reference (include/solver.hpp), device-backed.
+// luDecompose / solveLinearSystemLU keep their signatures and error behaviour (false / zero
+// vector + message on std::cerr, no exceptions for singular systems) but run the batched
+// CUDA LU (csim_dev_lu_solve) with B = 1; n <= 32.  They throw std::runtime_error only when
+// there is no CUDA device (there is no CPU solver in this library).
+// solveLinearSystemGaussSeidel is on the reference's interface but off its default path
+// (src/dcanalysis.cpp:260-262) and is not implemented on the device yet: it throws.
+#pragma once
+#include <vector>
+
+#include "dense.hpp"
+
+namespace Solver {
+using Eigen::MatrixXd;
+using Eigen::VectorXd;
+
+enum class LinearSolver { DirectLU, GaussSeidel };
+
+// Row permutation only (perm[i] = original row at position i); LU receives A with its rows
+// permuted (the packed L\U factors stay on the device and are not exported).
+bool luDecompose(const MatrixXd& A, MatrixXd& LU, std::vector<int>& perm);
+VectorXd solveLinearSystemLU(const MatrixXd& A, const VectorXd& b);
+VectorXd solveLinearSystemGaussSeidel(const MatrixXd& A, const VectorXd& b, const VectorXd& x0, int maxIters = 1000,
+                                      double tol = 1e-10);
+VectorXd solveLinearSystemGaussSeidel(const MatrixXd& A, const VectorXd& b, int maxIters = 1000, double tol = 1e-10);
+}  // namespace Solver

@@ -215,6 +215,13 @@ int csim_batch_dc(csim_batch* batch, double* x, int32_t* iters, uint64_t* pivot_
  * host; x_dc [N][B] and x_final [N][B] may be NULL.                             */
 int csim_batch_tran(csim_batch* batch, const csim_tran_args* args, double* x_dc, double* x_final, double* wave,
                     int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status);
+/* Host-pointer forms of the two standalone kernels (copies inside; for the C++ drop-in
+ * classes Element::stamp and Solver::solveLinearSystemLU and for small tests).            */
+int csim_host_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double* params, const double* x,
+                        const double* x_prev, const double* src_val, double dt, double source_scale,
+                        double gmin, double* vals, double* rhs);
+int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                       int32_t* singular, double lu_eps);
 /* Milliseconds of the kernels of the last csim_batch_* call, measured with CUDA
  * events on the batch's stream (copies excluded).                               */
 float csim_batch_last_kernel_ms(const csim_batch* batch);

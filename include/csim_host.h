@@ -1,0 +1,35 @@
+/* csim_host.h — C window onto the C++ host layer (include/csim/*.hpp) for bindings that cannot
+ * include C++ (Python ctypes): the product's own netlist parser (reference grammar,
+ * src/parser.cpp), lowering to csim_topology and host-libm source tabulation.
+ * No numerics of the Newton path live here.                                                    */
+#ifndef CSIM_HOST_H
+#define CSIM_HOST_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+typedef struct csimh_netlist csimh_netlist;
+
+const char* csimh_last_error(void);
+/* parseStream + ensureDefaultOp + assignEquationIndices + lower (src/main.cpp:29-34). NULL on error. */
+csimh_netlist* csimh_parse(const char* netlist_text);
+void csimh_free(csimh_netlist* h);
+int csimh_dims(const csimh_netlist* h, int32_t* n_unknowns, int32_t* n_node_eq, int32_t* n_elems,
+               int32_t* n_params, int32_t* n_sources);
+/* arrays sized per csimh_dims; nodes is [n_elems][4]; nominal is [n_params] */
+int csimh_topology(const csimh_netlist* h, int32_t* type, int32_t* flags, int32_t* nodes, int32_t* branch,
+                   int32_t* param_off, double* nominal);
+int csimh_node_name(const csimh_netlist* h, int32_t eq, char* out, int32_t cap);
+int csimh_elem_name(const csimh_netlist* h, int32_t idx, char* out, int32_t cap);
+int csimh_csv_header(const csimh_netlist* h, char* out, int32_t cap);
+int csimh_tran_cfg(const csimh_netlist* h, double* tstep, double* tstop, double* tstart, int32_t* enabled);
+int csimh_hb_cfg(const csimh_netlist* h, double* f0, int32_t* n_harm, int32_t* enabled);
+int csimh_plot_probes(const csimh_netlist* h, int32_t* out, int32_t cap);
+int csimh_tabulate_sources(const csimh_netlist* h, double dt, int32_t n_steps, int32_t* mode, int32_t* group,
+                           double* table, int32_t* n_groups);
+int csimh_sin_table(double freq, double td, double phi, double dt, int32_t n_steps, double* out);
+int csimh_run_tran_csv(const csimh_netlist* h, const char* path);
+#ifdef __cplusplus
+}
+#endif
+#endif
