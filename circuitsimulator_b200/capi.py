@@ -31,6 +31,8 @@ EXPORTS = [
     "csim_batch_create", "csim_batch_destroy", "csim_batch_set_params", "csim_batch_dc",
     "csim_batch_tran", "csim_batch_last_kernel_ms", "csim_pivot_hash_update",
     "csim_host_stamp_csr", "csim_host_lu_solve",
+    "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
+    "csim_plan_generate_source", "csim_dev_selftest_div",
 ]
 
 
@@ -95,6 +97,13 @@ def lib():
         L.csim_dev_lu_solve.argtypes = [C.c_int32, C.c_int64] + [C.c_void_p] * 5 + [C.c_double, C.c_void_p]
         L.csim_dev_dc.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6
         L.csim_dev_tran.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(TranArgsC)] + [C.c_void_p] * 7
+        L.csim_plan_jit_mode.argtypes = [C.c_void_p, C.c_int]
+        L.csim_plan_specialize.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+        L.csim_plan_spec_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_uint64),
+                                          C.POINTER(C.c_uint64), C.c_char_p, C.c_int32]
+        L.csim_plan_spec_source.argtypes = [C.c_void_p, C.c_char_p, C.c_int32]
+        L.csim_plan_generate_source.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_char_p, C.c_int32]
+        L.csim_dev_selftest_div.argtypes = [C.c_int64] + [C.c_void_p] * 5
         L.csim_batch_create.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
         L.csim_batch_destroy.argtypes = [C.c_void_p]
         L.csim_batch_set_params.argtypes = [C.c_void_p, C.c_void_p]
@@ -158,6 +167,39 @@ class Plan:
             self.close()
         except Exception:
             pass
+
+    def jit_mode(self, mode: int):
+        """0: generic kernels only; 1: specialise the transient kernel automatically (default)."""
+        _check(lib().csim_plan_jit_mode(self.handle, int(mode)), "csim_plan_jit_mode")
+
+    def specialize(self, perm):
+        perm = _i32(perm)
+        assert perm.size == self.n_unknowns
+        _check(lib().csim_plan_specialize(self.handle, _ip(perm)), "csim_plan_specialize")
+
+    def spec_info(self):
+        act, fb, sv = C.c_int32(), C.c_uint64(), C.c_uint64()
+        perm = np.zeros(self.n_unknowns, np.int32)
+        log = C.create_string_buffer(1 << 14)
+        _check(lib().csim_plan_spec_info(self.handle, C.byref(act), _ip(perm), C.byref(fb), C.byref(sv), log, len(log)),
+               "csim_plan_spec_info")
+        return dict(active=bool(act.value), perm=perm, fallback_solves=int(fb.value), solves=int(sv.value),
+                    log=log.value.decode(errors="replace"))
+
+    def spec_source(self) -> str:
+        n = lib().csim_plan_spec_source(self.handle, None, 0)
+        buf = C.create_string_buffer(n + 1)
+        lib().csim_plan_spec_source(self.handle, buf, n + 1)
+        return buf.value.decode()
+
+    def generate_source(self, perm) -> str:
+        perm = _i32(perm)
+        n = lib().csim_plan_generate_source(self.handle, _ip(perm), None, 0)
+        if n < 0:
+            _check(n, "csim_plan_generate_source")
+        buf = C.create_string_buffer(n + 1)
+        lib().csim_plan_generate_source(self.handle, _ip(perm), buf, n + 1)
+        return buf.value.decode()
 
     def pattern(self, mode: int):
         nnz = C.c_int32()
@@ -360,3 +402,14 @@ class Batch:
     @property
     def last_kernel_ms(self) -> float:
         return float(lib().csim_batch_last_kernel_ms(self.handle))
+
+
+def selftest_div(a, b):
+    """(q_split, q_ref) on the device for float64 CUDA tensors a, b (see csim_dev_selftest_div)."""
+    torch = _torch()
+    _dev_f64(a)
+    _dev_f64(b, a.shape)
+    qs, qr = torch.empty_like(a), torch.empty_like(a)
+    _check(lib().csim_dev_selftest_div(a.numel(), _ptr(a), _ptr(b), _ptr(qs), _ptr(qr), _stream()),
+           "csim_dev_selftest_div")
+    return qs, qr

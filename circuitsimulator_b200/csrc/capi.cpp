@@ -10,8 +10,13 @@
 #include <vector>
 
 #include "../../include/csim_b200.h"
+#include <cstdlib>
+#include <mutex>
+
+#include "jit.hpp"
 #include "kernels.hpp"
 #include "plan.hpp"
+#include "specialize.hpp"
 
 using namespace csim;
 
@@ -44,12 +49,28 @@ cudaError_t upload(const std::vector<T>& v, const T** out, std::vector<void*>& o
 }
 }  // namespace
 
+// Specialised (run-time generated) transient kernel of a plan; see specialize.hpp.
+struct SpecState {
+    std::mutex mu;
+    int mode = 1;        // 0 = generic kernels only, 1 = specialise automatically on first use
+    bool tried = false;  // a specialisation attempt has been made
+    bool ready = false;  // kernel loaded and usable
+    SpecHost host;
+    JitKernel k;
+    SpecTables dev{};
+    size_t smem = 0;
+    std::vector<void*> owned;
+    unsigned long long* d_stats = nullptr;  // [2]: fallback solves, Newton solves
+    std::string log;
+};
+
 struct csim_plan {
     HostPlan host;
     DevPlan dev{};
     int device = -1;
     int sm_count = 0;
     std::vector<void*> owned;
+    mutable SpecState spec;
 };
 
 struct csim_batch {
@@ -76,6 +97,130 @@ struct DevBuf {  // RAII scratch for the host-pointer convenience calls
     }
     template <typename T> T* as() { return static_cast<T*>(p); }
 };
+}  // namespace
+
+namespace {
+
+// Generates, compiles (NVRTC, sm_100a) and loads the transient kernel specialised to `perm`.
+int spec_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
+    SpecState& sp = plan->spec;
+    sp.ready = false;
+    for (void* d : sp.owned) cudaFree(d);
+    sp.owned.clear();
+    jit_unload(sp.k);
+    const std::string why = spec_unsupported_reason(plan->host);
+    if (!why.empty()) {
+        sp.log = "not specialised: " + why;
+        return fail(CSIM_E_UNSUPPORTED, sp.log);
+    }
+    try {
+        sp.host = generate_tran_spec(plan->host, perm);
+    } catch (const std::exception& e) {
+        sp.log = e.what();
+        return fail(CSIM_E_INVALID, sp.log);
+    }
+    std::vector<char> cubin;
+    std::string log;
+    if (!jit_compile(sp.host.source, "csim_tran_spec.cu", jit_library_dir() + "/csrc", cubin, log)) {
+        sp.log = "NVRTC: " + log;
+        return fail(CSIM_E_CUDA, sp.log);
+    }
+    CU(jit_load(cubin, "csim_tran_spec", sp.k));
+    sp.smem = spec_smem_bytes(plan->host, sp.host);
+    CU(cudaKernelSetAttributeForDevice(sp.k.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp.smem,
+                                       plan->device));
+    SpecTables& t = sp.dev;
+    CU(upload(sp.host.gidx, &t.gidx, sp.owned));
+    CU(upload(sp.host.prefix, &t.prefix, sp.owned));
+    CU(upload(sp.host.mos_lane, &t.mos_lane, sp.owned));
+    t.n_adds = sp.host.n_adds;
+    t.prefix_len = sp.host.prefix_len;
+    t.n_mos = sp.host.n_mos;
+    t.n_values = plan->host.mode[CSIM_MODE_TRAN].n_values;
+    t.hash_lo = sp.host.hash_lo;
+    t.hash_hi = sp.host.hash_hi;
+    void* st = nullptr;
+    CU(cudaMalloc(&st, 2 * sizeof(unsigned long long)));
+    sp.owned.push_back(st);
+    sp.d_stats = static_cast<unsigned long long*>(st);
+    CU(cudaMemset(st, 0, 2 * sizeof(unsigned long long)));
+    sp.log = "specialised: " + std::to_string(sp.host.n_lu_steps) + " elimination steps, " +
+             std::to_string(sp.host.n_elim_updates) + " row updates, " + std::to_string(sp.host.n_back_terms) +
+             " back-substitution terms, " + std::to_string(sp.host.n_g_adds) + "+" +
+             std::to_string(sp.host.n_rhs_adds) + " assembly adds per Newton iteration; " +
+             std::to_string(sp.smem) + " B shared memory per CTA" + (log.size() > 1 ? "\n" + log : "");
+    sp.ready = true;
+    return CSIM_OK;
+}
+
+// Pivot order the reference's LU picks for instance 0 of the batch at its current state: one TRAN
+// assembly (device stamp kernel) + one generic LU (device).  Only the ORDER is used, as a prediction.
+int spec_pilot(const csim_plan* plan, int64_t B, const double* d_params, const double* d_x, double dt,
+               cudaStream_t stream, std::vector<int32_t>& perm) {
+    const int N = plan->host.N, P = plan->host.n_params, S = plan->host.n_sources;
+    const ModeProgram& mp = plan->host.mode[CSIM_MODE_TRAN];
+    std::vector<double> p(P > 0 ? P : 1), x(N), sv(S > 0 ? S : 1, 0.0);
+    CU(cudaStreamSynchronize(stream));
+    if (P > 0) CU(cudaMemcpy2D(p.data(), sizeof(double), d_params, sizeof(double) * B, sizeof(double), P, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy2D(x.data(), sizeof(double), d_x, sizeof(double) * B, sizeof(double), N, cudaMemcpyDeviceToHost));
+    std::vector<double> vals(mp.colidx.size()), rhs(N);
+    int rc = csim_host_stamp_csr(plan, CSIM_MODE_TRAN, 1, p.data(), x.data(), x.data(), sv.data(), dt, 1.0,
+                                 plan->host.consts.tran_gmin, vals.data(), rhs.data());
+    if (rc) return rc;
+    std::vector<double> A((size_t)N * N, 0.0), sol(N);
+    for (int i = 0; i < N; ++i)
+        for (int k = mp.rowptr[i]; k < mp.rowptr[i + 1]; ++k) A[(size_t)i * N + mp.colidx[k]] = vals[k];
+    perm.assign(N, 0);
+    int32_t singular = 0;
+    rc = csim_host_lu_solve(N, 1, A.data(), rhs.data(), sol.data(), perm.data(), &singular, plan->host.consts.lu_eps);
+    if (rc) return rc;
+    if (singular) return fail(CSIM_E_UNSUPPORTED, "pilot factorisation is singular");
+    return CSIM_OK;
+}
+
+// true -> the specialised kernel is loaded and should be used for this launch
+bool spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const double* d_x, double dt,
+                  cudaStream_t stream) {
+    SpecState& sp = plan->spec;
+    std::lock_guard<std::mutex> lock(sp.mu);
+    if (sp.mode == 0) return false;
+    if (sp.ready) return true;
+    if (sp.tried) return false;
+    sp.tried = true;
+    const char* env = std::getenv("CSIM_JIT");
+    if (env && env[0] == '0') {
+        sp.mode = 0;
+        sp.log = "disabled by CSIM_JIT=0";
+        return false;
+    }
+    if (!spec_unsupported_reason(plan->host).empty()) {
+        sp.log = "not specialised: " + spec_unsupported_reason(plan->host);
+        return false;
+    }
+    std::vector<int32_t> perm;
+    if (spec_pilot(plan, B, d_params, d_x, dt, stream, perm) != CSIM_OK) {
+        sp.log = std::string("pilot failed: ") + csim_last_error();
+        return false;
+    }
+    return spec_build(plan, perm) == CSIM_OK;
+}
+
+cudaError_t spec_launch(const csim_plan* plan, const DevTran& T, int64_t B, const double* params, double* x,
+                        double* wave, int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash,
+                        uint32_t* status, cudaStream_t stream) {
+    SpecState& sp = plan->spec;
+    DevPlan P = plan->dev;
+    DevTran Tc = T;
+    SpecTables ST = sp.dev;
+    long long Bll = B;
+    unsigned long long* stats = sp.d_stats;
+    void* args[] = {&P, &Tc, &ST, &Bll, &params, &x, &wave, &iters_total, &iters_step, &pivot_hash, &status, &stats};
+    const int wpb = sp.host.warps_per_block;
+    const unsigned blocks = (unsigned)((B + wpb - 1) / wpb);
+    return cudaLaunchKernel(reinterpret_cast<const void*>(sp.k.kernel), dim3(blocks), dim3(wpb * 32), args, sp.smem,
+                            stream);
+}
+
 }  // namespace
 
 extern "C" {
@@ -177,6 +322,8 @@ void csim_plan_destroy(csim_plan* plan) {
     if (plan->device >= 0) {
         cudaSetDevice(plan->device);
         for (void* d : plan->owned) cudaFree(d);
+        for (void* d : plan->spec.owned) cudaFree(d);
+        jit_unload(plan->spec.k);
     }
     delete plan;
 }
@@ -303,7 +450,12 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
     T.src_group = d_pack + ns;
     T.src_group_b = a->src_group_b;
     T.probes = d_pack + 2 * ns;
-    cudaError_t e = launch_tran(plan->dev, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
+    cudaError_t e;
+    if (spec_prepare(plan, B, params, x, a->dt, stream)) {
+        e = spec_launch(plan, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
+    } else {
+        e = launch_tran(plan->dev, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
+    }
     cudaFreeAsync(d_pack, stream);
     if (e != cudaSuccess) return cuda_fail(e, "tran_kernel launch");
     return CSIM_OK;
@@ -512,6 +664,69 @@ int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, d
     CU(cudaMemcpy(x, dx.p, sizeof(double) * (size_t)n * B, cudaMemcpyDeviceToHost));
     if (perm) CU(cudaMemcpy(perm, dp.p, sizeof(int32_t) * (size_t)n * B, cudaMemcpyDeviceToHost));
     if (singular) CU(cudaMemcpy(singular, ds.p, sizeof(int32_t) * (size_t)B, cudaMemcpyDeviceToHost));
+    return CSIM_OK;
+}
+
+int csim_plan_jit_mode(csim_plan* plan, int mode) {
+    if (!plan || mode < 0 || mode > 1) return fail(CSIM_E_INVALID, "csim_plan_jit_mode: bad argument");
+    std::lock_guard<std::mutex> lock(plan->spec.mu);
+    plan->spec.mode = mode;
+    return CSIM_OK;
+}
+
+int csim_plan_specialize(csim_plan* plan, const int32_t* perm) {
+    int rc = need_device(plan, "csim_plan_specialize");
+    if (rc) return rc;
+    if (!perm) return fail(CSIM_E_INVALID, "csim_plan_specialize: null permutation");
+    std::lock_guard<std::mutex> lock(plan->spec.mu);
+    plan->spec.tried = true;
+    plan->spec.mode = 1;
+    return spec_build(plan, std::vector<int32_t>(perm, perm + plan->host.N));
+}
+
+int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, uint64_t* fallback_solves,
+                        uint64_t* solves, char* log, int32_t log_cap) {
+    if (!plan) return fail(CSIM_E_INVALID, "csim_plan_spec_info: null plan");
+    SpecState& sp = plan->spec;
+    std::lock_guard<std::mutex> lock(sp.mu);
+    if (active) *active = sp.ready && sp.mode != 0 ? 1 : 0;
+    if (perm && sp.ready)
+        for (int i = 0; i < plan->host.N; ++i) perm[i] = sp.host.perm[i];
+    unsigned long long st[2] = {0, 0};
+    if (sp.ready && sp.d_stats) {
+        cudaSetDevice(plan->device);
+        cudaDeviceSynchronize();
+        cudaMemcpy(st, sp.d_stats, sizeof(st), cudaMemcpyDeviceToHost);
+    }
+    if (fallback_solves) *fallback_solves = st[0];
+    if (solves) *solves = st[1];
+    if (log && log_cap > 0) std::snprintf(log, (size_t)log_cap, "%s", sp.log.c_str());
+    return CSIM_OK;
+}
+
+int csim_plan_spec_source(const csim_plan* plan, char* out, int32_t cap) {
+    if (!plan) return fail(CSIM_E_INVALID, "csim_plan_spec_source: null plan");
+    std::lock_guard<std::mutex> lock(plan->spec.mu);
+    const std::string& src = plan->spec.host.source;
+    if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", src.c_str());
+    return (int)src.size();
+}
+
+// Host-only: the CUDA source the generator emits for `perm` (no device, no compilation).
+int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* out, int32_t cap) {
+    if (!plan || !perm) return fail(CSIM_E_INVALID, "csim_plan_generate_source: null argument");
+    try {
+        SpecHost sh = generate_tran_spec(plan->host, std::vector<int32_t>(perm, perm + plan->host.N));
+        if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", sh.source.c_str());
+        return (int)sh.source.size();
+    } catch (const std::exception& e) {
+        return fail(CSIM_E_UNSUPPORTED, e.what());
+    }
+}
+
+int csim_dev_selftest_div(int64_t n, const double* a, const double* b, double* q_split, double* q_ref, void* stream) {
+    if (n <= 0 || !a || !b || !q_split || !q_ref) return fail(CSIM_E_INVALID, "csim_dev_selftest_div: bad argument");
+    CU(launch_div_selftest(n, a, b, q_split, q_ref, (cudaStream_t)stream));
     return CSIM_OK;
 }
 

@@ -1,8 +1,9 @@
 // device_plan.cuh — device-side view of a csim_plan (POD, passed to kernels by value).
 #pragma once
-#include <cstdint>
+#include <stdint.h>
 
-#include "plan.hpp"
+#include "../../include/csim_b200.h"
+#include "plan_pod.h"
 
 namespace csim {
 
@@ -35,6 +36,15 @@ struct DevTran {
     const int32_t* src_group;    // [n_sources]
     const int32_t* src_group_b;  // [n_sources][B] or nullptr
     const int32_t* probes;       // [n_probes]
+};
+
+// Device-side tables of a specialised kernel (built by specialize.cpp).
+struct SpecTables {
+    const uint16_t* gidx;      // [n_adds][32]  index into vv (value/negated-value pairs) per lane
+    const uint32_t* prefix;    // [prefix_len][32] contribution words (col | sub<<6 | value<<8), 0xFFFFFFFF = none
+    const int32_t* mos_lane;   // [32][8]: param offset, d, g, s, is_p, out, -, -   (lane m = m-th MOSFET)
+    int32_t n_adds, prefix_len, n_mos, n_values;
+    uint32_t hash_lo, hash_hi; // sum_i mix(i, perm[i]) of the predicted permutation
 };
 
 }  // namespace csim

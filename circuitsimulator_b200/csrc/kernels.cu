@@ -5,11 +5,13 @@
 //   dc_kernel        : DC operating point (source ramp + damped Newton), warp-per-instance
 //   tran_kernel      : backward-Euler step loop + damped Newton, warp-per-instance
 #include <cuda_runtime.h>
+#include <math_constants.h>
 
 #include <cstdint>
 
 #include "kernels.hpp"
 #include "newton_warp.cuh"
+#include "spec_runtime.cuh"
 
 namespace csim {
 
@@ -40,7 +42,7 @@ stamp_csr_kernel(DevPlan P, int64_t B, const double* __restrict__ params, const 
                 case SK_RES: v = (p == 0.0) ? 0.0 : 1.0 / p; break;
                 case SK_CAP: v = (p <= 0.0 || dt <= 0.0) ? 0.0 : p / dt; break;
                 case SK_CAPHALF: {
-                    double c = dmul(0.5, p);
+                    double c = d_mul(0.5, p);
                     v = (c <= 0.0 || dt <= 0.0) ? 0.0 : c / dt;
                 } break;
                 case SK_IND_ONE: v = (p <= 0.0) ? 0.0 : 1.0; break;
@@ -56,9 +58,9 @@ stamp_csr_kernel(DevPlan P, int64_t B, const double* __restrict__ params, const 
                 double v;
                 if (op.kind == TK_CAP_HIST) {
                     double vb = op.b >= 0 ? __ldg(x_prev + (int64_t)op.b * B + b) : 0.0;
-                    v = dmul(-vt[op.g * TS], dsub(va, vb));
+                    v = d_mul(-vt[op.g * TS], d_sub(va, vb));
                 } else {
-                    v = dmul(vt[op.g * TS], va);
+                    v = d_mul(vt[op.g * TS], va);
                 }
                 vt[op.out * TS] = v;
             }
@@ -70,8 +72,8 @@ stamp_csr_kernel(DevPlan P, int64_t B, const double* __restrict__ params, const 
                 v = __ldg(src_val + (int64_t)op.index * B + b);
             } else {
                 double base = __ldg(params + (int64_t)op.param * B + b);
-                if (op.is_sin) base = dadd(base, __ldg(params + (int64_t)(op.param + 1) * B + b));
-                v = dmul(base, scale);
+                if (op.is_sin) base = d_add(base, __ldg(params + (int64_t)(op.param + 1) * B + b));
+                v = d_mul(base, scale);
             }
             vt[op.out * TS] = v;
         }
@@ -98,7 +100,7 @@ stamp_csr_kernel(DevPlan P, int64_t B, const double* __restrict__ params, const 
             for (; e < e1; ++e) {
                 uint32_t w = m.slot_entries[e];
                 double v = vt[(w >> 8) * TS];
-                acc = (w & 64u) ? dsub(acc, v) : dadd(acc, v);
+                acc = (w & 64u) ? d_sub(acc, v) : d_add(acc, v);
             }
             if (s < m.nnz) vals[(int64_t)s * B + b] = acc;
             else rhs[(int64_t)(s - m.nnz) * B + b] = acc;
@@ -151,7 +153,7 @@ __device__ __forceinline__ const uint32_t* load_prog(const DevMode& m, uint32_t*
 __device__ __forceinline__ double base_gmin(const csim_constants& c, double s) {
     if (s < 0.0) s = 0.0;
     if (s > 1.0) s = 1.0;
-    return dadd(dmul(c.gmin_high_base, dsub(1.0, s)), dmul(c.gmin_low_base, s));
+    return d_add(d_mul(c.gmin_high_base, d_sub(1.0, s)), d_mul(c.gmin_low_base, s));
 }
 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
@@ -209,23 +211,23 @@ dc_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double* __res
                 const double xr = lane < N ? w.bs[lane] : 0.0;
                 if (__any_sync(kFull, !lane_finite(xr))) {  // dcanalysis.cpp:135-138
                     st |= CSIM_ST_NONFINITE;
-                    double g10 = dmul(gmin, c.dc_nonfinite_mul);
+                    double g10 = d_mul(gmin, c.dc_nonfinite_mul);
                     gmin = g10 < c.dc_nonfinite_cap ? g10 : c.dc_nonfinite_cap;
                     continue;
                 }
                 // ConvController::update (src/dcanalysis.cpp:268-307)
-                const double xn = dadd(x, dmul(c.dc_alpha, dsub(xr, x)));
-                const double err = warp_norm2(dsub(xn, x));
+                const double xn = d_add(x, d_mul(c.dc_alpha, d_sub(xr, x)));
+                const double err = warp_norm2(d_sub(xn, x));
                 const double gbase = base_gmin(c, scale);
                 double gnext = gbase;
                 if (!(iter == 0 || !lane_finite(prevErr))) {
-                    if (err > dmul(prevErr, c.slow_conv_ratio)) {
-                        double g2 = dmul(gmin, 2.0);
+                    if (err > d_mul(prevErr, c.slow_conv_ratio)) {
+                        double g2 = d_mul(gmin, 2.0);
                         gnext = g2 < c.gmin_abs_max ? g2 : c.gmin_abs_max;
-                    } else if (err < dmul(prevErr, c.fast_conv_ratio)) {
-                        gnext = dadd(dmul(0.5, gmin), dmul(0.5, gbase));
+                    } else if (err < d_mul(prevErr, c.fast_conv_ratio)) {
+                        gnext = d_add(d_mul(0.5, gmin), d_mul(0.5, gbase));
                     } else {
-                        gnext = dadd(dmul(0.7, gmin), dmul(0.3, gbase));
+                        gnext = d_add(d_mul(0.7, gmin), d_mul(0.3, gbase));
                     }
                 }
                 x = xn;
@@ -295,8 +297,8 @@ tran_kernel(DevPlan P, DevTran T, int64_t B, const double* __restrict__ params, 
                 dead = true;
                 break;
             }
-            const double xn = dadd(x, dmul(c.tran_alpha, dsub(xr, x)));  // tanalisis.cpp:365
-            const double err = warp_norm2(dsub(xn, x));                   // tanalisis.cpp:366
+            const double xn = d_add(x, d_mul(c.tran_alpha, d_sub(xr, x)));  // tanalisis.cpp:365
+            const double err = warp_norm2(d_sub(xn, x));                   // tanalisis.cpp:366
             x = xn;
             __syncwarp();
             w.xs[lane] = x;
@@ -318,6 +320,24 @@ tran_kernel(DevPlan P, DevTran T, int64_t B, const double* __restrict__ params, 
         if (pivot_hash) pivot_hash[b] = h;
         if (status) status[b] |= st;
     }
+}
+
+// =============================================================================
+// self-test of the split IEEE division used by the specialised kernels
+// =============================================================================
+__global__ void div_selftest_kernel(int64_t n, const double* __restrict__ a, const double* __restrict__ b,
+                                    double* __restrict__ q_split, double* __restrict__ q_ref) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double y = rcp_seq(b[i]);
+        q_split[i] = fdiv(a[i], b[i], y, true);
+        q_ref[i] = a[i] / b[i];
+    }
+}
+
+cudaError_t launch_div_selftest(int64_t n, const double* a, const double* b, double* q_split, double* q_ref,
+                                cudaStream_t stream) {
+    div_selftest_kernel<<<1184, 256, 0, stream>>>(n, a, b, q_split, q_ref);
+    return cudaGetLastError();
 }
 
 // =============================================================================

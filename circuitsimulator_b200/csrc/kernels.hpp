@@ -22,4 +22,7 @@ cudaError_t launch_tran(const DevPlan& P, const DevTran& T, int64_t B, const dou
                         int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status,
                         cudaStream_t stream);
 
+cudaError_t launch_div_selftest(int64_t n, const double* a, const double* b, double* q_split, double* q_ref,
+                                cudaStream_t stream);
+
 }  // namespace csim

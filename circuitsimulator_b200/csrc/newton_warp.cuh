@@ -10,8 +10,9 @@
 // skips exact zeros of the pivot row, which is bit-identical to the dense loops
 // for finite data (F3).
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <cuda_runtime.h>
-#include <math_constants.h>
+#endif
 
 #include "device_plan.cuh"
 
@@ -20,9 +21,9 @@ namespace csim {
 constexpr int kLD = 33;  // row stride of the per-warp matrix, in doubles
 constexpr unsigned kFull = 0xFFFFFFFFu;
 
-__device__ __forceinline__ double dadd(double a, double b) { return __dadd_rn(a, b); }
-__device__ __forceinline__ double dsub(double a, double b) { return __dsub_rn(a, b); }
-__device__ __forceinline__ double dmul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double d_add(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double d_sub(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double d_mul(double a, double b) { return __dmul_rn(a, b); }
 
 struct WarpMem {
     double* S;   // [32*kLD] matrix
@@ -58,7 +59,7 @@ __device__ __forceinline__ void eval_static(const DevMode& m, const double* __re
             case SK_RES: v = (p == 0.0) ? 0.0 : 1.0 / p; break;                           // element.cpp:20-24
             case SK_CAP: v = (p <= 0.0 || dt <= 0.0) ? 0.0 : p / dt; break;               // tanalisis.cpp:65-67
             case SK_CAPHALF: {
-                double c = dmul(0.5, p);                                                  // tanalisis.cpp:338
+                double c = d_mul(0.5, p);                                                  // tanalisis.cpp:338
                 v = (c <= 0.0 || dt <= 0.0) ? 0.0 : c / dt;
             } break;
             case SK_IND_ONE: v = (p <= 0.0) ? 0.0 : 1.0; break;                           // tanalisis.cpp:296
@@ -76,9 +77,9 @@ __device__ __forceinline__ void eval_step(const DevMode& m, const double* xp, do
         double v;
         if (op.kind == TK_CAP_HIST) {
             double vb = op.b >= 0 ? xp[op.b] : 0.0;
-            v = dmul(-vt[op.g], dsub(va, vb));  // I_hist = -Gc * vPrev
+            v = d_mul(-vt[op.g], d_sub(va, vb));  // I_hist = -Gc * vPrev
         } else {
-            v = dmul(vt[op.g], va);             // V_hist = -R_eq * iPrev  (vt[g] = -R_eq)
+            v = d_mul(vt[op.g], va);             // V_hist = -R_eq * iPrev  (vt[g] = -R_eq)
         }
         vt[op.out] = v;
     }
@@ -90,15 +91,15 @@ __device__ __forceinline__ void eval_src_dc(const DevMode& m, const double* __re
     for (int i = lane; i < m.n_src; i += 32) {
         SrcOp op = m.src_ops[i];
         double base = params[(int64_t)op.param * B + b];
-        if (op.is_sin) base = dadd(base, params[(int64_t)(op.param + 1) * B + b]);
-        vt[op.out] = dmul(base, scale);
+        if (op.is_sin) base = d_add(base, params[(int64_t)(op.param + 1) * B + b]);
+        vt[op.out] = d_mul(base, scale);
     }
 }
 
 // SourceSpec::evalTran (include/sim.hpp:160-162) through the host-tabulated waveform
 __device__ __forceinline__ void eval_src_tran(const DevMode& m, const DevTran& T, const double* __restrict__ params,
                                               int64_t B, int64_t b, int step, double* vt, int lane) {
-    const double tnow = dmul((double)(step + 1), T.dt);  // tanalisis.cpp:256
+    const double tnow = d_mul((double)(step + 1), T.dt);  // tanalisis.cpp:256
     for (int i = lane; i < m.n_src; i += 32) {
         SrcOp op = m.src_ops[i];
         const int s = op.index;
@@ -111,12 +112,12 @@ __device__ __forceinline__ void eval_src_tran(const DevMode& m, const DevTran& T
                 double v0 = params[(int64_t)(op.param + 1) * B + b];
                 double td = params[(int64_t)(op.param + 4) * B + b];
                 if (tnow < td) w = v0;
-                else w = dadd(v0, dmul(params[(int64_t)(op.param + 2) * B + b], tab));
+                else w = d_add(v0, d_mul(params[(int64_t)(op.param + 2) * B + b], tab));
             } else {
                 w = tab;
             }
         }
-        vt[op.out] = dadd(params[(int64_t)op.param * B + b], w);
+        vt[op.out] = d_add(params[(int64_t)op.param * B + b], w);
     }
 }
 
@@ -124,35 +125,35 @@ __device__ __forceinline__ void eval_src_tran(const DevMode& m, const DevTran& T
 __device__ __forceinline__ void mos_eval(double Vth, double K, double lambda, bool is_p, double off_gds, double Vd,
                                          double Vg, double Vs, double& gd, double& gg, double& gs, double& cst) {
     const double pp = is_p ? -1.0 : 1.0;
-    const double Vgs = dmul(pp, dsub(Vg, Vs));
-    const double Vds = dmul(pp, dsub(Vd, Vs));
+    const double Vgs = d_mul(pp, d_sub(Vg, Vs));
+    const double Vds = d_mul(pp, d_sub(Vd, Vs));
     double Ids0, gds0, gm0;
     if (Vgs > Vth && Vds >= 0.0) {
-        const double Vov = dsub(Vgs, Vth);
+        const double Vov = d_sub(Vgs, Vth);
         if (Vds < Vov) {  // triode
-            Ids0 = dmul(K, dsub(dmul(Vov, Vds), dmul(dmul(0.5, Vds), Vds)));
-            gds0 = dmul(K, dsub(Vov, Vds));
-            gm0 = dmul(K, Vds);
+            Ids0 = d_mul(K, d_sub(d_mul(Vov, Vds), d_mul(d_mul(0.5, Vds), Vds)));
+            gds0 = d_mul(K, d_sub(Vov, Vds));
+            gm0 = d_mul(K, Vds);
         } else {  // saturation
-            Ids0 = dmul(dmul(dmul(0.5, K), Vov), Vov);
+            Ids0 = d_mul(d_mul(d_mul(0.5, K), Vov), Vov);
             gds0 = 0.0;
-            gm0 = dmul(K, Vov);
+            gm0 = d_mul(K, Vov);
         }
     } else {
         Ids0 = 0.0;
         gm0 = 0.0;
         gds0 = off_gds;
     }
-    double factor = dadd(1.0, dmul(lambda, Vds));
+    double factor = d_add(1.0, d_mul(lambda, Vds));
     if (factor < 0.0) factor = 0.0;
-    const double Ids_eff = dmul(Ids0, factor);
-    const double dVds = dadd(dmul(gds0, factor), dmul(Ids0, lambda));
-    const double dVgs = dmul(gm0, factor);
-    const double Ids = dmul(pp, Ids_eff);
+    const double Ids_eff = d_mul(Ids0, factor);
+    const double dVds = d_add(d_mul(gds0, factor), d_mul(Ids0, lambda));
+    const double dVgs = d_mul(gm0, factor);
+    const double Ids = d_mul(pp, Ids_eff);
     gd = dVds;
     gg = dVgs;
-    gs = -dadd(dVds, dVgs);
-    cst = dsub(dsub(dsub(Ids, dmul(gd, Vd)), dmul(gg, Vg)), dmul(gs, Vs));
+    gs = -d_add(dVds, dVgs);
+    cst = d_sub(d_sub(d_sub(Ids, d_mul(gd, Vd)), d_mul(gg, Vg)), d_mul(gs, Vs));
 }
 
 __device__ __forceinline__ void eval_mos(const DevMode& m, const double* __restrict__ params, int64_t B, int64_t b,
@@ -186,8 +187,8 @@ __device__ __forceinline__ void assemble(const DevMode& m, const uint32_t* prog,
             double v = w.vt[word >> 8];
             if (word & 64u) v = -v;
             int col = word & 63u;
-            if (col == kRhsCol) rb = dadd(rb, v);
-            else row[col] = dadd(row[col], v);
+            if (col == kRhsCol) rb = d_add(rb, v);
+            else row[col] = d_add(row[col], v);
         }
     }
     w.bs[lane] = rb;
@@ -250,9 +251,9 @@ __device__ __forceinline__ bool lu_solve_warp(double* S, double* bs, int N, int 
             while (mm) {
                 int j = __ffs(mm) - 1;
                 mm &= mm - 1;
-                row[j] = dsub(row[j], dmul(f, S[k * kLD + j]));  // solver.hpp:74
+                row[j] = d_sub(row[j], d_mul(f, S[k * kLD + j]));  // solver.hpp:74
             }
-            bs[lane] = dsub(bs[lane], dmul(f, bk));  // forward substitution, fused (solver.hpp:106-113)
+            bs[lane] = d_sub(bs[lane], d_mul(f, bk));  // forward substitution, fused (solver.hpp:106-113)
         }
         __syncwarp();
     }
@@ -271,7 +272,7 @@ __device__ __forceinline__ bool lu_solve_warp(double* S, double* bs, int N, int 
         while (cm) {
             int j = __ffs(cm) - 1;
             cm &= cm - 1;
-            sum = dsub(sum, dmul(S[i * kLD + j], bs[j]));
+            sum = d_sub(sum, d_mul(S[i * kLD + j], bs[j]));
         }
         const double diag = S[i * kLD + i];
         const double xi = (fabs(diag) < 1e-15) ? 0.0 : sum / diag;
@@ -301,9 +302,9 @@ __device__ __forceinline__ uint64_t hash_update(uint64_t h, int perm, int N, int
 // sqrt of the 32-leaf pairwise tree sum of squares (norm definition: include/csim_b200.h,
 // oracle/csim_norm2.h); every lane returns the same value.
 __device__ __forceinline__ double warp_norm2(double d) {
-    double v = dmul(d, d);
+    double v = d_mul(d, d);
 #pragma unroll
-    for (int s = 16; s >= 1; s >>= 1) v = dadd(v, __shfl_xor_sync(kFull, v, s));
+    for (int s = 16; s >= 1; s >>= 1) v = d_add(v, __shfl_xor_sync(kFull, v, s));
     return sqrt(v);
 }
 

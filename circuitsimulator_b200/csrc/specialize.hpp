@@ -1,0 +1,44 @@
+// specialize.hpp — run-time code generation of the transient kernel for ONE netlist topology
+// and ONE predicted pivot permutation (host side).
+//
+// Why: ncu on the generic kernel (profiles/r1_v1_*) shows 9,557 warp-instructions per Newton
+// iteration of which ~13 % are FP64 — the rest is index arithmetic, loop control and pivot
+// bookkeeping that depend only on the topology.  Given the topology and the permutation the
+// reference's partial pivoting is expected to pick, every address, loop trip count and
+// structural zero is known, so the generator emits straight-line CUDA with the matrix rows in
+// registers and only the structurally non-zero operations.  The permutation is a PREDICTION:
+// the generated code verifies the reference's first-max-wins rule at every elimination step
+// and re-does the solve with the generic pivoting path when it does not hold, so results are
+// bit-identical to the generic kernel in every case.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "plan.hpp"
+
+namespace csim {
+
+struct SpecHost {
+    std::vector<int32_t> perm;       // predicted: perm[i] = original row at position i
+    std::string source;              // CUDA C++ translation unit (entry: csim_tran_spec)
+    std::vector<uint16_t> gidx;      // [n_adds][32]
+    std::vector<uint32_t> prefix;    // [prefix_len][32]
+    std::vector<int32_t> mos_lane;   // [32][8]
+    int32_t n_adds = 0, prefix_len = 0, n_mos = 0;
+    uint32_t hash_lo = 0, hash_hi = 0;
+    int32_t warps_per_block = 4, blocks_per_sm = 4;
+    // statistics of the generated code (per Newton iteration)
+    int32_t n_elim_updates = 0, n_lu_steps = 0, n_back_terms = 0, n_g_adds = 0, n_rhs_adds = 0;
+};
+
+// Why a topology cannot be specialised (empty string = it can).
+std::string spec_unsupported_reason(const HostPlan& hp);
+
+// perm must be a permutation of 0..N-1.  Throws std::runtime_error on inconsistent input.
+SpecHost generate_tran_spec(const HostPlan& hp, const std::vector<int32_t>& perm);
+
+// Per-block dynamic shared memory of the generated kernel.
+size_t spec_smem_bytes(const HostPlan& hp, const SpecHost& sh);
+
+}  // namespace csim

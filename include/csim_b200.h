@@ -22,6 +22,8 @@
  *     include the host<->device copies.
  *   - there is no CPU fallback: without a CUDA device every compute entry point
  *     fails with CSIM_E_CUDA.
+ *   - prototypes are hidden from NVRTC (__CUDACC_RTC__): the run-time-compiled
+ *     specialised kernels include this header for the shared types only.
  */
 #ifndef CSIM_B200_H
 #define CSIM_B200_H
@@ -100,7 +102,9 @@ typedef struct csim_constants {
 } csim_constants;
 
 /* Fills *c with the reference's literals. */
+#ifndef __CUDACC_RTC__
 void csim_default_constants(csim_constants* c);
+#endif
 
 /* ---- flat topology: what Circuit + assignEquationIndices() define ------- *
  * (include/circuit.hpp:33-66, src/circuit.cpp:42-61).  Elements are listed in
@@ -122,24 +126,63 @@ typedef struct csim_topology {
 typedef struct csim_plan csim_plan;   /* topology lowered to device tables; immutable, shareable   */
 typedef struct csim_batch csim_batch; /* B instances on one device: owns device buffers + a stream */
 
+#ifndef __CUDACC_RTC__
 const char* csim_last_error(void);
 int csim_abi_version(void);
+#endif
 /* Number of visible CUDA devices, or CSIM_E_CUDA. */
+#ifndef __CUDACC_RTC__
 int csim_device_count(void);
+#endif
 
 /* Builds the stamp programs (ordered per-slot contribution lists for the DC
  * and the TRAN assembly), the CSR patterns and uploads them to `device`.
  * consts == NULL -> reference defaults.                                        */
+#ifndef __CUDACC_RTC__
 int csim_plan_create(const csim_topology* topo, const csim_constants* consts, int device, csim_plan** out);
 void csim_plan_destroy(csim_plan* plan);
+#endif
 
 /* Host-side introspection (no device work).  mode: 0 = DC assembly, 1 = TRAN
  * assembly.  Structural pattern of G in CSR, rows ascending, columns ascending
  * within a row.  Pass NULL arrays to query *nnz only.                          */
 #define CSIM_MODE_DC 0
 #define CSIM_MODE_TRAN 1
+#ifndef __CUDACC_RTC__
 int csim_plan_pattern(const csim_plan* plan, int mode, int32_t* nnz, int32_t* rowptr /*[N+1]*/, int32_t* colidx /*[nnz]*/);
 int csim_plan_dims(const csim_plan* plan, int32_t* n_unknowns, int32_t* n_params, int32_t* n_sources);
+#endif
+
+/* ---- run-time specialisation of the transient kernel ------------------------- *
+ * For N <= 32 the library generates (NVRTC, sm_100a) a transient kernel for this
+ * topology and a PREDICTED pivot permutation: matrix rows in registers, only the
+ * structurally non-zero operations of stamping, LU and the triangular solves, in
+ * the reference's order.  Every factorisation verifies the reference's
+ * first-max-wins pivot rule (include/solver.hpp:46-56); where the prediction does
+ * not hold, that solve is redone with the generic pivoting code, so results do
+ * not depend on the prediction.  By default csim_dev_tran specialises on first
+ * use, predicting the permutation from instance 0 at its start state.           */
+#ifndef __CUDACC_RTC__
+/* mode 0: generic kernels only; 1: specialise automatically (default; CSIM_JIT=0 in the environment = 0) */
+int csim_plan_jit_mode(csim_plan* plan, int mode);
+/* Specialise now for perm[N] (perm[i] = original row expected at pivot position i). */
+int csim_plan_specialize(csim_plan* plan, const int32_t* perm);
+/* active: 1 when a specialised kernel is loaded; perm [N] (NULL ok); counters since load:
+ * Newton solves done by the generic fallback / all Newton solves; log: generator + NVRTC messages. */
+int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, uint64_t* fallback_solves,
+                        uint64_t* solves, char* log, int32_t log_cap);
+/* Generated CUDA source of the loaded kernel; returns its length (out may be NULL). */
+int csim_plan_spec_source(const csim_plan* plan, char* out, int32_t cap);
+/* Host-only: source the generator emits for perm (no device needed); returns its length. */
+int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* out, int32_t cap);
+#endif
+
+#ifndef __CUDACC_RTC__
+/* Self-test: q_split[i] = the specialised kernels' "reciprocal once + 3-operation quotient"
+ * division of a[i]/b[i], q_ref[i] = the compiler's IEEE a[i]/b[i]; they must be bit-identical. */
+int csim_dev_selftest_div(int64_t n, const double* a, const double* b, double* q_split, double* q_ref,
+                          void* stream);
+#endif
 
 /* ===================== device-pointer entry points ======================== */
 
@@ -152,24 +195,30 @@ int csim_plan_dims(const csim_plan* plan, int32_t* n_unknowns, int32_t* n_params
  * src_val [n_sources][B] = value of each independent source (already scaled
  * for DC, evaluated at t for TRAN), or NULL to use evalDC(scale) from params;
  * vals [nnz(mode)][B], rhs [N][B].                                             */
+#ifndef __CUDACC_RTC__
 int csim_dev_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double* params, const double* x,
                        const double* x_prev, const double* src_val, double dt, double source_scale,
                        double gmin, double* vals, double* rhs, void* stream);
+#endif
 
 /* Batched Solver::solveLinearSystemLU (include/solver.hpp:83-131) on dense
  * N x N systems, N <= 32: A [N*N][B] row-major over (i,j), b [N][B] ->
  * x [N][B], perm [N][B] (perm[i] = original row now at position i,
  * solver.hpp:41-44,66), singular [B] (1 -> x is the zero vector).              */
+#ifndef __CUDACC_RTC__
 int csim_dev_lu_solve(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
                       int32_t* singular, double lu_eps, void* stream);
+#endif
 
 /* DC operating point for every instance (dcSolveLU, src/dcanalysis.cpp:242-248:
  * Newton ramp 95-163 when the netlist has MOSFETs, direct solve 46-68 otherwise).
  * x [N][B] out; iters [dc_ramp_steps][B] Newton iterations spent per ramp step
  * (may be NULL); pivot_hash [B] in/out running hash of every pivot permutation
  * (may be NULL; see csim_pivot_hash_* below); status [B] OR-ed in.              */
+#ifndef __CUDACC_RTC__
 int csim_dev_dc(const csim_plan* plan, int64_t B, const double* params, double* x, int32_t* iters,
                 uint64_t* pivot_hash, uint32_t* status, void* stream);
+#endif
 
 typedef struct csim_tran_args {
     double dt;              /* .TRAN tstep                                                   */
@@ -199,32 +248,44 @@ typedef struct csim_tran_args {
  * wave[(b*n_probes + p)*wave_ld + r]; row 0 of the reference CSV (t = 0, the DC
  * point) is NOT written here.  iters_total [B] += Newton iterations;
  * iters_step [nSteps][B] uint8 per-step counts (may be NULL).                   */
+#ifndef __CUDACC_RTC__
 int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const csim_tran_args* args,
                   double* x, double* wave, int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash,
                   uint32_t* status, void* stream);
+#endif
 
 /* ======================= host-pointer entry points ======================== */
+#ifndef __CUDACC_RTC__
 int csim_batch_create(const csim_plan* plan, int64_t B, csim_batch** out);
 void csim_batch_destroy(csim_batch* batch);
 int csim_batch_set_params(csim_batch* batch, const double* params /*[P][B] host*/);
+#endif
 /* DC operating point; x [N][B], iters [ramp][B] (NULL ok), status [B] (NULL ok). */
+#ifndef __CUDACC_RTC__
 int csim_batch_dc(csim_batch* batch, double* x, int32_t* iters, uint64_t* pivot_hash, uint32_t* status);
+#endif
 /* DC operating point followed by the whole transient, as
  * runTransientAnalysisBackwardEuler does (src/tanalisis.cpp:112 then 255-420).
  * args->src_table / src_group_b are HOST pointers here.  wave as above but
  * host; x_dc [N][B] and x_final [N][B] may be NULL.                             */
+#ifndef __CUDACC_RTC__
 int csim_batch_tran(csim_batch* batch, const csim_tran_args* args, double* x_dc, double* x_final, double* wave,
                     int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status);
+#endif
 /* Host-pointer forms of the two standalone kernels (copies inside; for the C++ drop-in
  * classes Element::stamp and Solver::solveLinearSystemLU and for small tests).            */
+#ifndef __CUDACC_RTC__
 int csim_host_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double* params, const double* x,
                         const double* x_prev, const double* src_val, double dt, double source_scale,
                         double gmin, double* vals, double* rhs);
 int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
                        int32_t* singular, double lu_eps);
+#endif
 /* Milliseconds of the kernels of the last csim_batch_* call, measured with CUDA
  * events on the batch's stream (copies excluded).                               */
+#ifndef __CUDACC_RTC__
 float csim_batch_last_kernel_ms(const csim_batch* batch);
+#endif
 
 /* ---- pivot-sequence hash (shared definition, host-callable) ------------- *
  * Every factorisation contributes f = sum_i mix(i, perm[i]) (mod 2^64) and the
@@ -233,7 +294,9 @@ float csim_batch_last_kernel_ms(const csim_batch* batch);
  * overwhelming probability) they chose the same pivot rows in the same order
  * in every factorisation.                                                       */
 #define CSIM_PIVOT_HASH_INIT 0xCBF29CE484222325ull
+#ifndef __CUDACC_RTC__
 uint64_t csim_pivot_hash_update(uint64_t h, const int32_t* perm, int32_t n);
+#endif
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,153 @@
+"""GPU: the run-time specialised transient kernel (NVRTC) against the generic kernel and the oracle.
+The pivot permutation it is generated for is only a prediction; results must not depend on it."""
+import numpy as np
+import pytest
+
+from oracle import oraclelib as O
+from support import assert_same_bits, load_golden, make_plan, n_steps_of, perturb
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    assert torch.cuda.is_available()
+    return torch
+
+
+def dev(torch, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def u64(t):
+    return t.cpu().numpy().view(np.uint64)
+
+
+def run(capi, torch, plan, P, topo, dt, ns):
+    params = dev(torch, P.T)
+    d = capi.dc(plan, params)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    setup = capi.TranSetup(dt, ns, m, grp, tab, probes=np.arange(topo.n_unknowns))
+    t = capi.tran(plan, params, d["x"].clone(), setup, pivot_hash=d["hash"].clone(), status=d["status"].clone(),
+                  want_iters_step=True)
+    torch.cuda.synchronize()
+    return dict(x=t["x"].cpu().numpy(), wave=t["wave"].cpu().numpy(), its=t["iters_step"].cpu().numpy(),
+                hash=u64(t["hash"]), status=t["status"].cpu().numpy(), total=t["iters_total"].cpu().numpy())
+
+
+def same(a, b, what):
+    assert_same_bits(a["wave"], b["wave"], what + " waveforms")
+    assert_same_bits(a["x"], b["x"], what + " final state")
+    assert np.array_equal(a["its"], b["its"]) and np.array_equal(a["hash"], b["hash"]), what
+    assert np.array_equal(a["status"], b["status"]) and np.array_equal(a["total"], b["total"]), what
+
+
+def test_split_division_is_bit_identical_to_ieee_division(torch):
+    """rcp_seq + fdiv (spec_runtime.cuh) == a / b for random, huge, tiny, zero, inf and NaN operands."""
+    from circuitsimulator_b200 import capi
+    rng = np.random.default_rng(0)
+    n = 1 << 22
+    a = rng.normal(size=n) * 10.0 ** rng.uniform(-30, 30, n)
+    b = rng.normal(size=n) * 10.0 ** rng.uniform(-30, 30, n)
+    # adversarial exponents / mantissas
+    k = 1 << 18
+    a[:k] = np.ldexp(rng.uniform(1, 2, k), rng.integers(-1074, 1023, k))
+    b[:k] = np.ldexp(rng.uniform(1, 2, k), rng.integers(-1074, 1023, k))
+    b[k:2 * k] = np.nextafter(np.ldexp(1.0, rng.integers(-500, 500, k)), 0)        # mantissa all ones
+    a[2 * k:3 * k] = rng.integers(1, 1 << 20, k).astype(float)                        # exact small quotients
+    b[2 * k:3 * k] = rng.integers(1, 1 << 20, k).astype(float)
+    special = np.array([0.0, -0.0, np.inf, -np.inf, np.nan, 1.0, -1.0, 5e-324, 1.7976931348623157e308, 2.2250738585072014e-308])
+    aa, bb = np.meshgrid(special, special)
+    a[-aa.size:], b[-bb.size:] = aa.ravel(), bb.ravel()
+    qs, qr = capi.selftest_div(dev(torch, a), dev(torch, b))
+    torch.cuda.synchronize()
+    qs, qr = qs.cpu().numpy(), qr.cpu().numpy()
+    nan = np.isnan(qr)
+    assert np.array_equal(np.isnan(qs), nan)
+    assert np.array_equal(qs[~nan].view(np.uint64), qr[~nan].view(np.uint64))
+    with np.errstate(all="ignore"):
+        host = a / b  # x86 IEEE division == what the reference computes
+    assert np.array_equal(qr[~nan].view(np.uint64), host[~nan].view(np.uint64))
+
+
+def test_dbmixer_specialised_equals_generic_and_oracle(torch):
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("dbmixer")
+    B, dt, ns = 12, float(g["dt"]), 600
+    P = perturb(topo.params, topo, B, 20261104)
+    generic = make_plan(topo)
+    generic.jit_mode(0)
+    a = run(capi, torch, generic, P, topo, dt, ns)
+    assert not generic.spec_info()["active"]
+    spec = make_plan(topo)
+    b = run(capi, torch, spec, P, topo, dt, ns)
+    info = spec.spec_info()
+    assert info["active"], info["log"]
+    same(a, b, "dbmixer specialised vs generic")
+    assert info["solves"] == int(b["total"].sum()) and info["fallback_solves"] == 0, info
+    assert list(info["perm"]) == [21, 1, 2, 3, 4, 5, 6, 7, 22, 9, 23, 11, 12, 13, 24, 25, 26, 27, 28, 29, 30, 0, 8, 10,
+                                  14, 15, 16, 17, 18, 19, 20]  # the reference's TRAN permutation
+    assert_same_bits(b["wave"][0].T[:400], g["wave_first"], "nominal vs golden")
+    assert "csim_tran_spec" in spec.spec_source()
+    for k in (0, 3, 7):
+        od = O.dc(topo, P[k])
+        m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+        ot = O.tran(topo, P[k], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(b["wave"][k].T, ot["wave"], f"inst {k} vs oracle")
+        assert b["hash"][k] == np.uint64(ot["hash"])
+
+
+def test_buffer_specialised_with_pivot_misses(torch):
+    """buffer.sp changes its pivot order ~12 % of the time: those solves must take the generic path and the
+    result must still be bit-identical (full 300 steps, every unknown)."""
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    B, dt, ns = 16, float(g["dt"]), n_steps_of(g)
+    P = perturb(topo.params, topo, B, 20261104 + 3)
+    generic = make_plan(topo)
+    generic.jit_mode(0)
+    a = run(capi, torch, generic, P, topo, dt, ns)
+    spec = make_plan(topo)
+    b = run(capi, torch, spec, P, topo, dt, ns)
+    info = spec.spec_info()
+    assert info["active"], info["log"]
+    same(a, b, "buffer specialised vs generic")
+    assert 0 < info["fallback_solves"] < info["solves"], info
+    assert_same_bits(b["wave"][0].T, g["wave"], "nominal buffer vs golden")
+    assert b["hash"][0] == np.uint64(g["hash"])
+
+
+def test_wrong_prediction_only_costs_time(torch):
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    B, dt, ns = 6, float(g["dt"]), 60
+    P = perturb(topo.params, topo, B, 5)
+    generic = make_plan(topo)
+    generic.jit_mode(0)
+    a = run(capi, torch, generic, P, topo, dt, ns)
+    wrong = make_plan(topo)
+    wrong.specialize(np.arange(topo.n_unknowns))  # identity: never what partial pivoting picks here
+    b = run(capi, torch, wrong, P, topo, dt, ns)
+    info = wrong.spec_info()
+    assert info["active"] and info["fallback_solves"] == info["solves"] > 0
+    same(a, b, "identity prediction")
+
+
+def test_degenerate_and_chunked_through_specialised_kernel(torch):
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    plan = make_plan(topo)
+    dt, ns = float(g["dt"]), 40
+    P = np.repeat(topo.params[None], 3, 0)
+    e_l = [e for e in range(topo.n_elems) if topo.elem_type[e] == O.ELEM_L]
+    P[1, topo.elem_param[e_l[0]]] = 0.0  # empty branch row -> singular -> zero vector
+    b = run(capi, torch, plan, P, topo, dt, ns)
+    assert plan.spec_info()["active"]
+    for k in range(3):
+        od = O.dc(topo, P[k])
+        m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+        ot = O.tran(topo, P[k], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(b["wave"][k].T, ot["wave"], f"inst {k}")
+        assert int(b["status"][k]) == (od["status"] | ot["status"]) and b["hash"][k] == np.uint64(ot["hash"])
+    assert int(b["status"][1]) & capi.ST_LU_SINGULAR

@@ -1,0 +1,52 @@
+"""CPU: the kernel generator emits source for a plan without any device, and NVRTC (no GPU needed to compile)
+accepts it for sm_100a."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oraclelib as O
+from support import load_golden
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _perm(topo, g):
+    dt = float(g["dt"])
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, 2)
+    x = g["x_dc"]
+    G, I = O.stamp(topo, 1, topo.params, x, x, O.src_tran(topo, topo.params, m, grp, tab, 0, dt), dt=dt, gmin=1e-6)
+    return O.lu_solve(G, I)[1]
+
+
+@pytest.mark.parametrize("name", ["buffer", "dbmixer"])
+def test_generated_source_compiles_for_sm100a(name):
+    from circuitsimulator_b200 import capi
+    nvrtc = pytest.importorskip("cuda.bindings.nvrtc")
+    g, topo = load_golden(name)
+    plan = capi.Plan(topo.n_unknowns, topo.n_node_eq, topo.elem_type, topo.elem_flags, topo.elem_nodes,
+                     topo.elem_branch, topo.elem_param, topo.n_params, device=-1)
+    src = plan.generate_source(_perm(topo, g))
+    assert "csim_tran_spec" in src and f"#define SPEC_N {topo.n_unknowns}" in src
+    shim = (b"#pragma once\ntypedef signed char int8_t; typedef unsigned char uint8_t; typedef short int16_t; "
+            b"typedef unsigned short uint16_t;\ntypedef int int32_t; typedef unsigned int uint32_t; "
+            b"typedef long long int64_t; typedef unsigned long long uint64_t;\n")
+    err, prog = nvrtc.nvrtcCreateProgram(src.encode(), b"spec.cu", 1, [shim], [b"stdint.h"])
+    opts = [b"--gpu-architecture=sm_100a", b"--std=c++17", b"--fmad=false",
+            ("-I" + os.path.join(ROOT, "circuitsimulator_b200", "csrc")).encode()]
+    err, = nvrtc.nvrtcCompileProgram(prog, len(opts), opts)
+    _, n = nvrtc.nvrtcGetProgramLogSize(prog)
+    log = b" " * n
+    nvrtc.nvrtcGetProgramLog(prog, log)
+    assert int(err) == 0, log.decode()
+    _, cs = nvrtc.nvrtcGetCUBINSize(prog)
+    assert cs > 10000
+
+
+def test_generator_rejects_non_permutations():
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    plan = capi.Plan(topo.n_unknowns, topo.n_node_eq, topo.elem_type, topo.elem_flags, topo.elem_nodes,
+                     topo.elem_branch, topo.elem_param, topo.n_params, device=-1)
+    with pytest.raises(capi.CsimError, match="permutation"):
+        plan.generate_source(np.zeros(topo.n_unknowns, np.int32))
