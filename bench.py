@@ -339,11 +339,19 @@ def run_ours(args):
     s1.record()
     torch.cuda.synchronize()
     stamp_ms = s0.elapsed_time(s1) / nrep
-    bytes_per_inst = 8 * (P + N + N + nnz + N)  # params + x + x_prev + vals + rhs
+    # Algorithmic bytes per instance = the DISTINCT doubles one TRAN assembly has to read (device parameters,
+    # the MOSFET terminals of x, the companion-model entries of x_prev, one value per source) and write
+    # (CSR values + RHS) — counted by the plan (csim_plan_stamp_info).  SURVEY.md §8(d)'s upper figure
+    # 8*(P+N+N+nnz+N) also counts source-waveform parameters and x/x_prev entries no stamp reads; it is
+    # reported next to it, the roofline fraction uses the smaller, exact one.
+    sinfo = plan.stamp_info(capi.MODE_TRAN, True)
+    bytes_per_inst = sinfo["bytes_read"] + sinfo["bytes_written"]
     achieved = bytes_per_inst * Bs / (stamp_ms / 1e3) / 1e9
-    roofline = {"kernel": "stamp_csr_kernel<TRAN>", "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
+    roofline = {"kernel": "csim_stamp_spec<TRAN>" if sinfo["active"] else "stamp_csr_kernel<TRAN>", "bound": "hbm",
+                "achieved": achieved, "peak": peaks["hbm_gbs"],
                 "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_kind": peak_kind,
-                "bytes_per_instance": bytes_per_inst, "instances": Bs, "ms": stamp_ms,
+                "bytes_per_instance": bytes_per_inst, "bytes_per_instance_survey_formula": 8 * (P + N + N + nnz + N),
+                "instances": Bs, "ms": stamp_ms,
                 "l2": "inputs+outputs %.2f GB > 126 MB L2" % (bytes_per_inst * Bs / 1e9)}
     del sp, sx, sxp, ssv, svals, srhs
 

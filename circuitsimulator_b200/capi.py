@@ -33,6 +33,7 @@ EXPORTS = [
     "csim_host_stamp_csr", "csim_host_lu_solve",
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",
+    "csim_plan_stamp_info", "csim_plan_generate_stamp_source",
 ]
 
 
@@ -104,6 +105,9 @@ def lib():
         L.csim_plan_spec_source.argtypes = [C.c_void_p, C.c_char_p, C.c_int32]
         L.csim_plan_generate_source.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_char_p, C.c_int32]
         L.csim_dev_selftest_div.argtypes = [C.c_int64] + [C.c_void_p] * 5
+        L.csim_plan_stamp_info.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int64),
+                                           C.POINTER(C.c_int64), C.c_char_p, C.c_int32]
+        L.csim_plan_generate_stamp_source.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int32]
         L.csim_batch_create.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
         L.csim_batch_destroy.argtypes = [C.c_void_p]
         L.csim_batch_set_params.argtypes = [C.c_void_p, C.c_void_p]
@@ -199,6 +203,23 @@ class Plan:
             _check(n, "csim_plan_generate_source")
         buf = C.create_string_buffer(n + 1)
         lib().csim_plan_generate_source(self.handle, _ip(perm), buf, n + 1)
+        return buf.value.decode()
+
+    def stamp_info(self, mode: int, has_src_val: bool = True):
+        """Specialisation state of the standalone assembly kernel and its algorithmic bytes per instance."""
+        act, br, bw = C.c_int32(), C.c_int64(), C.c_int64()
+        log = C.create_string_buffer(1 << 14)
+        _check(lib().csim_plan_stamp_info(self.handle, mode, int(has_src_val), C.byref(act), C.byref(br), C.byref(bw),
+                                          log, len(log)), "csim_plan_stamp_info")
+        return dict(active=bool(act.value), bytes_read=int(br.value), bytes_written=int(bw.value),
+                    log=log.value.decode(errors="replace"))
+
+    def generate_stamp_source(self, mode: int) -> str:
+        n = lib().csim_plan_generate_stamp_source(self.handle, mode, None, 0)
+        if n < 0:
+            _check(n, "csim_plan_generate_stamp_source")
+        buf = C.create_string_buffer(n + 1)
+        lib().csim_plan_generate_stamp_source(self.handle, mode, buf, n + 1)
         return buf.value.decode()
 
     def pattern(self, mode: int):

@@ -22,6 +22,7 @@ using namespace csim;
 
 namespace {
 thread_local std::string g_err;
+thread_local bool g_generic_stamp_only = false;  // set while the pivot pilot runs (it holds the plan's JIT lock)
 int fail(int code, const std::string& msg) {
     g_err = msg;
     return code;
@@ -51,7 +52,7 @@ cudaError_t upload(const std::vector<T>& v, const T** out, std::vector<void*>& o
 
 // Specialised (run-time generated) transient kernel of a plan; see specialize.hpp.
 struct SpecState {
-    std::mutex mu;
+    std::recursive_mutex mu;
     int mode = 1;        // 0 = generic kernels only, 1 = specialise automatically on first use
     bool tried = false;  // a specialisation attempt has been made
     bool ready = false;  // kernel loaded and usable
@@ -64,6 +65,14 @@ struct SpecState {
     std::string log;
 };
 
+// Specialised standalone assembly kernel, one per mode (specialize_stamp.cpp).
+struct StampSpecState {
+    bool tried = false, ready = false;
+    StampSpecHost host;
+    JitKernel k;
+    std::string log;
+};
+
 struct csim_plan {
     HostPlan host;
     DevPlan dev{};
@@ -71,6 +80,7 @@ struct csim_plan {
     int sm_count = 0;
     std::vector<void*> owned;
     mutable SpecState spec;
+    mutable StampSpecState stamp_spec[2];
 };
 
 struct csim_batch {
@@ -164,8 +174,10 @@ int spec_pilot(const csim_plan* plan, int64_t B, const double* d_params, const d
     if (P > 0) CU(cudaMemcpy2D(p.data(), sizeof(double), d_params, sizeof(double) * B, sizeof(double), P, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy2D(x.data(), sizeof(double), d_x, sizeof(double) * B, sizeof(double), N, cudaMemcpyDeviceToHost));
     std::vector<double> vals(mp.colidx.size()), rhs(N);
+    g_generic_stamp_only = true;
     int rc = csim_host_stamp_csr(plan, CSIM_MODE_TRAN, 1, p.data(), x.data(), x.data(), sv.data(), dt, 1.0,
                                  plan->host.consts.tran_gmin, vals.data(), rhs.data());
+    g_generic_stamp_only = false;
     if (rc) return rc;
     std::vector<double> A((size_t)N * N, 0.0), sol(N);
     for (int i = 0; i < N; ++i)
@@ -182,7 +194,7 @@ int spec_pilot(const csim_plan* plan, int64_t B, const double* d_params, const d
 bool spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const double* d_x, double dt,
                   cudaStream_t stream) {
     SpecState& sp = plan->spec;
-    std::lock_guard<std::mutex> lock(sp.mu);
+    std::lock_guard<std::recursive_mutex> lock(sp.mu);
     if (sp.mode == 0) return false;
     if (sp.ready) return true;
     if (sp.tried) return false;
@@ -219,6 +231,54 @@ cudaError_t spec_launch(const csim_plan* plan, const DevTran& T, int64_t B, cons
     const unsigned blocks = (unsigned)((B + wpb - 1) / wpb);
     return cudaLaunchKernel(reinterpret_cast<const void*>(sp.k.kernel), dim3(blocks), dim3(wpb * 32), args, sp.smem,
                             stream);
+}
+
+// true -> the specialised assembly kernel of `mode` is loaded (compiled on first use)
+bool stamp_spec_prepare(const csim_plan* plan, int mode) {
+    SpecState& sp = plan->spec;
+    std::lock_guard<std::recursive_mutex> lock(sp.mu);
+    StampSpecState& ss = plan->stamp_spec[mode];
+    if (sp.mode == 0) return false;
+    if (ss.ready) return true;
+    if (ss.tried) return false;
+    ss.tried = true;
+    const char* env = std::getenv("CSIM_JIT");
+    if (env && env[0] == '0') {
+        ss.log = "disabled by CSIM_JIT=0";
+        return false;
+    }
+    try {
+        ss.host = generate_stamp_spec(plan->host, mode);
+    } catch (const std::exception& e) {
+        ss.log = e.what();
+        return false;
+    }
+    std::vector<char> cubin;
+    std::string log;
+    if (!jit_compile(ss.host.source, "csim_stamp_spec.cu", jit_library_dir() + "/csrc", cubin, log)) {
+        ss.log = "NVRTC: " + log;
+        return false;
+    }
+    if (jit_load(cubin, "csim_stamp_spec", ss.k) != cudaSuccess) {
+        ss.log = "cudaLibraryLoadData failed";
+        cudaGetLastError();
+        return false;
+    }
+    ss.log = "specialised" + (log.size() > 1 ? "\n" + log : std::string());
+    ss.ready = true;
+    return true;
+}
+
+cudaError_t stamp_spec_launch(const csim_plan* plan, int mode, int64_t B, const double* params, const double* x,
+                              const double* x_prev, const double* src_val, double dt, double scale, double gmin,
+                              double* vals, double* rhs, cudaStream_t stream) {
+    StampSpecState& ss = plan->stamp_spec[mode];
+    long long Bll = B;
+    double off = plan->host.consts.mos_off_gds;
+    void* args[] = {&Bll, &params, &x, &x_prev, &src_val, &dt, &scale, &gmin, &off, &vals, &rhs};
+    const int T = ss.host.threads;
+    const unsigned blocks = (unsigned)((B + T - 1) / T);
+    return cudaLaunchKernel(reinterpret_cast<const void*>(ss.k.kernel), dim3(blocks), dim3(T), args, 0, stream);
 }
 
 }  // namespace
@@ -324,6 +384,8 @@ void csim_plan_destroy(csim_plan* plan) {
         for (void* d : plan->owned) cudaFree(d);
         for (void* d : plan->spec.owned) cudaFree(d);
         jit_unload(plan->spec.k);
+        jit_unload(plan->stamp_spec[0].k);
+        jit_unload(plan->stamp_spec[1].k);
     }
     delete plan;
 }
@@ -366,8 +428,12 @@ int csim_dev_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double*
     if (rc) return rc;
     if (mode < 0 || mode > 1 || B <= 0 || !params || !x || !vals || !rhs || (mode == CSIM_MODE_TRAN && !x_prev))
         return fail(CSIM_E_INVALID, "csim_dev_stamp_csr: bad argument");
-    CU(launch_stamp_csr(plan->dev, mode, B, params, x, x_prev, src_val, dt, source_scale, gmin, vals, rhs,
-                        plan->sm_count, (cudaStream_t)stream));
+    if (!g_generic_stamp_only && stamp_spec_prepare(plan, mode))
+        CU(stamp_spec_launch(plan, mode, B, params, x, x_prev, src_val, dt, source_scale, gmin, vals, rhs,
+                             (cudaStream_t)stream));
+    else
+        CU(launch_stamp_csr(plan->dev, mode, B, params, x, x_prev, src_val, dt, source_scale, gmin, vals, rhs,
+                            plan->sm_count, (cudaStream_t)stream));
     return CSIM_OK;
 }
 
@@ -669,7 +735,7 @@ int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, d
 
 int csim_plan_jit_mode(csim_plan* plan, int mode) {
     if (!plan || mode < 0 || mode > 1) return fail(CSIM_E_INVALID, "csim_plan_jit_mode: bad argument");
-    std::lock_guard<std::mutex> lock(plan->spec.mu);
+    std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
     plan->spec.mode = mode;
     return CSIM_OK;
 }
@@ -678,7 +744,7 @@ int csim_plan_specialize(csim_plan* plan, const int32_t* perm) {
     int rc = need_device(plan, "csim_plan_specialize");
     if (rc) return rc;
     if (!perm) return fail(CSIM_E_INVALID, "csim_plan_specialize: null permutation");
-    std::lock_guard<std::mutex> lock(plan->spec.mu);
+    std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
     plan->spec.tried = true;
     plan->spec.mode = 1;
     return spec_build(plan, std::vector<int32_t>(perm, perm + plan->host.N));
@@ -688,7 +754,7 @@ int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, u
                         uint64_t* solves, char* log, int32_t log_cap) {
     if (!plan) return fail(CSIM_E_INVALID, "csim_plan_spec_info: null plan");
     SpecState& sp = plan->spec;
-    std::lock_guard<std::mutex> lock(sp.mu);
+    std::lock_guard<std::recursive_mutex> lock(sp.mu);
     if (active) *active = sp.ready && sp.mode != 0 ? 1 : 0;
     if (perm && sp.ready)
         for (int i = 0; i < plan->host.N; ++i) perm[i] = sp.host.perm[i];
@@ -706,7 +772,7 @@ int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, u
 
 int csim_plan_spec_source(const csim_plan* plan, char* out, int32_t cap) {
     if (!plan) return fail(CSIM_E_INVALID, "csim_plan_spec_source: null plan");
-    std::lock_guard<std::mutex> lock(plan->spec.mu);
+    std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
     const std::string& src = plan->spec.host.source;
     if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", src.c_str());
     return (int)src.size();
@@ -717,6 +783,30 @@ int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* 
     if (!plan || !perm) return fail(CSIM_E_INVALID, "csim_plan_generate_source: null argument");
     try {
         SpecHost sh = generate_tran_spec(plan->host, std::vector<int32_t>(perm, perm + plan->host.N));
+        if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", sh.source.c_str());
+        return (int)sh.source.size();
+    } catch (const std::exception& e) {
+        return fail(CSIM_E_UNSUPPORTED, e.what());
+    }
+}
+
+int csim_plan_stamp_info(const csim_plan* plan, int mode, int has_src_val, int32_t* spec_active, int64_t* bytes_read,
+                         int64_t* bytes_written, char* log, int32_t log_cap) {
+    if (!plan || mode < 0 || mode > 1) return fail(CSIM_E_INVALID, "csim_plan_stamp_info: bad argument");
+    const StampTraffic t = stamp_traffic(plan->host, mode, has_src_val != 0);
+    if (bytes_read) *bytes_read = 8 * t.doubles_read;
+    if (bytes_written) *bytes_written = 8 * t.doubles_written;
+    std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
+    const StampSpecState& ss = plan->stamp_spec[mode];
+    if (spec_active) *spec_active = ss.ready && plan->spec.mode != 0 ? 1 : 0;
+    if (log && log_cap > 0) std::snprintf(log, (size_t)log_cap, "%s", ss.log.c_str());
+    return CSIM_OK;
+}
+
+int csim_plan_generate_stamp_source(const csim_plan* plan, int mode, char* out, int32_t cap) {
+    if (!plan || mode < 0 || mode > 1) return fail(CSIM_E_INVALID, "csim_plan_generate_stamp_source: bad argument");
+    try {
+        StampSpecHost sh = generate_stamp_spec(plan->host, mode);
         if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", sh.source.c_str());
         return (int)sh.source.size();
     } catch (const std::exception& e) {

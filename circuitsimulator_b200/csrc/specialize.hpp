@@ -41,4 +41,20 @@ SpecHost generate_tran_spec(const HostPlan& hp, const std::vector<int32_t>& perm
 // Per-block dynamic shared memory of the generated kernel.
 size_t spec_smem_bytes(const HostPlan& hp, const SpecHost& sh);
 
+// ---- standalone assembly kernel (specialize_stamp.cpp) ---------------------------------------
+struct StampSpecHost {
+    int32_t mode = 0;
+    std::string source;  // CUDA C++ translation unit (entry: csim_stamp_spec)
+    int32_t threads = 128, blocks_per_sm = 3;
+};
+// mode: CSIM_MODE_DC / CSIM_MODE_TRAN.  Any topology (no N <= 32 restriction).
+StampSpecHost generate_stamp_spec(const HostPlan& hp, int mode);
+
+// Distinct doubles one assembly reads / writes per instance (what the kernels — generic and
+// specialised alike — must move; repeated reads of one input hit L1).
+struct StampTraffic {
+    int64_t doubles_read = 0, doubles_written = 0;
+};
+StampTraffic stamp_traffic(const HostPlan& hp, int mode, bool has_src_val);
+
 }  // namespace csim

@@ -177,6 +177,18 @@ int csim_plan_spec_source(const csim_plan* plan, char* out, int32_t cap);
 int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* out, int32_t cap);
 #endif
 
+/* The standalone assembly kernel (csim_dev_stamp_csr) is specialised the same way on first use
+ * (straight-line code, every distinct input loaded once, values in registers); any N.
+ * bytes_read / bytes_written: distinct input / output bytes ONE assembly of `mode` moves per
+ * instance (has_src_val: sources given per instance instead of evalDC(scale) from the parameters) —
+ * the algorithmic traffic the roofline figure is computed from.                                  */
+#ifndef __CUDACC_RTC__
+int csim_plan_stamp_info(const csim_plan* plan, int mode, int has_src_val, int32_t* spec_active, int64_t* bytes_read,
+                         int64_t* bytes_written, char* log, int32_t log_cap);
+/* Host-only: source the generator emits for the assembly kernel of `mode`; returns its length. */
+int csim_plan_generate_stamp_source(const csim_plan* plan, int mode, char* out, int32_t cap);
+#endif
+
 #ifndef __CUDACC_RTC__
 /* Self-test: q_split[i] = the specialised kernels' "reciprocal once + 3-operation quotient"
  * division of a[i]/b[i], q_ref[i] = the compiler's IEEE a[i]/b[i]; they must be bit-identical. */

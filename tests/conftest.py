@@ -9,6 +9,7 @@ if ROOT not in sys.path:
 
 
 def pytest_configure(config):
+    import torch  # noqa: F401  (before cuda.bindings: importing torch after NVRTC's bindings fails in this image)
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with `-m gpu`)")
 
 

@@ -24,13 +24,21 @@ def dev(torch, a):
     return torch.from_numpy(np.ascontiguousarray(a)).cuda()
 
 
+@pytest.mark.parametrize("jit", [1, 0])
 @pytest.mark.parametrize("name,mode", [("buffer", 0), ("buffer", 1), ("dbmixer", 0), ("dbmixer", 1)])
-def test_stamp_csr_bit_exact(torch, name, mode):
+def test_stamp_csr_bit_exact(torch, name, mode, jit):
+    """Both forms of the assembly kernel (run-time specialised / generic interpreter) against the oracle;
+    B is not a multiple of the CTA size; a few instances carry the degenerate values the reference special-cases
+    (R == 0, C <= 0, L <= 0: src/element.cpp:20-23, src/tanalisis.cpp:65,296)."""
     from circuitsimulator_b200 import capi
     g, topo = load_golden(name)
     plan = make_plan(topo)
-    B, N, dt = 96, topo.n_unknowns, float(g["dt"])
+    plan.jit_mode(jit)
+    B, N, dt = 301, topo.n_unknowns, float(g["dt"])
     P = perturb(topo.params, topo, B, 42)
+    for b, ty in ((3, O.ELEM_R), (4, O.ELEM_C), (5, O.ELEM_L), (6, O.ELEM_MOS)):
+        e = int(np.argwhere(topo.elem_type == ty)[0, 0])
+        P[b, topo.elem_param[e] + (3 if ty == O.ELEM_MOS else 0)] = 0.0 if ty != O.ELEM_C else -1e-12
     rng = np.random.default_rng(5)
     X = np.stack([g["x_dc"] + rng.normal(scale=0.3, size=N) for _ in range(B)])
     XP = np.stack([g["x_dc"] + rng.normal(scale=0.3, size=N) for _ in range(B)])
@@ -40,6 +48,7 @@ def test_stamp_csr_bit_exact(torch, name, mode):
     vals, rhs = capi.stamp_csr(plan, mode, dev(torch, P.T), dev(torch, X.T), dev(torch, XP.T), dev(torch, SV.T),
                                dt=dt, gmin=gmin)
     torch.cuda.synchronize()
+    assert plan.stamp_info(mode)["active"] == bool(jit), plan.stamp_info(mode)["log"]
     vals, rhs = vals.cpu().numpy(), rhs.cpu().numpy()
     rowptr, colidx = plan.pattern(mode)
     rows = np.repeat(np.arange(N), np.diff(rowptr))
