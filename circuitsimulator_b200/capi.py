@@ -33,7 +33,7 @@ EXPORTS = [
     "csim_host_stamp_csr", "csim_host_lu_solve",
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",
-    "csim_plan_stamp_info", "csim_plan_generate_stamp_source",
+    "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
 ]
 
 
@@ -108,6 +108,7 @@ def lib():
         L.csim_plan_stamp_info.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int64),
                                            C.POINTER(C.c_int64), C.c_char_p, C.c_int32]
         L.csim_plan_generate_stamp_source.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int32]
+        L.csim_plan_generate_source_kind.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int32), C.c_char_p, C.c_int32]
         L.csim_batch_create.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_void_p)]
         L.csim_batch_destroy.argtypes = [C.c_void_p]
         L.csim_batch_set_params.argtypes = [C.c_void_p, C.c_void_p]
@@ -173,7 +174,7 @@ class Plan:
             pass
 
     def jit_mode(self, mode: int):
-        """0: generic kernels only; 1: specialise the transient kernel automatically (default)."""
+        """0: generic kernels only; 1: automatic (default); 2: warp-per-instance; 3: thread-per-instance."""
         _check(lib().csim_plan_jit_mode(self.handle, int(mode)), "csim_plan_jit_mode")
 
     def specialize(self, perm):
@@ -187,7 +188,7 @@ class Plan:
         log = C.create_string_buffer(1 << 14)
         _check(lib().csim_plan_spec_info(self.handle, C.byref(act), _ip(perm), C.byref(fb), C.byref(sv), log, len(log)),
                "csim_plan_spec_info")
-        return dict(active=bool(act.value), perm=perm, fallback_solves=int(fb.value), solves=int(sv.value),
+        return dict(active=bool(act.value), kind=int(act.value), perm=perm, fallback_solves=int(fb.value), solves=int(sv.value),
                     log=log.value.decode(errors="replace"))
 
     def spec_source(self) -> str:
@@ -196,13 +197,14 @@ class Plan:
         lib().csim_plan_spec_source(self.handle, buf, n + 1)
         return buf.value.decode()
 
-    def generate_source(self, perm) -> str:
+    def generate_source(self, perm, kind: int = 2) -> str:
+        """Source of a specialised transient kernel: kind 2 = warp per instance, 3 = thread per instance."""
         perm = _i32(perm)
-        n = lib().csim_plan_generate_source(self.handle, _ip(perm), None, 0)
+        n = lib().csim_plan_generate_source_kind(self.handle, kind, _ip(perm), None, 0)
         if n < 0:
-            _check(n, "csim_plan_generate_source")
+            _check(n, "csim_plan_generate_source_kind")
         buf = C.create_string_buffer(n + 1)
-        lib().csim_plan_generate_source(self.handle, _ip(perm), buf, n + 1)
+        lib().csim_plan_generate_source_kind(self.handle, kind, _ip(perm), buf, n + 1)
         return buf.value.decode()
 
     def stamp_info(self, mode: int, has_src_val: bool = True):

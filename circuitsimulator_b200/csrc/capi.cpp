@@ -53,7 +53,10 @@ cudaError_t upload(const std::vector<T>& v, const T** out, std::vector<void*>& o
 // Specialised (run-time generated) transient kernel of a plan; see specialize.hpp.
 struct SpecState {
     std::recursive_mutex mu;
-    int mode = 1;        // 0 = generic kernels only, 1 = specialise automatically on first use
+    // 0 = generic kernels only; 1 = automatic (thread-per-instance kernel; falls back to the warp-per-instance
+    // one when too many solves miss the predicted pivot order); 2 = warp-per-instance; 3 = thread-per-instance
+    int mode = 1;
+    int kind = 0;        // kernel in use: 0 none yet, 2 warp-per-instance, 3 thread-per-instance
     bool tried = false;  // a specialisation attempt has been made
     bool ready = false;  // kernel loaded and usable
     SpecHost host;
@@ -61,6 +64,15 @@ struct SpecState {
     SpecTables dev{};
     size_t smem = 0;
     std::vector<void*> owned;
+    unsigned long long* d_stats = nullptr;  // [2]: fallback solves, Newton solves
+    std::string log;
+};
+
+// Thread-per-instance specialised transient kernel (specialize_tpi.cpp).
+struct TpiState {
+    bool ready = false;
+    TpiHost host;
+    JitKernel k;
     unsigned long long* d_stats = nullptr;  // [2]: fallback solves, Newton solves
     std::string log;
 };
@@ -81,6 +93,7 @@ struct csim_plan {
     std::vector<void*> owned;
     mutable SpecState spec;
     mutable StampSpecState stamp_spec[2];
+    mutable TpiState tpi;
 };
 
 struct csim_batch {
@@ -163,6 +176,40 @@ int spec_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     return CSIM_OK;
 }
 
+// Generates, compiles and loads the thread-per-instance kernel specialised to `perm`.
+int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
+    TpiState& tp = plan->tpi;
+    tp.ready = false;
+    if (tp.d_stats) cudaFree(tp.d_stats);
+    tp.d_stats = nullptr;
+    jit_unload(tp.k);
+    try {
+        tp.host = generate_tran_tpi(plan->host, perm);
+    } catch (const std::exception& e) {
+        tp.log = e.what();
+        return fail(CSIM_E_UNSUPPORTED, tp.log);
+    }
+    std::vector<char> cubin;
+    std::string log;
+    if (!jit_compile(tp.host.source, "csim_tran_tpi.cu", jit_library_dir() + "/csrc", cubin, log)) {
+        tp.log = "NVRTC: " + log;
+        return fail(CSIM_E_CUDA, tp.log);
+    }
+    CU(jit_load(cubin, "csim_tran_tpi", tp.k));
+    CU(cudaKernelSetAttributeForDevice(tp.k.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)tp.host.smem_bytes, plan->device));
+    CU(cudaMalloc((void**)&tp.d_stats, 2 * sizeof(unsigned long long)));
+    CU(cudaMemset(tp.d_stats, 0, 2 * sizeof(unsigned long long)));
+    tp.log = "thread-per-instance: " + std::to_string(tp.host.n_slots) + " shared doubles per instance, " +
+             std::to_string(tp.host.threads) + " instances per CTA; per Newton iteration: " +
+             std::to_string(tp.host.n_lu_divs) + " multipliers, " + std::to_string(tp.host.n_elim_updates) +
+             " row updates, " + std::to_string(tp.host.n_back_terms) + " back-substitution terms, " +
+             std::to_string(tp.host.n_g_adds) + "+" + std::to_string(tp.host.n_rhs_adds) + " assembly adds" +
+             (log.size() > 1 ? "\n" + log : "");
+    tp.ready = true;
+    return CSIM_OK;
+}
+
 // Pivot order the reference's LU picks for instance 0 of the batch at its current state: one TRAN
 // assembly (device stamp kernel) + one generic LU (device).  Only the ORDER is used, as a prediction.
 int spec_pilot(const csim_plan* plan, int64_t B, const double* d_params, const double* d_x, double dt,
@@ -190,31 +237,57 @@ int spec_pilot(const csim_plan* plan, int64_t B, const double* d_params, const d
     return CSIM_OK;
 }
 
-// true -> the specialised kernel is loaded and should be used for this launch
-bool spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const double* d_x, double dt,
-                  cudaStream_t stream) {
+// In automatic mode the thread-per-instance kernel is kept only while its predicted pivot order holds for
+// (almost) every solve: a lane that misses redoes the solve alone while its 31 neighbours wait.
+constexpr double kTpiMaxMissRate = 0.02;
+constexpr unsigned long long kTpiMinSolves = 20000;
+
+// Kernel to use for this launch: 0 generic, 2 warp-per-instance, 3 thread-per-instance (compiled on first use).
+int spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const double* d_x, double dt,
+                 cudaStream_t stream) {
     SpecState& sp = plan->spec;
+    TpiState& tp = plan->tpi;
     std::lock_guard<std::recursive_mutex> lock(sp.mu);
-    if (sp.mode == 0) return false;
-    if (sp.ready) return true;
-    if (sp.tried) return false;
+    if (sp.mode == 0) return 0;
+    if (sp.mode == 1 && sp.kind == 3 && tp.ready && tp.d_stats) {  // re-evaluate the automatic choice
+        unsigned long long st[2] = {0, 0};
+        cudaStreamSynchronize(stream);
+        if (cudaMemcpy(st, tp.d_stats, sizeof(st), cudaMemcpyDeviceToHost) == cudaSuccess && st[1] >= kTpiMinSolves &&
+            (double)st[0] > kTpiMaxMissRate * (double)st[1]) {
+            tp.log += "\nautomatic mode: " + std::to_string(st[0]) + " of " + std::to_string(st[1]) +
+                      " solves missed the predicted pivot order -> warp-per-instance kernel";
+            sp.kind = 2;
+            if (!sp.ready && spec_build(plan, tp.host.perm) != CSIM_OK) sp.kind = 0;
+            sp.tried = true;
+        }
+    }
+    if (sp.kind == 3 && tp.ready) return 3;
+    if (sp.kind == 2 && sp.ready) return 2;
+    if (sp.tried) return 0;
     sp.tried = true;
+    int want = sp.mode == 2 ? 2 : 3;
     const char* env = std::getenv("CSIM_JIT");
     if (env && env[0] == '0') {
         sp.mode = 0;
         sp.log = "disabled by CSIM_JIT=0";
-        return false;
+        return 0;
+    }
+    if (env && (env[0] == '2' || env[0] == '3')) {
+        want = env[0] - '0';
+        sp.mode = want;
     }
     if (!spec_unsupported_reason(plan->host).empty()) {
         sp.log = "not specialised: " + spec_unsupported_reason(plan->host);
-        return false;
+        return 0;
     }
     std::vector<int32_t> perm;
     if (spec_pilot(plan, B, d_params, d_x, dt, stream, perm) != CSIM_OK) {
         sp.log = std::string("pilot failed: ") + csim_last_error();
-        return false;
+        return 0;
     }
-    return spec_build(plan, perm) == CSIM_OK;
+    if (want == 3 && tpi_build(plan, perm) == CSIM_OK) return sp.kind = 3;
+    if (spec_build(plan, perm) == CSIM_OK) return sp.kind = 2;
+    return 0;
 }
 
 cudaError_t spec_launch(const csim_plan* plan, const DevTran& T, int64_t B, const double* params, double* x,
@@ -279,6 +352,26 @@ cudaError_t stamp_spec_launch(const csim_plan* plan, int mode, int64_t B, const 
     const int T = ss.host.threads;
     const unsigned blocks = (unsigned)((B + T - 1) / T);
     return cudaLaunchKernel(reinterpret_cast<const void*>(ss.k.kernel), dim3(blocks), dim3(T), args, 0, stream);
+}
+
+cudaError_t tpi_launch(const csim_plan* plan, const DevTran& T, int64_t B, const double* params, double* x,
+                       double* wave, int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status,
+                       cudaStream_t stream) {
+    TpiState& tp = plan->tpi;
+    DevPlan P = plan->dev;
+    DevTran Tc = T;
+    long long Bll = B;
+    double* scratch = nullptr;
+    cudaError_t e = cudaMallocAsync((void**)&scratch, sizeof(double) * (size_t)tp.host.n_scratch_rows * B, stream);
+    if (e != cudaSuccess) return e;
+    unsigned long long* stats = tp.d_stats;
+    void* args[] = {&P, &Tc, &Bll, &params, &x, &wave, &iters_total, &iters_step, &pivot_hash, &status, &scratch, &stats};
+    const int T_ = tp.host.threads;
+    const unsigned blocks = (unsigned)((B + T_ - 1) / T_);
+    e = cudaLaunchKernel(reinterpret_cast<const void*>(tp.k.kernel), dim3(blocks), dim3(T_), args, tp.host.smem_bytes,
+                         stream);
+    cudaFreeAsync(scratch, stream);
+    return e;
 }
 
 }  // namespace
@@ -371,6 +464,15 @@ int csim_plan_create(const csim_topology* topo, const csim_constants* consts, in
             CU(upload(mp.row_prog, &dm.row_prog, p->owned));
             CU(upload(mp.slot_ptr, &dm.slot_ptr, p->owned));
             CU(upload(mp.slot_entries, &dm.slot_entries, p->owned));
+            std::vector<uint32_t> cw;
+            std::vector<int32_t> cr;
+            for (const Contribution& c : mp.contribs) {
+                cw.push_back(contrib_word(c.col >= 0 ? c.col : kRhsCol, c.sub != 0, c.value));
+                cr.push_back(c.row);
+            }
+            dm.n_contribs = (int)cw.size();
+            CU(upload(cw, &dm.contrib_words, p->owned));
+            CU(upload(cr, &dm.contrib_rows, p->owned));
         }
     }
     *out = p.release();
@@ -384,6 +486,8 @@ void csim_plan_destroy(csim_plan* plan) {
         for (void* d : plan->owned) cudaFree(d);
         for (void* d : plan->spec.owned) cudaFree(d);
         jit_unload(plan->spec.k);
+        jit_unload(plan->tpi.k);
+        if (plan->tpi.d_stats) cudaFree(plan->tpi.d_stats);
         jit_unload(plan->stamp_spec[0].k);
         jit_unload(plan->stamp_spec[1].k);
     }
@@ -517,7 +621,10 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
     T.src_group_b = a->src_group_b;
     T.probes = d_pack + 2 * ns;
     cudaError_t e;
-    if (spec_prepare(plan, B, params, x, a->dt, stream)) {
+    const int kind = spec_prepare(plan, B, params, x, a->dt, stream);
+    if (kind == 3) {
+        e = tpi_launch(plan, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
+    } else if (kind == 2) {
         e = spec_launch(plan, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
     } else {
         e = launch_tran(plan->dev, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
@@ -734,8 +841,12 @@ int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, d
 }
 
 int csim_plan_jit_mode(csim_plan* plan, int mode) {
-    if (!plan || mode < 0 || mode > 1) return fail(CSIM_E_INVALID, "csim_plan_jit_mode: bad argument");
+    if (!plan || mode < 0 || mode > 3) return fail(CSIM_E_INVALID, "csim_plan_jit_mode: bad argument");
     std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
+    if (mode != plan->spec.mode) {
+        plan->spec.tried = false;
+        plan->spec.kind = 0;
+    }
     plan->spec.mode = mode;
     return CSIM_OK;
 }
@@ -745,35 +856,49 @@ int csim_plan_specialize(csim_plan* plan, const int32_t* perm) {
     if (rc) return rc;
     if (!perm) return fail(CSIM_E_INVALID, "csim_plan_specialize: null permutation");
     std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
-    plan->spec.tried = true;
-    plan->spec.mode = 1;
-    return spec_build(plan, std::vector<int32_t>(perm, perm + plan->host.N));
+    SpecState& sp = plan->spec;
+    sp.tried = true;
+    if (sp.mode == 0) sp.mode = 1;
+    const std::vector<int32_t> pv(perm, perm + plan->host.N);
+    if (sp.mode != 2) {
+        rc = tpi_build(plan, pv);
+        if (rc == CSIM_OK) sp.kind = 3;
+        return rc;
+    }
+    rc = spec_build(plan, pv);
+    if (rc == CSIM_OK) sp.kind = 2;
+    return rc;
 }
 
 int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, uint64_t* fallback_solves,
                         uint64_t* solves, char* log, int32_t log_cap) {
     if (!plan) return fail(CSIM_E_INVALID, "csim_plan_spec_info: null plan");
     SpecState& sp = plan->spec;
+    TpiState& tp = plan->tpi;
     std::lock_guard<std::recursive_mutex> lock(sp.mu);
-    if (active) *active = sp.ready && sp.mode != 0 ? 1 : 0;
-    if (perm && sp.ready)
-        for (int i = 0; i < plan->host.N; ++i) perm[i] = sp.host.perm[i];
-    unsigned long long st[2] = {0, 0};
-    if (sp.ready && sp.d_stats) {
+    const int kind = sp.mode == 0 ? 0 : (sp.kind == 3 && tp.ready ? 3 : (sp.kind == 2 && sp.ready ? 2 : 0));
+    if (active) *active = kind;
+    if (perm && kind)
+        for (int i = 0; i < plan->host.N; ++i) perm[i] = kind == 3 ? tp.host.perm[i] : sp.host.perm[i];
+    unsigned long long st[2] = {0, 0}, st2[2] = {0, 0};
+    if (plan->device >= 0 && (tp.d_stats || sp.d_stats)) {
         cudaSetDevice(plan->device);
         cudaDeviceSynchronize();
-        cudaMemcpy(st, sp.d_stats, sizeof(st), cudaMemcpyDeviceToHost);
+        if (tp.ready && tp.d_stats) cudaMemcpy(st, tp.d_stats, sizeof(st), cudaMemcpyDeviceToHost);
+        if (sp.ready && sp.d_stats) cudaMemcpy(st2, sp.d_stats, sizeof(st2), cudaMemcpyDeviceToHost);
     }
-    if (fallback_solves) *fallback_solves = st[0];
-    if (solves) *solves = st[1];
-    if (log && log_cap > 0) std::snprintf(log, (size_t)log_cap, "%s", sp.log.c_str());
+    if (fallback_solves) *fallback_solves = st[0] + st2[0];
+    if (solves) *solves = st[1] + st2[1];
+    std::string all = sp.log;
+    if (!tp.log.empty()) all = tp.log + (all.empty() ? "" : "\n" + all);
+    if (log && log_cap > 0) std::snprintf(log, (size_t)log_cap, "%s", all.c_str());
     return CSIM_OK;
 }
 
 int csim_plan_spec_source(const csim_plan* plan, char* out, int32_t cap) {
     if (!plan) return fail(CSIM_E_INVALID, "csim_plan_spec_source: null plan");
     std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
-    const std::string& src = plan->spec.host.source;
+    const std::string& src = plan->spec.kind == 3 ? plan->tpi.host.source : plan->spec.host.source;
     if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", src.c_str());
     return (int)src.size();
 }
@@ -785,6 +910,20 @@ int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* 
         SpecHost sh = generate_tran_spec(plan->host, std::vector<int32_t>(perm, perm + plan->host.N));
         if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", sh.source.c_str());
         return (int)sh.source.size();
+    } catch (const std::exception& e) {
+        return fail(CSIM_E_UNSUPPORTED, e.what());
+    }
+}
+
+// kind: 2 = warp-per-instance kernel (csim_tran_spec), 3 = thread-per-instance kernel (csim_tran_tpi)
+int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_t* perm, char* out, int32_t cap) {
+    if (!plan || !perm) return fail(CSIM_E_INVALID, "csim_plan_generate_source_kind: null argument");
+    if (kind == 2) return csim_plan_generate_source(plan, perm, out, cap);
+    if (kind != 3) return fail(CSIM_E_INVALID, "csim_plan_generate_source_kind: kind must be 2 or 3");
+    try {
+        TpiHost th = generate_tran_tpi(plan->host, std::vector<int32_t>(perm, perm + plan->host.N));
+        if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", th.source.c_str());
+        return (int)th.source.size();
     } catch (const std::exception& e) {
         return fail(CSIM_E_UNSUPPORTED, e.what());
     }

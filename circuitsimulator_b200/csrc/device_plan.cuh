@@ -16,6 +16,10 @@ struct DevMode {
     const uint32_t* row_prog;      // [row_len][32]
     const int32_t* slot_ptr;       // [n_slots+1]
     const uint32_t* slot_entries;  // contribution words per slot, reference order
+    // every contribution in the reference's order: word = contrib_word(col | RHS, sub, value), row separately
+    int32_t n_contribs, _pad;
+    const uint32_t* contrib_words;
+    const int32_t* contrib_rows;
 };
 
 struct DevPlan {

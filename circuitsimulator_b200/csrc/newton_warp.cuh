@@ -48,8 +48,9 @@ __device__ __forceinline__ WarpMem carve(double* base, int n_values) {
 
 // ---- value ops ---------------------------------------------------------------
 __device__ __forceinline__ void eval_static(const DevMode& m, const double* __restrict__ params, int64_t B,
-                                            int64_t b, double dt, double gmin, double* vt, int lane) {
-    for (int i = lane; i < m.n_static; i += 32) {
+                                            int64_t b, double dt, double gmin, double* vt, int lane,
+                                            int stride = 32) {
+    for (int i = lane; i < m.n_static; i += stride) {
         StaticOp op = m.static_ops[i];
         double p = op.param >= 0 ? params[(int64_t)op.param * B + b] : 0.0;
         double v;
@@ -70,8 +71,9 @@ __device__ __forceinline__ void eval_static(const DevMode& m, const double* __re
     }
 }
 
-__device__ __forceinline__ void eval_step(const DevMode& m, const double* xp, double* vt, int lane) {
-    for (int i = lane; i < m.n_step; i += 32) {
+__device__ __forceinline__ void eval_step(const DevMode& m, const double* xp, double* vt, int lane,
+                                          int stride = 32) {
+    for (int i = lane; i < m.n_step; i += stride) {
         StepOp op = m.step_ops[i];
         double va = op.a >= 0 ? xp[op.a] : 0.0;
         double v;
@@ -98,9 +100,10 @@ __device__ __forceinline__ void eval_src_dc(const DevMode& m, const double* __re
 
 // SourceSpec::evalTran (include/sim.hpp:160-162) through the host-tabulated waveform
 __device__ __forceinline__ void eval_src_tran(const DevMode& m, const DevTran& T, const double* __restrict__ params,
-                                              int64_t B, int64_t b, int step, double* vt, int lane) {
+                                              int64_t B, int64_t b, int step, double* vt, int lane,
+                                              int stride = 32) {
     const double tnow = d_mul((double)(step + 1), T.dt);  // tanalisis.cpp:256
-    for (int i = lane; i < m.n_src; i += 32) {
+    for (int i = lane; i < m.n_src; i += stride) {
         SrcOp op = m.src_ops[i];
         const int s = op.index;
         const int mode = T.src_mode[s];
@@ -157,8 +160,9 @@ __device__ __forceinline__ void mos_eval(double Vth, double K, double lambda, bo
 }
 
 __device__ __forceinline__ void eval_mos(const DevMode& m, const double* __restrict__ params, int64_t B, int64_t b,
-                                         double off_gds, const double* xs, double* vt, int lane) {
-    for (int i = lane; i < m.n_mos; i += 32) {
+                                         double off_gds, const double* xs, double* vt, int lane,
+                                         int stride = 32) {
+    for (int i = lane; i < m.n_mos; i += stride) {
         MosOp op = m.mos_ops[i];
         double Vth = params[(int64_t)op.param * B + b];
         double K = params[(int64_t)(op.param + 1) * B + b];

@@ -1,0 +1,33 @@
+// spec_analysis.hpp — symbolic analysis shared by the kernel generators (internal).
+#pragma once
+#include <cstdint>
+#include <vector>
+
+#include "plan.hpp"
+
+namespace csim {
+
+struct Term {
+    int value;
+    bool sub;
+};
+
+// TRAN assembly + LU of one topology under one (predicted) pivot permutation.  "Position" i holds
+// original row perm[i]; columns keep their original numbering.
+struct Analysis {
+    int N = 0;
+    std::vector<int> pos_of_row;
+    // per (position, column): ordered contributions; column N = RHS
+    std::vector<std::vector<std::vector<Term>>> slot;       // [pos][col]
+    std::vector<std::vector<std::vector<Term>>> rest;       // terms added every Newton iteration
+    std::vector<std::vector<std::vector<Term>>> prefix;     // terms folded into the static base
+    std::vector<int> K;                                     // [N+1] generated adds per column (N = RHS)
+    std::vector<std::vector<bool>> pat;                     // structural pattern incl. fill, permuted
+    std::vector<std::vector<int>> rows_k, cols_k, ucols;    // elimination rows / pivot-row columns / U columns
+    std::vector<bool> col_used_above;
+};
+
+// Throws std::runtime_error when perm is not a permutation of 0..N-1.
+Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm);
+
+}  // namespace csim

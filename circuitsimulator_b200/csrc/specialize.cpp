@@ -1,5 +1,6 @@
 // specialize.cpp — generator of the specialised transient kernel (see specialize.hpp).
 #include "specialize.hpp"
+#include "spec_analysis.hpp"
 
 #include <algorithm>
 #include <map>
@@ -16,26 +17,6 @@ std::string spec_unsupported_reason(const HostPlan& hp) {
     if (2 * (mp.n_values + 1) > 65535) return "value table too large for 16-bit indices";
     return "";
 }
-
-namespace {
-
-struct Term {
-    int value;
-    bool sub;
-};
-
-struct Analysis {
-    int N = 0;
-    std::vector<int> pos_of_row;
-    // per (position, column): ordered contributions; column N = RHS
-    std::vector<std::vector<std::vector<Term>>> slot;       // [pos][col]
-    std::vector<std::vector<std::vector<Term>>> rest;       // terms added every Newton iteration
-    std::vector<std::vector<std::vector<Term>>> prefix;     // terms folded into the static base
-    std::vector<int> K;                                     // [N+1] generated adds per column (N = RHS)
-    std::vector<std::vector<bool>> pat;                     // structural pattern incl. fill, permuted
-    std::vector<std::vector<int>> rows_k, cols_k, ucols;    // elimination rows / pivot-row columns / U columns
-    std::vector<bool> col_used_above;
-};
 
 Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm) {
     const ModeProgram& mp = hp.mode[CSIM_MODE_TRAN];
@@ -98,8 +79,6 @@ Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm) {
             }
     return A;
 }
-
-}  // namespace
 
 namespace {
 // must match warp_mem_doubles() in newton_warp.cuh and the carve-up in the generated kernel

@@ -41,6 +41,18 @@ SpecHost generate_tran_spec(const HostPlan& hp, const std::vector<int32_t>& perm
 // Per-block dynamic shared memory of the generated kernel.
 size_t spec_smem_bytes(const HostPlan& hp, const SpecHost& sh);
 
+// ---- thread-per-instance transient kernel (specialize_tpi.cpp, tpi_runtime.cuh) -----------------
+struct TpiHost {
+    std::vector<int32_t> perm;
+    std::string source;  // entry: csim_tran_tpi
+    int32_t threads = 128, n_slots = 0, n_scratch_rows = 0;
+    size_t smem_bytes = 0;
+    uint32_t hash_lo = 0, hash_hi = 0;
+    // statistics of the generated code (per Newton iteration, per instance)
+    int32_t n_elim_updates = 0, n_lu_divs = 0, n_back_terms = 0, n_g_adds = 0, n_rhs_adds = 0;
+};
+TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm);
+
 // ---- standalone assembly kernel (specialize_stamp.cpp) ---------------------------------------
 struct StampSpecHost {
     int32_t mode = 0;

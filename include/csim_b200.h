@@ -163,11 +163,15 @@ int csim_plan_dims(const csim_plan* plan, int32_t* n_unknowns, int32_t* n_params
  * not depend on the prediction.  By default csim_dev_tran specialises on first
  * use, predicting the permutation from instance 0 at its start state.           */
 #ifndef __CUDACC_RTC__
-/* mode 0: generic kernels only; 1: specialise automatically (default; CSIM_JIT=0 in the environment = 0) */
+/* mode 0: generic kernels only; 1 (default): automatic — the thread-per-instance kernel, replaced by the
+ * warp-per-instance one when more than 2 % of the solves miss the predicted pivot order; 2: warp-per-instance
+ * kernel (csim_tran_spec: one warp per instance, rows in registers); 3: thread-per-instance kernel
+ * (csim_tran_tpi: one thread per instance, state in shared memory).  CSIM_JIT=0|2|3 in the environment
+ * overrides.  All four paths give bit-identical results.                                              */
 int csim_plan_jit_mode(csim_plan* plan, int mode);
 /* Specialise now for perm[N] (perm[i] = original row expected at pivot position i). */
 int csim_plan_specialize(csim_plan* plan, const int32_t* perm);
-/* active: 1 when a specialised kernel is loaded; perm [N] (NULL ok); counters since load:
+/* active: 0 none / 2 / 3 = kind of the specialised kernel in use; perm [N] (NULL ok); counters since load:
  * Newton solves done by the generic fallback / all Newton solves; log: generator + NVRTC messages. */
 int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, uint64_t* fallback_solves,
                         uint64_t* solves, char* log, int32_t log_cap);
@@ -175,6 +179,9 @@ int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, u
 int csim_plan_spec_source(const csim_plan* plan, char* out, int32_t cap);
 /* Host-only: source the generator emits for perm (no device needed); returns its length. */
 int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* out, int32_t cap);
+/* Same for either specialised transient kernel: kind 2 = warp per instance (csim_tran_spec),
+ * kind 3 = thread per instance (csim_tran_tpi). */
+int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_t* perm, char* out, int32_t cap);
 #endif
 
 /* The standalone assembly kernel (csim_dev_stamp_csr) is specialised the same way on first use

@@ -71,7 +71,12 @@ def test_split_division_is_bit_identical_to_ieee_division(torch):
     assert np.array_equal(qr[~nan].view(np.uint64), host[~nan].view(np.uint64))
 
 
-def test_dbmixer_specialised_equals_generic_and_oracle(torch):
+KINDS = pytest.mark.parametrize("kind", [2, 3])  # 2: warp per instance (csim_tran_spec), 3: thread per instance (csim_tran_tpi)
+ENTRY = {2: "csim_tran_spec", 3: "csim_tran_tpi"}
+
+
+@KINDS
+def test_dbmixer_specialised_equals_generic_and_oracle(torch, kind):
     from circuitsimulator_b200 import capi
     g, topo = load_golden("dbmixer")
     B, dt, ns = 12, float(g["dt"]), 600
@@ -81,15 +86,16 @@ def test_dbmixer_specialised_equals_generic_and_oracle(torch):
     a = run(capi, torch, generic, P, topo, dt, ns)
     assert not generic.spec_info()["active"]
     spec = make_plan(topo)
+    spec.jit_mode(kind)
     b = run(capi, torch, spec, P, topo, dt, ns)
     info = spec.spec_info()
-    assert info["active"], info["log"]
+    assert info["kind"] == kind, info["log"]
     same(a, b, "dbmixer specialised vs generic")
     assert info["solves"] == int(b["total"].sum()) and info["fallback_solves"] == 0, info
     assert list(info["perm"]) == [21, 1, 2, 3, 4, 5, 6, 7, 22, 9, 23, 11, 12, 13, 24, 25, 26, 27, 28, 29, 30, 0, 8, 10,
                                   14, 15, 16, 17, 18, 19, 20]  # the reference's TRAN permutation
     assert_same_bits(b["wave"][0].T[:400], g["wave_first"], "nominal vs golden")
-    assert "csim_tran_spec" in spec.spec_source()
+    assert ENTRY[kind] in spec.spec_source()
     for k in (0, 3, 7):
         od = O.dc(topo, P[k])
         m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
@@ -98,7 +104,8 @@ def test_dbmixer_specialised_equals_generic_and_oracle(torch):
         assert b["hash"][k] == np.uint64(ot["hash"])
 
 
-def test_buffer_specialised_with_pivot_misses(torch):
+@KINDS
+def test_buffer_specialised_with_pivot_misses(torch, kind):
     """buffer.sp changes its pivot order ~12 % of the time: those solves must take the generic path and the
     result must still be bit-identical (full 300 steps, every unknown)."""
     from circuitsimulator_b200 import capi
@@ -109,16 +116,18 @@ def test_buffer_specialised_with_pivot_misses(torch):
     generic.jit_mode(0)
     a = run(capi, torch, generic, P, topo, dt, ns)
     spec = make_plan(topo)
+    spec.jit_mode(kind)
     b = run(capi, torch, spec, P, topo, dt, ns)
     info = spec.spec_info()
-    assert info["active"], info["log"]
+    assert info["kind"] == kind, info["log"]
     same(a, b, "buffer specialised vs generic")
     assert 0 < info["fallback_solves"] < info["solves"], info
     assert_same_bits(b["wave"][0].T, g["wave"], "nominal buffer vs golden")
     assert b["hash"][0] == np.uint64(g["hash"])
 
 
-def test_wrong_prediction_only_costs_time(torch):
+@KINDS
+def test_wrong_prediction_only_costs_time(torch, kind):
     from circuitsimulator_b200 import capi
     g, topo = load_golden("buffer")
     B, dt, ns = 6, float(g["dt"]), 60
@@ -127,23 +136,26 @@ def test_wrong_prediction_only_costs_time(torch):
     generic.jit_mode(0)
     a = run(capi, torch, generic, P, topo, dt, ns)
     wrong = make_plan(topo)
+    wrong.jit_mode(kind)
     wrong.specialize(np.arange(topo.n_unknowns))  # identity: never what partial pivoting picks here
     b = run(capi, torch, wrong, P, topo, dt, ns)
     info = wrong.spec_info()
-    assert info["active"] and info["fallback_solves"] == info["solves"] > 0
+    assert info["kind"] == kind and info["fallback_solves"] == info["solves"] > 0
     same(a, b, "identity prediction")
 
 
-def test_degenerate_and_chunked_through_specialised_kernel(torch):
+@KINDS
+def test_degenerate_and_chunked_through_specialised_kernel(torch, kind):
     from circuitsimulator_b200 import capi
     g, topo = load_golden("buffer")
     plan = make_plan(topo)
+    plan.jit_mode(kind)
     dt, ns = float(g["dt"]), 40
     P = np.repeat(topo.params[None], 3, 0)
     e_l = [e for e in range(topo.n_elems) if topo.elem_type[e] == O.ELEM_L]
     P[1, topo.elem_param[e_l[0]]] = 0.0  # empty branch row -> singular -> zero vector
     b = run(capi, torch, plan, P, topo, dt, ns)
-    assert plan.spec_info()["active"]
+    assert plan.spec_info()["kind"] == kind
     for k in range(3):
         od = O.dc(topo, P[k])
         m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
@@ -151,3 +163,23 @@ def test_degenerate_and_chunked_through_specialised_kernel(torch):
         assert_same_bits(b["wave"][k].T, ot["wave"], f"inst {k}")
         assert int(b["status"][k]) == (od["status"] | ot["status"]) and b["hash"][k] == np.uint64(ot["hash"])
     assert int(b["status"][1]) & capi.ST_LU_SINGULAR
+
+
+def test_automatic_mode_picks_the_kernel_by_miss_rate(torch):
+    """Default mode: thread-per-instance first; buffer.sp misses the predicted pivot order far more often than
+    2 % of the solves, so the next launch moves to the warp-per-instance kernel; dbmixer.sp stays."""
+    from circuitsimulator_b200 import capi
+    for name, ns, final in (("buffer", 150, 2), ("dbmixer", 120, 3)):
+        g, topo = load_golden(name)
+        B, dt = 64, float(g["dt"])
+        P = perturb(topo.params, topo, B, 11)
+        generic = make_plan(topo)
+        generic.jit_mode(0)
+        a = run(capi, torch, generic, P, topo, dt, ns)
+        auto = make_plan(topo)
+        b1 = run(capi, torch, auto, P, topo, dt, ns)
+        assert auto.spec_info()["kind"] == 3, auto.spec_info()["log"]
+        b2 = run(capi, torch, auto, P, topo, dt, ns)
+        assert auto.spec_info()["kind"] == final, auto.spec_info()["log"]
+        same(a, b1, name + " auto first launch")
+        same(a, b2, name + " auto second launch")

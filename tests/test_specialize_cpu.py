@@ -19,15 +19,16 @@ def _perm(topo, g):
     return O.lu_solve(G, I)[1]
 
 
+@pytest.mark.parametrize("kind", [2, 3])
 @pytest.mark.parametrize("name", ["buffer", "dbmixer"])
-def test_generated_source_compiles_for_sm100a(name):
+def test_generated_source_compiles_for_sm100a(name, kind):
     from circuitsimulator_b200 import capi
     nvrtc = pytest.importorskip("cuda.bindings.nvrtc")
     g, topo = load_golden(name)
     plan = capi.Plan(topo.n_unknowns, topo.n_node_eq, topo.elem_type, topo.elem_flags, topo.elem_nodes,
                      topo.elem_branch, topo.elem_param, topo.n_params, device=-1)
-    src = plan.generate_source(_perm(topo, g))
-    assert "csim_tran_spec" in src and f"#define SPEC_N {topo.n_unknowns}" in src
+    src = plan.generate_source(_perm(topo, g), kind)
+    assert {2: "csim_tran_spec", 3: "csim_tran_tpi"}[kind] in src and f"#define SPEC_N {topo.n_unknowns}" in src
     shim = (b"#pragma once\ntypedef signed char int8_t; typedef unsigned char uint8_t; typedef short int16_t; "
             b"typedef unsigned short uint16_t;\ntypedef int int32_t; typedef unsigned int uint32_t; "
             b"typedef long long int64_t; typedef unsigned long long uint64_t;\n")

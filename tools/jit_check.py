@@ -18,14 +18,10 @@ m, grp, tab = O.make_source_tables(topo, topo.params, dt, 4)
 x = g["x_dc"]
 G, I = O.stamp(topo, 1, topo.params, x, x, O.src_tran(topo, topo.params, m, grp, tab, 0, dt), dt=dt, gmin=1e-6)
 _, perm, _ = O.lu_solve(G, I)
-L = capi.lib()
-L.csim_plan_generate_source.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_char_p, C.c_int32]
-n = L.csim_plan_generate_source(plan.handle, perm.ctypes.data_as(C.POINTER(C.c_int32)), None, 0)
-assert n > 0, L.csim_last_error()
-buf = C.create_string_buffer(n + 1)
-L.csim_plan_generate_source(plan.handle, perm.ctypes.data_as(C.POINTER(C.c_int32)), buf, n + 1)
-src = buf.value
-out = os.path.join("/tmp", f"spec_{name}.cu"); open(out, "wb").write(src)
+kind = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+src = plan.generate_source(perm, kind).encode()
+os.makedirs(os.path.join(ROOT, "build"), exist_ok=True)
+out = os.path.join(ROOT, "build", f"spec_{name}_{kind}.cu"); open(out, "wb").write(src)
 print("source:", out, len(src.splitlines()), "lines; perm", perm.tolist())
 shim = b"#pragma once\ntypedef signed char int8_t; typedef unsigned char uint8_t; typedef short int16_t; typedef unsigned short uint16_t;\ntypedef int int32_t; typedef unsigned int uint32_t; typedef long long int64_t; typedef unsigned long long uint64_t;\n"
 err, prog = nvrtc.nvrtcCreateProgram(src, b"spec.cu", 1, [shim], [b"stdint.h"])
@@ -36,8 +32,9 @@ _, ls = nvrtc.nvrtcGetProgramLogSize(prog); log = b" " * ls; nvrtc.nvrtcGetProgr
 print("nvrtc:", err, log.decode()[-1500:])
 _, cs = nvrtc.nvrtcGetCUBINSize(prog)
 if cs:
-    cub = b" " * cs; nvrtc.nvrtcGetCUBIN(prog, cub); open(f"/tmp/spec_{name}.cubin", "wb").write(cub)
-    sass = subprocess.run(["cuobjdump", "-sass", f"/tmp/spec_{name}.cubin"], capture_output=True, text=True).stdout
+    cub = b" " * cs; nvrtc.nvrtcGetCUBIN(prog, cub); open(out + "bin", "wb").write(cub)
+    sass = subprocess.run(["cuobjdump", "-sass", out + "bin"], capture_output=True, text=True).stdout
+    open(out[:-3] + ".sass", "w").write(sass)
     import re, collections
     ops = collections.Counter()
     for line in sass.splitlines():
