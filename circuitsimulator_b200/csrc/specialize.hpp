@@ -49,9 +49,13 @@ struct TpiHost {
     size_t smem_bytes = 0;
     uint32_t hash_lo = 0, hash_hi = 0;
     // statistics of the generated code (per Newton iteration, per instance)
-    int32_t n_elim_updates = 0, n_lu_divs = 0, n_back_terms = 0, n_g_adds = 0, n_rhs_adds = 0;
+    int32_t n_elim_updates = 0, n_lu_divs = 0, n_back_terms = 0, n_g_adds = 0, n_rhs_adds = 0, n_rcp = 0;
 };
-TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm);
+struct TpiOptions {
+    bool const_prop = true;  // track +-1 / gmin entries symbolically (exact rewrites only)
+    bool x_in_smem = true;   // Newton iterate in shared memory instead of registers
+};
+TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt = TpiOptions());
 
 // ---- standalone assembly kernel (specialize_stamp.cpp) ---------------------------------------
 struct StampSpecHost {

@@ -7,7 +7,15 @@
 // (include/solver.hpp:70-76), so every intermediate is bit-identical — and then parks its U part,
 // pivot, pivot reciprocal and forward-substituted right-hand side in shared memory.  Multipliers
 // are never stored (forward substitution is fused, solver.hpp:106-113).
+//
+// Constant propagation: entries whose value is the same compile-time constant for every instance
+// (the +-1 incidence entries of voltage-source and inductor branch rows, gmin) are tracked
+// symbolically through assembly and elimination.  Only IEEE-exact rewrites are applied
+// (x*1 = x, x*(-1) = -x, x/1 = x, x/(-1) = -x, x-(-y) = x+y, constant folding in host binary64,
+// which rounds like the device); sums with +0 are kept because they normalise -0.
 #include <algorithm>
+#include <cmath>
+#include <cstdio>
 #include <map>
 #include <set>
 #include <sstream>
@@ -21,24 +29,74 @@ namespace csim {
 namespace {
 
 constexpr size_t kMaxSmem = 232448;  // 227 KB dynamic shared memory per CTA on sm_100
-
-struct SlotMap {
-    int n = 0;
-    int alloc() { return n++; }
-};
+constexpr int kTpb = 32;             // one warp per CTA: the SM packs as many CTAs as shared memory allows
 
 std::string S(int slot) { return "sm[" + std::to_string(slot) + " * TPB + tid]"; }
 
+std::string lit(double v) {  // exact literal
+    if (v == 0.0) return std::signbit(v) ? "(-0.0)" : "0.0";
+    if (v == 1.0) return "1.0";
+    if (v == -1.0) return "(-1.0)";
+    char buf[64];
+    std::snprintf(buf, sizeof buf, "%a", v);
+    return std::string("(") + buf + ")";
+}
+
+// a value of the generated program: a compile-time constant or an expression (variable name,
+// shared-memory slot or nested call)
+struct Val {
+    bool c = false;
+    double v = 0.0;
+    std::string e;
+    static Val K(double x) {
+        Val r;
+        r.c = true;
+        r.v = x;
+        r.e = lit(x);
+        return r;
+    }
+    static Val E(const std::string& s) {
+        Val r;
+        r.e = s;
+        return r;
+    }
+};
+
+Val neg(const Val& a) {
+    if (a.c) return Val::K(-a.v);
+    if (a.e.size() > 3 && a.e.compare(0, 2, "(-") == 0 && a.e.back() == ')' && a.e.find('(', 1) == std::string::npos)
+        return Val::E(a.e.substr(2, a.e.size() - 3));
+    return Val::E("(-" + a.e + ")");
+}
+Val add(const Val& a, const Val& b) {
+    if (a.c && b.c) return Val::K(a.v + b.v);
+    return Val::E("d_add(" + a.e + ", " + b.e + ")");
+}
+Val sub(const Val& a, const Val& b) {
+    if (a.c && b.c) return Val::K(a.v - b.v);
+    return Val::E("d_sub(" + a.e + ", " + b.e + ")");
+}
+Val mul(const Val& a, const Val& b) {
+    if (a.c && b.c) return Val::K(a.v * b.v);
+    if (a.c && a.v == 1.0) return b;
+    if (b.c && b.v == 1.0) return a;
+    if (a.c && a.v == -1.0) return neg(b);
+    if (b.c && b.v == -1.0) return neg(a);
+    return Val::E("d_mul(" + a.e + ", " + b.e + ")");
+}
+
 }  // namespace
 
-TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm) {
+TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt) {
     const std::string why = spec_unsupported_reason(hp);
     if (!why.empty()) throw std::runtime_error("specialize: " + why);
     const ModeProgram& mp = hp.mode[CSIM_MODE_TRAN];
+    const csim_constants& C = hp.consts;
     const Analysis A = analyse(hp, perm);
     const int N = A.N;
     TpiHost H;
     H.perm = perm;
+    H.threads = kTpb;
     for (int i = 0; i < N; ++i) {  // pivot-hash contribution of the predicted permutation
         uint32_t key = (uint32_t)i * 1024u + (uint32_t)perm[i] + 1u;
         uint32_t lo = key * 0x9E3779B1u;
@@ -52,42 +110,68 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm) 
     // ---- classify values ------------------------------------------------------------------------
     enum Kind { STATIC, STEP, SRC, MOS };
     std::vector<Kind> kind(mp.n_values, STATIC);
+    std::vector<bool> is_const(mp.n_values, false);
+    std::vector<double> const_val(mp.n_values, 0.0);
+    std::vector<int> ind_params;  // inductances: L <= 0 makes SK_IND_ONE 0 -> such instances always solve generically
+    for (const StaticOp& s : mp.static_ops) {
+        if (s.kind == SK_ONE || (s.kind == SK_IND_ONE && opt.const_prop)) {
+            is_const[s.out] = true;
+            const_val[s.out] = 1.0;
+            if (s.kind == SK_IND_ONE) ind_params.push_back(s.param);
+        } else if (s.kind == SK_GMIN) {
+            is_const[s.out] = true;
+            const_val[s.out] = C.tran_gmin;
+        }
+    }
+    if (!opt.const_prop)
+        for (const StaticOp& s : mp.static_ops)
+            if (s.kind == SK_ONE) is_const[s.out] = false;  // (gmin stays a literal either way)
     for (const StepOp& s : mp.step_ops) kind[s.out] = STEP;
     for (const SrcOp& s : mp.src_ops) kind[s.out] = SRC;
     for (const MosOp& m : mp.mos_ops)
         for (int t = 0; t < 4; ++t) kind[m.out + t] = MOS;
 
-    // ---- shared-memory slots --------------------------------------------------------------------
-    SlotMap sm;
-    // Y first and contiguous: doubles as the probe scratch at output time
-    const int Y0 = sm.n;
-    for (int i = 0; i < N; ++i) sm.alloc();
-    std::vector<int> D(N), RD(N);
-    for (int i = 0; i < N; ++i) {
-        D[i] = sm.alloc();
-        RD[i] = sm.alloc();
+    // ---- shared-memory slots: Y first and contiguous (probe scratch), the rest on demand -------------
+    int n_slots = 0;
+    auto alloc = [&]() { return n_slots++; };
+    const int Y0 = n_slots;
+    n_slots += N;
+    int X0 = -1;
+    if (opt.x_in_smem) {
+        X0 = n_slots;
+        n_slots += N;
     }
-    std::map<std::pair<int, int>, int> U;
-    for (int i = 0; i < N; ++i)
-        for (int j : A.ucols[i]) U[{i, j}] = sm.alloc();
-    // static prefix sums, one slot per distinct ordered term list
+    auto xrd = [&](int k) -> std::string {
+        if (k < 0) return "0.0";
+        return opt.x_in_smem ? S(X0 + k) : "x" + std::to_string(k);
+    };
+    // static prefix sums: constant-folded, or one slot per distinct ordered term list
     std::map<std::vector<std::pair<int, bool>>, int> base_of;
-    std::vector<std::vector<int>> base_slot(N, std::vector<int>(N, -1));
+    std::vector<std::vector<Val>> base(N, std::vector<Val>(N, Val::K(0.0)));
     for (int i = 0; i < N; ++i)
         for (int j = 0; j < N; ++j) {
             if (A.prefix[i][j].empty()) continue;
+            bool all_c = true;
+            for (const Term& t : A.prefix[i][j]) all_c = all_c && is_const[t.value];
+            if (all_c) {
+                Val acc = Val::K(0.0);
+                for (const Term& t : A.prefix[i][j])
+                    acc = t.sub ? sub(acc, Val::K(const_val[t.value])) : add(acc, Val::K(const_val[t.value]));
+                base[i][j] = acc;
+                continue;
+            }
             std::vector<std::pair<int, bool>> key;
             for (const Term& t : A.prefix[i][j]) key.push_back({t.value, t.sub});
             auto it = base_of.find(key);
-            if (it == base_of.end()) it = base_of.emplace(key, sm.alloc()).first;
-            base_slot[i][j] = it->second;
+            if (it == base_of.end()) it = base_of.emplace(key, alloc()).first;
+            base[i][j] = Val::E(S(it->second));
         }
-    // non-MOS values referenced by the per-iteration terms
+    // non-MOS, non-constant values referenced by the per-iteration terms
     std::map<int, int> val_slot;
     for (int i = 0; i < N; ++i)
         for (int j = 0; j <= N; ++j)
             for (const Term& t : A.rest[i][j])
-                if (kind[t.value] != MOS && !val_slot.count(t.value)) val_slot[t.value] = sm.alloc();
+                if (kind[t.value] != MOS && !is_const[t.value] && !val_slot.count(t.value)) val_slot[t.value] = alloc();
     // static values needed again at every step (companion-model conductances) -> global scratch rows
     std::map<int, int> gs_row;
     for (const StepOp& s : mp.step_ops)
@@ -97,55 +181,33 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm) 
         }
     H.n_scratch_rows = (int)gs_row.size() + N;  // + x_prev for the generic fallback
     const int XP0 = (int)gs_row.size();
-    H.n_slots = sm.n;
-    int tpb = 128;
-    while (tpb > 32 && (size_t)sm.n * 8 * tpb > kMaxSmem) tpb -= 32;
-    if ((size_t)sm.n * 8 * tpb > kMaxSmem) throw std::runtime_error("specialize: per-instance state exceeds shared memory");
-    H.threads = tpb;
-    H.smem_bytes = (size_t)sm.n * 8 * tpb;
 
-    auto val = [&](int v) -> std::string {  // per-iteration operand
-        if (kind[v] == MOS) return "m" + std::to_string(v);
-        return S(val_slot.at(v));
+    auto val = [&](int v) -> Val {  // per-iteration operand
+        if (is_const[v]) return Val::K(const_val[v]);
+        if (kind[v] == MOS) return Val::E("m" + std::to_string(v));
+        return Val::E(S(val_slot.at(v)));
     };
 
-    std::ostringstream o;
-    o << "// generated by specialize_tpi.cpp — thread-per-instance transient kernel for one topology and one\n"
-         "// predicted pivot permutation; " << sm.n << " shared-memory doubles per instance, " << tpb << " instances per CTA.\n"
-         "#include \"tpi_runtime.cuh\"\n"
-         "using namespace csim;\n"
-         "#define TPB " << tpb << "\n"
-         "#define SPEC_N " << N << "\n"
-         "#define SPEC_NV " << mp.n_values << "\n"
-         "#define PRM(k) ld_nohoist(params + (long long)(k) * B + bb)\n"
-         "extern \"C\" __global__ void __launch_bounds__(TPB, 1)\n"
-         "csim_tran_tpi(DevPlan P, DevTran T, long long B, const double* __restrict__ params,\n"
-         "              double* __restrict__ xio, double* __restrict__ wave, int* __restrict__ iters_total,\n"
-         "              unsigned char* __restrict__ iters_step, unsigned long long* __restrict__ pivot_hash,\n"
-         "              unsigned int* __restrict__ status, double* __restrict__ scratch,\n"
-         "              unsigned long long* __restrict__ stats) {\n"
-         "    extern __shared__ double sm[];\n"
-         "    const csim_constants& c = P.c;\n"
-         "    const int tid = threadIdx.x;\n"
-         "    const long long b = (long long)blockIdx.x * TPB + tid;\n"
-         "    const bool live = b < B;\n"
-         "    const long long bb = live ? b : B - 1;  // idle lanes shadow the last instance and never store\n"
-         "    const double dt = T.dt, alpha = c.tran_alpha, tol = c.tran_tol, eps = c.lu_eps, off_gds = c.mos_off_gds;\n"
-         "    unsigned long long h = (live && pivot_hash) ? pivot_hash[b] : CSIM_PIVOT_HASH_INIT;\n"
+    std::ostringstream o;  // kernel body after the prologue (slot count is only known at the end)
+    o << "    unsigned long long h = (live && pivot_hash) ? pivot_hash[b] : CSIM_PIVOT_HASH_INIT;\n"
          "    const unsigned long long F = 0x" << std::hex << (((unsigned long long)H.hash_hi << 32) | H.hash_lo) << std::dec << "ull;\n"
+         "    const double dt = T.dt;\n"
          "    unsigned int st = 0, n_fallback = 0;\n"
          "    int total = 0;\n"
-         "    bool dead = !live;\n";
-    for (int i = 0; i < N; ++i) o << "    double x" << i << " = xio[(long long)" << i << " * B + bb];\n";
-
+         "    bool dead = !live, degen = false;\n";
+    for (int i = 0; i < N; ++i) {
+        if (opt.x_in_smem) o << "    " << S(X0 + i) << " = xio[(long long)" << i << " * B + bb];\n";
+        else o << "    double x" << i << " = xio[(long long)" << i << " * B + bb];\n";
+    }
     // ---- one-off: static values, base sums ---------------------------------------------------------
     o << "    {\n";
+    for (int p : ind_params) o << "        degen = degen || !(__ldg(params + (long long)" << p << " * B + bb) > 0.0);\n";
     for (const StaticOp& op : mp.static_ops) {
         o << "        const double v" << op.out << " = ";
         const std::string P = "__ldg(params + (long long)" + std::to_string(op.param) + " * B + bb)";
-        switch (op.kind) {
+        if (is_const[op.out]) o << lit(const_val[op.out]);
+        else switch (op.kind) {
             case SK_ONE: o << "1.0"; break;
-            case SK_GMIN: o << "c.tran_gmin"; break;
             case SK_RES: o << "res_g(" << P << ")"; break;
             case SK_CAP: o << "cap_g(" << P << ", dt)"; break;
             case SK_CAPHALF: o << "cap_half(" << P << ", dt)"; break;
@@ -170,14 +232,14 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm) 
          "        if (__all_sync(0xFFFFFFFFu, dead)) break;\n";
     // ---- per step: x_prev -> scratch, companion history terms, source values -------------------------
     for (int i = 0; i < N; ++i)
-        o << "        if (live) scratch[(long long)" << (XP0 + i) << " * B + b] = x" << i << ";\n";
-    auto xn = [](int k) { return k >= 0 ? "x" + std::to_string(k) : std::string("0.0"); };
+        o << "        if (live) scratch[(long long)" << (XP0 + i) << " * B + b] = " << xrd(i) << ";\n";
     for (const StepOp& op : mp.step_ops) {
+        if (!val_slot.count(op.out)) continue;
         const std::string g = "scratch[(long long)" + std::to_string(gs_row[op.g]) + " * B + bb]";
         std::string e;
-        if (op.kind == TK_CAP_HIST) e = "d_mul(-" + g + ", d_sub(" + xn(op.a) + ", " + xn(op.b) + "))";
-        else e = "d_mul(" + g + ", " + xn(op.a) + ")";
-        if (val_slot.count(op.out)) o << "        " << S(val_slot[op.out]) << " = " << e << ";\n";
+        if (op.kind == TK_CAP_HIST) e = "d_mul(-" + g + ", d_sub(" + xrd(op.a) + ", " + xrd(op.b) + "))";
+        else e = "d_mul(" + g + ", " + xrd(op.a) + ")";
+        o << "        " << S(val_slot[op.out]) << " = " << e << ";\n";
     }
     if (!mp.src_ops.empty()) {
         o << "        {\n            const double tnow = d_mul((double)(step + 1), dt);  // tanalisis.cpp:256\n";
@@ -190,78 +252,138 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm) 
     }
     o << "        int count = 0;\n"
          "        bool done = dead;\n"
-         "        for (int iter = 0; iter < c.tran_max_iters; ++iter) {\n"
+         "        for (int iter = 0; iter < " << C.tran_max_iters << "; ++iter) {\n"
          "            if (__all_sync(0xFFFFFFFFu, done)) break;\n"
-         "            bool bad = false, slow = false;\n";
+         "            bool bad = degen;\n"
+         "            unsigned int glo = 0xFFFFFFFFu, ghi = 0u;\n";
     // ---- MOSFET linearisation -------------------------------------------------------------------------
     for (const MosOp& op : mp.mos_ops) {
         o << "            double m" << op.out << ", m" << op.out + 1 << ", m" << op.out + 2 << ", m" << op.out + 3 << ";\n"
           << "            mos_eval(PRM(" << op.param << "), PRM(" << op.param + 1 << "), PRM(" << op.param + 2 << "), "
-          << (op.is_p ? "true" : "false") << ", off_gds, " << xn(op.d) << ", " << xn(op.g) << ", " << xn(op.s) << ", m"
-          << op.out << ", m" << op.out + 1 << ", m" << op.out + 2 << ", m" << op.out + 3 << ");\n";
+          << (op.is_p ? "true" : "false") << ", " << lit(C.mos_off_gds) << ", " << xrd(op.d) << ", " << xrd(op.g) << ", "
+          << xrd(op.s) << ", m" << op.out << ", m" << op.out + 1 << ", m" << op.out + 2 << ", m" << op.out + 3 << ");\n";
     }
     // ---- rows: assemble, eliminate, park ----------------------------------------------------------------
+    // generator-side description of the factorisation so far
+    std::vector<Val> Dv(N), RDv(N), Yv(N);
+    std::vector<std::map<int, Val>> Uv(N);
+    char num[64];
+    auto fabs_lit = [&](double v) { return lit(std::fabs(v)); };
+    // a / pivot(k): exact rewrites for +-1 pivots, constant folding, otherwise the guarded split division
+    auto divide = [&](const Val& a, int k, const std::string& tmp, const char* ind) -> Val {
+        const Val& d = Dv[k];
+        if (d.c && d.v == 1.0) return a;
+        if (d.c && d.v == -1.0) return neg(a);
+        if (a.c && d.c) return Val::K(a.v / d.v);
+        o << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo, ghi);\n";
+        H.n_lu_divs++;
+        return Val::E(tmp);
+    };
     for (int i = 0; i < N; ++i) {
         o << "            {  // position " << i << " = row " << perm[i] << "\n";
-        std::vector<int> cols;
-        for (int j = 0; j < N; ++j)
-            if (A.pat[i][j]) cols.push_back(j);
-        for (int j : cols) {
-            std::string acc = base_slot[i][j] >= 0 ? S(base_slot[i][j]) : std::string("0.0");
+        std::map<int, Val> row;
+        std::set<int> declared;
+        auto assign = [&](int j, const Val& v) {  // j == N: right-hand side
+            const std::string name = j == N ? std::string("rb") : "r" + std::to_string(j);
+            if (v.c) {
+                row[j] = v;
+                return;
+            }
+            if (v.e == name) return;
+            o << "                " << (declared.count(j) ? "" : "double ") << name << " = " << v.e << ";\n";
+            declared.insert(j);
+            row[j] = Val::E(name);
+        };
+        for (int j = 0; j <= N; ++j) {
+            if (j < N && !A.pat[i][j]) continue;
+            Val acc = j < N ? base[i][j] : Val::K(0.0);
             for (const Term& t : A.rest[i][j]) {
-                acc = std::string(t.sub ? "d_sub(" : "d_add(") + acc + ", " + val(t.value) + ")";
-                H.n_g_adds++;
+                acc = t.sub ? sub(acc, val(t.value)) : add(acc, val(t.value));
+                (j < N ? H.n_g_adds : H.n_rhs_adds)++;
             }
-            o << "                double r" << j << " = " << acc << ";\n";
-        }
-        {
-            std::string acc = "0.0";
-            for (const Term& t : A.rest[i][N]) {
-                acc = std::string(t.sub ? "d_sub(" : "d_add(") + acc + ", " + val(t.value) + ")";
-                H.n_rhs_adds++;
-            }
-            o << "                double rb = " << acc << ";\n";
+            assign(j, acc);
         }
         for (int k = 0; k < i; ++k) {
             if (!A.pat[i][k]) continue;
-            H.n_lu_divs++;
-            o << "                {\n"
-              << "                    const double pk = " << S(D[k]) << ";\n"
-              << "                    bad = bad || (fabs(r" << k << ") > fabs(pk));\n"
-              << "                    const double f = tdiv(r" << k << ", pk, " << S(RD[k]) << ", slow);\n";
+            const Val a = row[k];
+            // the reference would have picked this row instead of the predicted pivot (solver.hpp:46-56)
+            if (a.c && Dv[k].c) {
+                if (std::fabs(a.v) > std::fabs(Dv[k].v)) o << "                bad = true;\n";
+            } else {
+                o << "                bad = bad || (fabs(" << a.e << ") > " << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")")
+                  << ");\n";
+            }
+            std::snprintf(num, sizeof num, "f%d_%d", i, k);
+            const Val f = divide(a, k, num, "                ");
             for (int j : A.cols_k[k]) {
-                o << "                    r" << j << " = d_sub(r" << j << ", d_mul(f, " << S(U.at({k, j})) << "));\n";
+                assign(j, sub(row[j], mul(f, Uv[k].at(j))));
                 H.n_elim_updates++;
             }
-            o << "                    rb = d_sub(rb, d_mul(f, " << S(Y0 + k) << "));\n"
-              << "                }\n";
+            assign(N, sub(row[N], mul(f, Yv[k])));
         }
-        o << "                bad = bad || (fabs(r" << i << ") < eps);\n"
-          << "                " << S(D[i]) << " = r" << i << ";\n"
-          << "                " << S(RD[i]) << " = rcp_seq(r" << i << ");\n";
-        for (int j : A.ucols[i]) o << "                " << S(U.at({i, j})) << " = r" << j << ";\n";
-        o << "                " << S(Y0 + i) << " = rb;\n"
-          << "            }\n";
+        // pivot of this position: singular / non-finite pivots go to the generic path
+        const Val d = row[i];
+        if (d.c && (d.v == 1.0 || d.v == -1.0)) {
+            Dv[i] = d;
+        } else {
+            const int sd = alloc(), srd = alloc();
+            const std::string dn = "r" + std::to_string(i);
+            if (d.c) o << "                const double " << dn << " = " << d.e << ";\n";
+            o << "                bad = bad || !(fabs(" << dn << ") >= " << lit(C.lu_eps) << " && fabs(" << dn
+              << ") <= 0x1.fffffffffffffp+1023);\n"
+              << "                " << S(sd) << " = " << dn << ";\n"
+              << "                " << S(srd) << " = rcp_seq(" << dn << ");\n";
+            Dv[i] = Val::E(S(sd));
+            RDv[i] = Val::E(S(srd));
+            H.n_rcp++;
+        }
+        for (int j : A.ucols[i]) {
+            const Val u = row[j];
+            if (u.c) {
+                Uv[i][j] = u;
+            } else {
+                const int su = alloc();
+                o << "                " << S(su) << " = " << u.e << ";\n";
+                Uv[i][j] = Val::E(S(su));
+            }
+        }
+        if (row[N].c) {
+            Yv[i] = row[N];
+        } else {
+            o << "                " << S(Y0 + i) << " = rb;\n";
+            Yv[i] = Val::E(S(Y0 + i));
+        }
+        o << "            }\n";
     }
     // ---- back substitution (include/solver.hpp:116-128) ---------------------------------------------------
+    std::vector<Val> Q(N);
+    for (int i = 0; i < N; ++i) o << "            double q" << i << ";\n";
     for (int i = N - 1; i >= 0; --i) {
-        o << "            double q" << i << ";\n            {\n                double s = " << S(Y0 + i) << ";\n";
+        o << "            {\n";
+        Val s = Yv[i];
+        int t = 0;
         for (int j : A.ucols[i]) {
-            o << "                s = d_sub(s, d_mul(" << S(U.at({i, j})) << ", q" << j << "));\n";
+            s = sub(s, mul(Uv[i].at(j), Q[j]));
             H.n_back_terms++;
+            if (!s.c && (++t % 3) == 0) {  // keep expressions shallow
+                o << "                const double s" << t << " = " << s.e << ";\n";
+                s = Val::E("s" + std::to_string(t));
+            }
         }
-        o << "                const double dg = " << S(D[i]) << ";\n"
-          << "                q" << i << " = tdiv(s, dg, " << S(RD[i]) << ", slow);\n"
-          << "                if (fabs(dg) < 1e-15) q" << i << " = 0.0;\n"
-          << "            }\n";
+        const Val q = divide(s, i, "qq", "                ");
+        o << "                q" << i << " = " << q.e << ";\n";
+        if (!Dv[i].c) o << "                if (fabs(" << Dv[i].e << ") < 1e-15) q" << i << " = 0.0;\n";
+        o << "            }\n";
+        Q[i] = Val::E("q" + std::to_string(i));
     }
     // ---- prediction check / per-lane generic redo ------------------------------------------------------------
-    o << "            const bool redo = (bad || slow) && !done;\n"
+    o << "            const bool slow = (glo < 0x03600000u) || (ghi > 0x7FEFFFFFu);\n"
+         "            const bool redo = (bad || slow) && !done;\n"
          "            if (__any_sync(0xFFFFFFFFu, redo)) {\n"
          "                if (redo) {\n"
          "                    ++n_fallback;\n"
          "                    double xl[SPEC_N], xo[SPEC_N];\n";
-    for (int i = 0; i < N; ++i) o << "                    xl[" << i << "] = x" << i << ";\n";
+    for (int i = 0; i < N; ++i) o << "                    xl[" << i << "] = " << xrd(i) << ";\n";
     o << "                    tpi_generic_solve<SPEC_N, SPEC_NV>(P, T, params, B, bb, step, xl, scratch + (long long)" << XP0
       << " * B, xo, h, st);\n";
     for (int i = 0; i < N; ++i) o << "                    q" << i << " = xo[" << i << "];\n";
@@ -280,11 +402,17 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm) 
          "                }\n"
          "            }\n"
          "            const bool upd = !done;\n";
-    for (int i = 0; i < N; ++i)
-        o << "            const double n" << i << " = d_add(x" << i << ", d_mul(alpha, d_sub(q" << i << ", x" << i << ")));\n"
-          << "            double e" << i << " = d_sub(n" << i << ", x" << i << ");\n"
-          << "            e" << i << " = d_mul(e" << i << ", e" << i << ");\n"
-          << "            x" << i << " = upd ? n" << i << " : x" << i << ";\n";
+    for (int i = 0; i < N; ++i) {
+        const std::string xi = xrd(i), I = std::to_string(i);
+        if (opt.x_in_smem) o << "            const double xo" << I << " = " << xi << ";\n";
+        const std::string xv = opt.x_in_smem ? "xo" + I : xi;
+        o << "            const double n" << I << " = d_add(" << xv << ", d_mul(" << lit(C.tran_alpha) << ", d_sub(q" << I << ", "
+          << xv << ")));\n"
+          << "            double e" << I << " = d_sub(n" << I << ", " << xv << ");\n"
+          << "            e" << I << " = d_mul(e" << I << ", e" << I << ");\n";
+        if (opt.x_in_smem) o << "            if (upd) " << xi << " = n" << I << ";\n";
+        else o << "            x" << I << " = upd ? n" << I << " : x" << I << ";\n";
+    }
     // 32-leaf pairwise tree (oracle/csim_norm2.h); leaves >= N are +0 and adding +0 to a square is exact
     {
         std::vector<std::string> leaf(32);
@@ -298,23 +426,25 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm) 
         o << "            const double err = sqrt(" << leaf[0] << ");\n";
     }
     o << "            if (upd) {\n"
-         "                if (err < tol) done = true;\n"
-         "                else if (iter == c.tran_max_iters - 1) st |= CSIM_ST_TRAN_UNCONVERGED;\n"
+         "                if (err < " << lit(C.tran_tol) << ") done = true;\n"
+         "                else if (iter == " << C.tran_max_iters - 1 << ") st |= CSIM_ST_TRAN_UNCONVERGED;\n"
          "            }\n"
          "        }\n"
          "        total += count;\n"
          "        if (iters_step && live && count > 0) iters_step[(long long)step * B + b] = (unsigned char)count;\n"
          "        if ((step + 1) % T.out_stride == 0 && step >= T.out_begin_step && T.n_probes > 0) {\n";
-    for (int i = 0; i < N; ++i) o << "            " << S(Y0 + i) << " = x" << i << ";\n";
+    const int PB = opt.x_in_smem ? X0 : Y0;  // where the probes are read from
+    if (!opt.x_in_smem)
+        for (int i = 0; i < N; ++i) o << "            " << S(Y0 + i) << " = x" << i << ";\n";
     o << "            if (live && !dead) {\n"
          "                const long long r = (step + 1) / T.out_stride - 1 - r0;\n"
          "                for (int p = 0; p < T.n_probes; ++p)\n"
-         "                    wave[((long long)b * T.n_probes + p) * T.wave_ld + r] = sm[(" << Y0 << " + T.probes[p]) * TPB + tid];\n"
+         "                    wave[((long long)b * T.n_probes + p) * T.wave_ld + r] = sm[(" << PB << " + T.probes[p]) * TPB + tid];\n"
          "            }\n"
          "        }\n"
          "    }\n"
          "    if (live) {\n";
-    for (int i = 0; i < N; ++i) o << "        xio[(long long)" << i << " * B + b] = x" << i << ";\n";
+    for (int i = 0; i < N; ++i) o << "        xio[(long long)" << i << " * B + b] = " << xrd(i) << ";\n";
     o << "        if (iters_total) iters_total[b] += total;\n"
          "        if (pivot_hash) pivot_hash[b] = h;\n"
          "        if (status) status[b] |= st;\n"
@@ -324,7 +454,33 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm) 
          "        }\n"
          "    }\n"
          "}\n";
-    H.source = o.str();
+
+    H.n_slots = n_slots;
+    H.smem_bytes = (size_t)n_slots * 8 * kTpb;
+    if (H.smem_bytes > kMaxSmem) throw std::runtime_error("specialize: per-instance state exceeds shared memory");
+    std::ostringstream pro;
+    pro << "// generated by specialize_tpi.cpp — thread-per-instance transient kernel for one topology and one\n"
+           "// predicted pivot permutation; " << n_slots << " shared-memory doubles per instance, " << kTpb
+        << " instances per CTA.\n"
+           "#include \"tpi_runtime.cuh\"\n"
+           "using namespace csim;\n"
+           "#define TPB " << kTpb << "\n"
+           "#define SPEC_N " << N << "\n"
+           "#define SPEC_NV " << mp.n_values << "\n"
+           "#define PRM(k) ld_nohoist(params + (long long)(k) * B + bb)\n"
+           "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kMaxSmem / (H.smem_bytes + 1024)))
+        << ")\n"
+           "csim_tran_tpi(DevPlan P, DevTran T, long long B, const double* __restrict__ params,\n"
+           "              double* __restrict__ xio, double* __restrict__ wave, int* __restrict__ iters_total,\n"
+           "              unsigned char* __restrict__ iters_step, unsigned long long* __restrict__ pivot_hash,\n"
+           "              unsigned int* __restrict__ status, double* __restrict__ scratch,\n"
+           "              unsigned long long* __restrict__ stats) {\n"
+           "    extern __shared__ double sm[];\n"
+           "    const int tid = threadIdx.x;\n"
+           "    const long long b = (long long)blockIdx.x * TPB + tid;\n"
+           "    const bool live = b < B;\n"
+           "    const long long bb = live ? b : B - 1;  // idle lanes shadow the last instance and never store\n";
+    H.source = pro.str() + o.str();
     return H;
 }
 
