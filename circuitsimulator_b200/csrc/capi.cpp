@@ -184,7 +184,16 @@ int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     tp.d_stats = nullptr;
     jit_unload(tp.k);
     try {
-        tp.host = generate_tran_tpi(plan->host, perm);
+        TpiOptions opt;
+        if (const char* env = std::getenv("CSIM_TPI_OPTS")) {  // development aid: bit mask of TpiOptions
+            const int m = std::atoi(env);
+            opt.const_prop = m & 1;
+            opt.x_in_smem = m & 2;
+            opt.mos_in_smem = m & 4;
+            opt.q_in_smem = m & 8;
+            opt.mos_branchless = m & 16;
+        }
+        tp.host = generate_tran_tpi(plan->host, perm, opt);
     } catch (const std::exception& e) {
         tp.log = e.what();
         return fail(CSIM_E_UNSUPPORTED, tp.log);

@@ -54,6 +54,9 @@ struct TpiHost {
 struct TpiOptions {
     bool const_prop = true;  // track +-1 / gmin entries symbolically (exact rewrites only)
     bool x_in_smem = true;   // Newton iterate in shared memory instead of registers
+    bool mos_in_smem = false;    // MOSFET parameters and linearisation values parked in shared memory
+    bool q_in_smem = false;      // raw solution parked in the (dead) Y slots
+    bool mos_branchless = false; // evaluate both MOSFET regions and select (measured slower on dbmixer)
 };
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt = TpiOptions());
 

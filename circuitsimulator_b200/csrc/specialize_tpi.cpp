@@ -182,9 +182,18 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     H.n_scratch_rows = (int)gs_row.size() + N;  // + x_prev for the generic fallback
     const int XP0 = (int)gs_row.size();
 
+    std::map<int, int> mos_slot;
+    if (opt.mos_in_smem)
+        for (const MosOp& m : mp.mos_ops)
+            for (int t = 0; t < 4; ++t) mos_slot[m.out + t] = alloc();
+    std::map<int, int> prm_slot;  // MOSFET parameters (Vth, K, lambda), loaded once
+    if (opt.mos_in_smem)
+        for (const MosOp& m : mp.mos_ops)
+            for (int t = 0; t < 3; ++t)
+                if (!prm_slot.count(m.param + t)) prm_slot[m.param + t] = alloc();
     auto val = [&](int v) -> Val {  // per-iteration operand
         if (is_const[v]) return Val::K(const_val[v]);
-        if (kind[v] == MOS) return Val::E("m" + std::to_string(v));
+        if (kind[v] == MOS) return opt.mos_in_smem ? Val::E(S(mos_slot.at(v))) : Val::E("m" + std::to_string(v));
         return Val::E(S(val_slot.at(v)));
     };
 
@@ -200,6 +209,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         else o << "    double x" << i << " = xio[(long long)" << i << " * B + bb];\n";
     }
     // ---- one-off: static values, base sums ---------------------------------------------------------
+    for (const auto& kv : prm_slot)
+        o << "    " << S(kv.second) << " = __ldg(params + (long long)" << kv.first << " * B + bb);\n";
     o << "    {\n";
     for (int p : ind_params) o << "        degen = degen || !(__ldg(params + (long long)" << p << " * B + bb) > 0.0);\n";
     for (const StaticOp& op : mp.static_ops) {
@@ -258,10 +269,14 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
          "            unsigned int glo = 0xFFFFFFFFu, ghi = 0u;\n";
     // ---- MOSFET linearisation -------------------------------------------------------------------------
     for (const MosOp& op : mp.mos_ops) {
+        auto prm = [&](int k) { return opt.mos_in_smem ? S(prm_slot.at(k)) : "PRM(" + std::to_string(k) + ")"; };
         o << "            double m" << op.out << ", m" << op.out + 1 << ", m" << op.out + 2 << ", m" << op.out + 3 << ";\n"
-          << "            mos_eval(PRM(" << op.param << "), PRM(" << op.param + 1 << "), PRM(" << op.param + 2 << "), "
-          << (op.is_p ? "true" : "false") << ", " << lit(C.mos_off_gds) << ", " << xrd(op.d) << ", " << xrd(op.g) << ", "
-          << xrd(op.s) << ", m" << op.out << ", m" << op.out + 1 << ", m" << op.out + 2 << ", m" << op.out + 3 << ");\n";
+          << "            " << (opt.mos_branchless ? "mos_eval_sel" : "mos_eval_pp") << "<" << (op.is_p ? -1 : 1) << ">("
+          << prm(op.param) << ", " << prm(op.param + 1) << ", " << prm(op.param + 2) << ", " << lit(C.mos_off_gds) << ", "
+          << xrd(op.d) << ", " << xrd(op.g) << ", " << xrd(op.s) << ", m" << op.out << ", m" << op.out + 1 << ", m"
+          << op.out + 2 << ", m" << op.out + 3 << ");\n";
+        if (opt.mos_in_smem)
+            for (int t = 0; t < 4; ++t) o << "            " << S(mos_slot[op.out + t]) << " = m" << op.out + t << ";\n";
     }
     // ---- rows: assemble, eliminate, park ----------------------------------------------------------------
     // generator-side description of the factorisation so far
@@ -357,9 +372,11 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     }
     // ---- back substitution (include/solver.hpp:116-128) ---------------------------------------------------
     std::vector<Val> Q(N);
-    for (int i = 0; i < N; ++i) o << "            double q" << i << ";\n";
+    if (!opt.q_in_smem)
+        for (int i = 0; i < N; ++i) o << "            double q" << i << ";\n";
     for (int i = N - 1; i >= 0; --i) {
         o << "            {\n";
+        if (opt.q_in_smem) o << "                double q" << i << ";\n";
         Val s = Yv[i];
         int t = 0;
         for (int j : A.ucols[i]) {
@@ -373,8 +390,9 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         const Val q = divide(s, i, "qq", "                ");
         o << "                q" << i << " = " << q.e << ";\n";
         if (!Dv[i].c) o << "                if (fabs(" << Dv[i].e << ") < 1e-15) q" << i << " = 0.0;\n";
+        if (opt.q_in_smem) o << "                " << S(Y0 + i) << " = q" << i << ";\n";
         o << "            }\n";
-        Q[i] = Val::E("q" + std::to_string(i));
+        Q[i] = opt.q_in_smem ? Val::E(S(Y0 + i)) : Val::E("q" + std::to_string(i));
     }
     // ---- prediction check / per-lane generic redo ------------------------------------------------------------
     o << "            const bool slow = (glo < 0x03600000u) || (ghi > 0x7FEFFFFFu);\n"
@@ -386,12 +404,15 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     for (int i = 0; i < N; ++i) o << "                    xl[" << i << "] = " << xrd(i) << ";\n";
     o << "                    tpi_generic_solve<SPEC_N, SPEC_NV>(P, T, params, B, bb, step, xl, scratch + (long long)" << XP0
       << " * B, xo, h, st);\n";
-    for (int i = 0; i < N; ++i) o << "                    q" << i << " = xo[" << i << "];\n";
+    for (int i = 0; i < N; ++i)
+        o << "                    " << (opt.q_in_smem ? S(Y0 + i) : "q" + std::to_string(i)) << " = xo[" << i << "];\n";
     o << "                }\n"
          "            }\n"
          "            if (!redo && !done) h = (h ^ F) * 0x100000001B3ull;\n";
     // ---- damping, norm, convergence (src/tanalisis.cpp:359-376) -----------------------------------------------
     o << "            bool fin = true;\n";
+    if (opt.q_in_smem)
+        for (int i = 0; i < N; ++i) o << "            const double q" << i << " = " << S(Y0 + i) << ";\n";
     for (int i = 0; i < N; ++i) o << "            fin = fin && finite_d(q" << i << ");\n";
     o << "            if (!done) {\n"
          "                ++count;\n"
