@@ -200,7 +200,7 @@ def symbolic_flops(nl, plan, capi, torch):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from circuitsimulator_b200 import capi
+    from circuitsimulator_b200 import capi, shard
     from circuitsimulator_b200.netlist import Netlist
 
     rank = int(os.environ.get("RANK", "0"))
@@ -221,7 +221,7 @@ def run_ours(args):
     N, P = nl.n_unknowns, nl.n_params
     probes = nl.plot_probes if len(nl.plot_probes) else np.arange(min(2, N), dtype=np.int32)
     setup = nl.tran_setup(probes=probes, out_stride=args.out_stride, n_steps=n_steps)
-    params_host = torch.from_numpy(nl.monte_carlo(B, SEED, first=rank * B)).pin_memory()
+    params_host = torch.from_numpy(shard.shard_params(nl, world * B, rank, world, SEED)).pin_memory()
     params = params_host.to(dev)
 
     wave = torch.empty((B, len(probes), max(setup.n_out, 1)), dtype=torch.float64, device=dev)
@@ -305,12 +305,14 @@ def run_ours(args):
         barrier()
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         dec = wave[:, :, :: max(1, wave.shape[2] // 5000)].contiguous()  # decimated to <= 5000 points for the gather
-        lst = [torch.empty_like(dec) for _ in range(world)] if rank == 0 else None
         g0.record()
-        dist.gather(dec, lst, dst=0)
+        allw = shard.gather_instances(dec, dst=0, dim=0)
+        alli = shard.gather_instances(out["iters_total"], dst=0)
         g1.record()
         torch.cuda.synchronize()
         gather_ms = g0.elapsed_time(g1)
+        if rank == 0:
+            assert allw.shape[0] == world * B and alli.shape[0] == world * B
 
     if rank != 0:
         if world > 1:
