@@ -34,6 +34,7 @@ EXPORTS = [
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
+    "csim_dev_sstate",
 ]
 
 
@@ -60,6 +61,10 @@ class TopologyC(C.Structure):
         ("elem_nodes", C.POINTER(C.c_int32)), ("elem_branch", C.POINTER(C.c_int32)),
         ("elem_param", C.POINTER(C.c_int32)),
     ]
+
+
+class SstateArgsC(C.Structure):
+    _fields_ = [("steps_per_period", C.c_int32), ("max_periods", C.c_int32), ("tol", C.c_double)]
 
 
 class TranArgsC(C.Structure):
@@ -98,6 +103,8 @@ def lib():
         L.csim_dev_lu_solve.argtypes = [C.c_int32, C.c_int64] + [C.c_void_p] * 5 + [C.c_double, C.c_void_p]
         L.csim_dev_dc.argtypes = [C.c_void_p, C.c_int64] + [C.c_void_p] * 6
         L.csim_dev_tran.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(TranArgsC)] + [C.c_void_p] * 7
+        L.csim_dev_sstate.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(TranArgsC), C.POINTER(SstateArgsC)] + \
+            [C.c_void_p] * 7
         L.csim_plan_jit_mode.argtypes = [C.c_void_p, C.c_int]
         L.csim_plan_specialize.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
         L.csim_plan_spec_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_uint64),
@@ -364,6 +371,31 @@ def tran(plan: Plan, params, x, setup: TranSetup, step_begin=0, step_end=None, w
     _check(lib().csim_dev_tran(plan.handle, B, _ptr(params), C.byref(a), _ptr(x), _ptr(wave), _ptr(iters_total),
                                _ptr(iters_step), _ptr(pivot_hash), _ptr(status), _stream()), "csim_dev_tran")
     return dict(x=x, wave=wave, iters_total=iters_total, iters_step=iters_step, hash=pivot_hash, status=status)
+
+
+def sstate(plan: Plan, params, x, setup: TranSetup, steps_per_period: int, max_periods: int, tol: float,
+           pivot_hash=None, status=None, iters_total=None):
+    """csim_dev_sstate: periodic steady state by period-to-period integration (definition: csim_b200.h).
+    x [N,B] is updated in place; setup.table must cover max_periods*steps_per_period steps."""
+    torch = _torch()
+    B = params.shape[1]
+    _dev_f64(params, (plan.n_params, B))
+    _dev_f64(x, (plan.n_unknowns, B))
+    dev = params.device
+    if pivot_hash is None:
+        pivot_hash, status = new_diag(B, dev)
+    if iters_total is None:
+        iters_total = torch.zeros((B,), dtype=torch.int32, device=dev)
+    periods = torch.empty((B,), dtype=torch.int32, device=dev)
+    delta = torch.empty((B,), dtype=torch.float64, device=dev)
+    table = setup.device_table(dev)
+    gb = setup.src_group_b
+    a = setup.args(0, 0, table.data_ptr(), gb.data_ptr() if gb is not None else None, 0)
+    ss = SstateArgsC(int(steps_per_period), int(max_periods), float(tol))
+    _check(lib().csim_dev_sstate(plan.handle, B, _ptr(params), C.byref(a), C.byref(ss), _ptr(x), _ptr(periods),
+                                 _ptr(delta), _ptr(iters_total), _ptr(pivot_hash), _ptr(status), _stream()),
+           "csim_dev_sstate")
+    return dict(x=x, periods=periods, delta=delta, iters_total=iters_total, hash=pivot_hash, status=status)
 
 
 class Batch:

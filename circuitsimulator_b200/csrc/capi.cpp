@@ -22,6 +22,7 @@ using namespace csim;
 
 namespace {
 thread_local std::string g_err;
+thread_local const uint8_t* g_tran_skip = nullptr;  // per-instance skip mask of the steady-state driver
 thread_local bool g_generic_stamp_only = false;  // set while the pivot pilot runs (it holds the plan's JIT lock)
 int fail(int code, const std::string& msg) {
     g_err = msg;
@@ -629,6 +630,7 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
     T.src_group = d_pack + ns;
     T.src_group_b = a->src_group_b;
     T.probes = d_pack + 2 * ns;
+    T.skip = g_tran_skip;
     cudaError_t e;
     const int kind = spec_prepare(plan, B, params, x, a->dt, stream);
     if (kind == 3) {
@@ -640,6 +642,70 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
     }
     cudaFreeAsync(d_pack, stream);
     if (e != cudaSuccess) return cuda_fail(e, "tran_kernel launch");
+    return CSIM_OK;
+}
+
+int csim_dev_sstate(const csim_plan* plan, int64_t B, const double* params, const csim_tran_args* tran,
+                    const csim_sstate_args* ss, double* x, int32_t* periods, double* delta, int32_t* iters_total,
+                    uint64_t* pivot_hash, uint32_t* status, void* stream_v) {
+    int rc = need_device(plan, "csim_dev_sstate");
+    if (rc) return rc;
+    if (B <= 0 || !params || !tran || !ss || !x || !periods || !delta)
+        return fail(CSIM_E_INVALID, "csim_dev_sstate: null argument");
+    if (ss->steps_per_period <= 0 || ss->max_periods <= 0 || !(ss->tol > 0.0))
+        return fail(CSIM_E_INVALID, "csim_dev_sstate: steps_per_period, max_periods and tol must be positive");
+    if ((int64_t)ss->steps_per_period * ss->max_periods > 2147483647LL)
+        return fail(CSIM_E_INVALID, "csim_dev_sstate: step index overflows int32");
+    cudaStream_t stream = (cudaStream_t)stream_v;
+    const int N = plan->host.N;
+    double* x_prev = nullptr;
+    uint8_t* skip = nullptr;
+    unsigned long long* n_open = nullptr;
+    auto cleanup = [&]() {
+        cudaFreeAsync(x_prev, stream);
+        cudaFreeAsync(skip, stream);
+        cudaFreeAsync(n_open, stream);
+    };
+#define CUS(call)                                  \
+    do {                                           \
+        cudaError_t e__ = (call);                  \
+        if (e__ != cudaSuccess) {                  \
+            cleanup();                             \
+            return cuda_fail(e__, #call);          \
+        }                                          \
+    } while (0)
+    CUS(cudaMallocAsync((void**)&x_prev, sizeof(double) * (size_t)N * B, stream));
+    CUS(cudaMallocAsync((void**)&skip, (size_t)B, stream));
+    CUS(cudaMallocAsync((void**)&n_open, sizeof(unsigned long long), stream));
+    CUS(cudaMemsetAsync(skip, 0, (size_t)B, stream));
+    CUS(cudaMemsetAsync(periods, 0xFF, sizeof(int32_t) * (size_t)B, stream));  // -1
+    CUS(cudaMemsetAsync(delta, 0, sizeof(double) * (size_t)B, stream));
+    csim_tran_args a = *tran;
+    a.n_probes = 0;
+    a.probes = nullptr;
+    a.out_stride = 1;
+    a.out_begin_step = 0;
+    a.wave_ld = 0;
+    for (int k = 1; k <= ss->max_periods; ++k) {
+        CUS(cudaMemcpyAsync(x_prev, x, sizeof(double) * (size_t)N * B, cudaMemcpyDeviceToDevice, stream));
+        a.step_begin = (k - 1) * ss->steps_per_period;
+        a.step_end = k * ss->steps_per_period;
+        g_tran_skip = skip;
+        rc = csim_dev_tran(plan, B, params, &a, x, nullptr, iters_total, nullptr, pivot_hash, status, stream);
+        g_tran_skip = nullptr;
+        if (rc) {
+            cleanup();
+            return rc;
+        }
+        CUS(cudaMemsetAsync(n_open, 0, sizeof(unsigned long long), stream));
+        CUS(launch_sstate_check(N, B, x, x_prev, ss->tol, k, skip, periods, delta, n_open, stream));
+        unsigned long long open = 0;
+        CUS(cudaMemcpyAsync(&open, n_open, sizeof(open), cudaMemcpyDeviceToHost, stream));
+        CUS(cudaStreamSynchronize(stream));
+        if (open == 0) break;
+    }
+    cleanup();
+#undef CUS
     return CSIM_OK;
 }
 

@@ -262,7 +262,7 @@ tran_kernel(DevPlan P, DevTran T, int64_t B, const double* __restrict__ params, 
     uint32_t* progbuf = reinterpret_cast<uint32_t*>(smem + wd * kWarpsPerBlock);
     const uint32_t* prog = load_prog(m, progbuf);
     const int64_t b = (int64_t)blockIdx.x * kWarpsPerBlock + wib;
-    if (b >= B) return;
+    if (b >= B || (T.skip && T.skip[b])) return;
     WarpMem w = carve(smem + wd * wib, m.n_values);
 
     uint64_t h = pivot_hash ? pivot_hash[b] : CSIM_PIVOT_HASH_INIT;
@@ -320,6 +320,44 @@ tran_kernel(DevPlan P, DevTran T, int64_t B, const double* __restrict__ params, 
         if (pivot_hash) pivot_hash[b] = h;
         if (status) status[b] |= st;
     }
+}
+
+// =============================================================================
+// steady-state driver: periodicity check after every period (definition: include/csim_b200.h)
+// =============================================================================
+// Thread per instance.  delta = || x - x_prev ||_2 in the summation order of oracle/csim_norm2.h.
+__global__ void sstate_check_kernel(int N, int64_t B, const double* __restrict__ x, const double* __restrict__ x_prev,
+                                    double tol, int period, uint8_t* __restrict__ skip, int32_t* __restrict__ periods,
+                                    double* __restrict__ delta, unsigned long long* __restrict__ n_open) {
+    const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B || skip[b]) return;
+    double acc[32];
+#pragma unroll
+    for (int l = 0; l < 32; ++l) acc[l] = 0.0;
+    for (int i = 0; i < N; ++i) {
+        const double d = d_sub(x[(int64_t)i * B + b], x_prev[(int64_t)i * B + b]);
+        acc[i & 31] = d_add(acc[i & 31], d_mul(d, d));
+    }
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1)
+#pragma unroll
+        for (int i = 0; i < s; ++i) acc[i] = d_add(acc[i], acc[i + s]);
+    const double nrm = sqrt(acc[0]);
+    delta[b] = nrm;
+    if (nrm < tol) {
+        periods[b] = period;
+        skip[b] = 1;
+    } else {
+        atomicAdd(n_open, 1ull);
+    }
+}
+
+cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double* x_prev, double tol, int period,
+                                uint8_t* skip, int32_t* periods, double* delta, unsigned long long* n_open,
+                                cudaStream_t stream) {
+    sstate_check_kernel<<<(unsigned)((B + 127) / 128), 128, 0, stream>>>(N, B, x, x_prev, tol, period, skip, periods,
+                                                                         delta, n_open);
+    return cudaGetLastError();
 }
 
 // =============================================================================

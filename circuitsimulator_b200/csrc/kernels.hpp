@@ -22,6 +22,10 @@ cudaError_t launch_tran(const DevPlan& P, const DevTran& T, int64_t B, const dou
                         int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status,
                         cudaStream_t stream);
 
+cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double* x_prev, double tol, int period,
+                                uint8_t* skip, int32_t* periods, double* delta, unsigned long long* n_open,
+                                cudaStream_t stream);
+
 cudaError_t launch_div_selftest(int64_t n, const double* a, const double* b, double* q_split, double* q_ref,
                                 cudaStream_t stream);
 

@@ -181,7 +181,7 @@ SpecHost generate_tran_spec(const HostPlan& hp, const std::vector<int32_t>& perm
          "    __syncthreads();\n"
          "    const uint32_t* prog = progbuf;\n"
          "    const long long b = (long long)blockIdx.x * SPEC_WARPS + wib;\n"
-         "    if (b >= B) return;\n"
+         "    if (b >= B || (T.skip && T.skip[b])) return;\n"
          "    WarpMem w = carve(smem + wd * wib, m.n_values);\n"
          "    double* vv = smem + wd * wib + wdg;\n"
          "    double* base = w.S;  // the generic matrix area doubles as the static-part table\n"

@@ -499,8 +499,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
            "    extern __shared__ double sm[];\n"
            "    const int tid = threadIdx.x;\n"
            "    const long long b = (long long)blockIdx.x * TPB + tid;\n"
-           "    const bool live = b < B;\n"
-           "    const long long bb = live ? b : B - 1;  // idle lanes shadow the last instance and never store\n";
+           "    const bool live = b < B && !(T.skip && T.skip[b < B ? b : B - 1]);\n"
+           "    const long long bb = b < B ? b : B - 1;  // idle lanes shadow an instance and never store\n";
     H.source = pro.str() + o.str();
     return H;
 }

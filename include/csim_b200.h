@@ -273,6 +273,33 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
                   uint32_t* status, void* stream);
 #endif
 
+/* ---- periodic steady state ----------------------------------------------------------------- *
+ * The reference names a steady-state driver (src/sstateanalysis.cpp) but the file is EMPTY and the
+ * `.hb f0 nHarm` card (src/parser.cpp:551-572, include/sim.hpp:187-191) is parsed and never read,
+ * so there is no reference behaviour to match ("parity unpinned").  DEFINITION used here, built
+ * only from the reference's own transient step: with T = 1/f0 and steps_per_period = round(T/dt),
+ * integrate period after period with runTransientAnalysisBackwardEuler's step loop
+ * (src/tanalisis.cpp:255-420) from the given start state; after period k (k = 1, 2, ...) form
+ * delta_k = || x(kT) - x((k-1)T) ||_2 over all unknowns (summation order: oracle/csim_norm2.h);
+ * the instance has reached its periodic steady state at the first k with delta_k < tol and is
+ * frozen there (state, iteration counters, pivot hash, status).  Instances that never get there
+ * stop after max_periods with periods[b] = -1.  Step s of the run is t = (s+1)*dt counted from
+ * the start state, so the source table must cover max_periods * steps_per_period steps.        */
+typedef struct csim_sstate_args {
+    int32_t steps_per_period;
+    int32_t max_periods;
+    double tol;
+} csim_sstate_args;
+/* tran: dt and source tables as for csim_dev_tran (step range, probes and output fields ignored).
+ * x [N][B] in: start state (normally the DC operating point), out: state at convergence (or after
+ * max_periods); periods [B] out; delta [B] out: last delta_k of each instance; iters_total,
+ * pivot_hash, status as for csim_dev_tran.  Synchronises the stream once per period.           */
+#ifndef __CUDACC_RTC__
+int csim_dev_sstate(const csim_plan* plan, int64_t B, const double* params, const csim_tran_args* tran,
+                    const csim_sstate_args* ss, double* x, int32_t* periods, double* delta, int32_t* iters_total,
+                    uint64_t* pivot_hash, uint32_t* status, void* stream);
+#endif
+
 /* ======================= host-pointer entry points ======================== */
 #ifndef __CUDACC_RTC__
 int csim_batch_create(const csim_plan* plan, int64_t B, csim_batch** out);

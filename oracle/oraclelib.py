@@ -301,6 +301,23 @@ def tran(topo: Topology, params, dt, step_begin, step_end, src_mode, src_group, 
                 trace=_trace_out(t, bufs))
 
 
+def sstate(topo: Topology, params, dt, steps_per_period, max_periods, tol, src_mode, src_group, table, x0,
+           consts=None, pivot_hash=PIVOT_HASH_INIT):
+    """Periodic steady state, CPU restatement of the DEFINITION in include/csim_b200.h (the reference's
+    src/sstateanalysis.cpp is empty: parity against the reference is unpinned; this composes the pinned
+    transient oracle).  Returns dict(x, period (-1: not reached), delta, total, hash, status)."""
+    x = np.array(x0, np.float64, copy=True)
+    h, st, total, d = pivot_hash, 0, 0, 0.0
+    for k in range(1, max_periods + 1):
+        r = tran(topo, params, dt, (k - 1) * steps_per_period, k * steps_per_period, src_mode, src_group, table, x,
+                 consts=consts, want_wave=False, pivot_hash=h)
+        d = norm2(r["x"] - x)
+        x, h, st, total = r["x"], r["hash"], st | r["status"], total + r["total"]
+        if d < tol:
+            return dict(x=x, period=k, delta=d, total=total, hash=h, status=st)
+    return dict(x=x, period=-1, delta=d, total=total, hash=h, status=st)
+
+
 # -------------------------------------------------------------- reference API
 
 class Ref:

@@ -1,0 +1,71 @@
+"""GPU: periodic steady state (csim_dev_sstate) against the CPU restatement of the same definition.
+The reference's src/sstateanalysis.cpp is empty — parity with the reference is unpinned by construction;
+what is checked is that the device driver composes the (pinned) transient step exactly as defined in
+include/csim_b200.h: same period of convergence per instance, same frozen state bit for bit, same
+Newton totals and pivot hashes."""
+import numpy as np
+import pytest
+
+from oracle import oraclelib as O
+from support import assert_same_bits, load_golden, make_plan, perturb
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    assert torch.cuda.is_available()
+    return torch
+
+
+def dev(torch, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+@pytest.mark.parametrize("jit", [1, 0])
+def test_buffer_steady_state_matches_definition(torch, jit):
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    dt, spp, K, tol = float(g["dt"]), 100, 5, 2e-8  # Vin is a 10 MHz sine: T = 100 steps of 1 ns
+    B = 9
+    P = perturb(topo.params, topo, B, 77)
+    plan = make_plan(topo)
+    plan.jit_mode(jit)
+    params = dev(torch, P.T)
+    d = capi.dc(plan, params)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, spp * K)
+    setup = capi.TranSetup(dt, spp * K, m, grp, tab, probes=np.zeros(0, np.int32))
+    r = capi.sstate(plan, params, d["x"].clone(), setup, spp, K, tol, pivot_hash=d["hash"].clone(),
+                    status=d["status"].clone())
+    torch.cuda.synchronize()
+    periods = r["periods"].cpu().numpy()
+    assert set(periods.tolist()) == {2, 3}, periods  # the tolerance splits the batch: frozen instances must stay frozen
+    for b in range(B):
+        od = O.dc(topo, P[b])
+        o = O.sstate(topo, P[b], dt, spp, K, tol, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert periods[b] == o["period"]
+        assert_same_bits(r["x"][:, b].cpu().numpy(), o["x"], f"inst {b} state")
+        assert_same_bits(r["delta"][b].cpu().numpy(), np.float64(o["delta"]), f"inst {b} delta")
+        assert int(r["iters_total"][b]) == o["total"]
+        assert np.uint64(r["hash"][b].item() & 0xFFFFFFFFFFFFFFFF) == np.uint64(o["hash"])
+        assert int(r["status"][b]) == (od["status"] | o["status"])
+
+
+def test_steady_state_gives_up_after_max_periods(torch):
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    dt, spp, K = float(g["dt"]), 100, 2
+    P = perturb(topo.params, topo, 3, 5)
+    plan = make_plan(topo)
+    params = dev(torch, P.T)
+    d = capi.dc(plan, params)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, spp * K)
+    setup = capi.TranSetup(dt, spp * K, m, grp, tab, probes=np.zeros(0, np.int32))
+    r = capi.sstate(plan, params, d["x"].clone(), setup, spp, K, 1e-30)
+    assert (r["periods"].cpu().numpy() == -1).all()
+    o = O.sstate(topo, P[1], dt, spp, K, 1e-30, m, grp, tab, O.dc(topo, P[1])["x"])
+    assert o["period"] == -1
+    assert_same_bits(r["x"][:, 1].cpu().numpy(), o["x"], "state after max_periods")
+    with pytest.raises(capi.CsimError):
+        capi.sstate(plan, params, d["x"].clone(), setup, 0, K, 1e-6)
