@@ -34,7 +34,7 @@ EXPORTS = [
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
-    "csim_dev_sstate",
+    "csim_dev_sstate", "csim_batch_sstate",
 ]
 
 

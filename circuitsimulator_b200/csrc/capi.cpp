@@ -177,6 +177,21 @@ int spec_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     return CSIM_OK;
 }
 
+// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bits 8-9: replicas - 1); unset = defaults.
+TpiOptions tpi_options_from_env() {
+    TpiOptions opt;
+    if (const char* env = std::getenv("CSIM_TPI_OPTS")) {
+        const int m = std::atoi(env);
+        opt.const_prop = m & 1;
+        opt.x_in_smem = m & 2;
+        opt.mos_in_smem = m & 4;
+        opt.q_in_smem = m & 8;
+        opt.mos_branchless = m & 16;
+        opt.replicas = 1 + ((m >> 8) & 3);
+    }
+    return opt;
+}
+
 // Generates, compiles and loads the thread-per-instance kernel specialised to `perm`.
 int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     TpiState& tp = plan->tpi;
@@ -185,15 +200,7 @@ int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     tp.d_stats = nullptr;
     jit_unload(tp.k);
     try {
-        TpiOptions opt;
-        if (const char* env = std::getenv("CSIM_TPI_OPTS")) {  // development aid: bit mask of TpiOptions
-            const int m = std::atoi(env);
-            opt.const_prop = m & 1;
-            opt.x_in_smem = m & 2;
-            opt.mos_in_smem = m & 4;
-            opt.q_in_smem = m & 8;
-            opt.mos_branchless = m & 16;
-        }
+        const TpiOptions opt = tpi_options_from_env();
         tp.host = generate_tran_tpi(plan->host, perm, opt);
     } catch (const std::exception& e) {
         tp.log = e.what();
@@ -211,7 +218,8 @@ int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     CU(cudaMalloc((void**)&tp.d_stats, 2 * sizeof(unsigned long long)));
     CU(cudaMemset(tp.d_stats, 0, 2 * sizeof(unsigned long long)));
     tp.log = "thread-per-instance: " + std::to_string(tp.host.n_slots) + " shared doubles per instance, " +
-             std::to_string(tp.host.threads) + " instances per CTA; per Newton iteration: " +
+             std::to_string(tp.host.replicas) + " instance(s) per thread, " + std::to_string(tp.host.threads) +
+             " threads per CTA; per Newton iteration: " +
              std::to_string(tp.host.n_lu_divs) + " multipliers, " + std::to_string(tp.host.n_elim_updates) +
              " row updates, " + std::to_string(tp.host.n_back_terms) + " back-substitution terms, " +
              std::to_string(tp.host.n_g_adds) + "+" + std::to_string(tp.host.n_rhs_adds) + " assembly adds" +
@@ -377,7 +385,8 @@ cudaError_t tpi_launch(const csim_plan* plan, const DevTran& T, int64_t B, const
     unsigned long long* stats = tp.d_stats;
     void* args[] = {&P, &Tc, &Bll, &params, &x, &wave, &iters_total, &iters_step, &pivot_hash, &status, &scratch, &stats};
     const int T_ = tp.host.threads;
-    const unsigned blocks = (unsigned)((B + T_ - 1) / T_);
+    const int64_t per_cta = (int64_t)T_ * tp.host.replicas;
+    const unsigned blocks = (unsigned)((B + per_cta - 1) / per_cta);
     e = cudaLaunchKernel(reinterpret_cast<const void*>(tp.k.kernel), dim3(blocks), dim3(T_), args, tp.host.smem_bytes,
                          stream);
     cudaFreeAsync(scratch, stream);
@@ -868,6 +877,45 @@ int csim_batch_tran(csim_batch* b, const csim_tran_args* a, double* x_dc, double
 }
 
 
+int csim_batch_sstate(csim_batch* b, const csim_tran_args* a, const csim_sstate_args* ss, double* x_dc, double* x,
+                      int32_t* periods, double* delta, int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status) {
+    if (!b || !a || !ss || !x) return fail(CSIM_E_INVALID, "csim_batch_sstate: null argument");
+    const csim_plan* plan = b->plan;
+    CU(cudaSetDevice(plan->device));
+    const int N = plan->host.N;
+    const int64_t B = b->B;
+    int rc = batch_reset_diag(b);
+    if (rc) return rc;
+    DevBuf d_table, d_group_b, d_periods, d_delta, d_total;
+    if (a->src_table && a->n_groups > 0 && a->table_steps > 0)
+        CU(d_table.put(a->src_table, sizeof(double) * (size_t)a->n_groups * a->table_steps));
+    if (a->src_group_b) CU(d_group_b.put(a->src_group_b, sizeof(int32_t) * (size_t)plan->host.n_sources * B));
+    CU(d_periods.put(nullptr, sizeof(int32_t) * B));
+    CU(d_delta.put(nullptr, sizeof(double) * B));
+    CU(d_total.put(nullptr, sizeof(int32_t) * B));
+    CU(cudaMemsetAsync(d_total.p, 0, sizeof(int32_t) * B, b->stream));
+    csim_tran_args da = *a;
+    da.src_table = a->src_table ? d_table.as<double>() : nullptr;
+    da.src_group_b = a->src_group_b ? d_group_b.as<int32_t>() : nullptr;
+    CU(cudaEventRecord(b->ev0, b->stream));
+    rc = csim_dev_dc(plan, B, b->d_params, b->d_x, nullptr, b->d_hash, b->d_status, b->stream);
+    if (rc) return rc;
+    if (x_dc) CU(cudaMemcpyAsync(x_dc, b->d_x, sizeof(double) * (size_t)N * B, cudaMemcpyDeviceToHost, b->stream));
+    rc = csim_dev_sstate(plan, B, b->d_params, &da, ss, b->d_x, d_periods.as<int32_t>(), d_delta.as<double>(),
+                         d_total.as<int32_t>(), b->d_hash, b->d_status, b->stream);
+    if (rc) return rc;
+    CU(cudaEventRecord(b->ev1, b->stream));
+    CU(cudaMemcpyAsync(x, b->d_x, sizeof(double) * (size_t)N * B, cudaMemcpyDeviceToHost, b->stream));
+    if (periods) CU(cudaMemcpyAsync(periods, d_periods.p, sizeof(int32_t) * B, cudaMemcpyDeviceToHost, b->stream));
+    if (delta) CU(cudaMemcpyAsync(delta, d_delta.p, sizeof(double) * B, cudaMemcpyDeviceToHost, b->stream));
+    if (iters_total) CU(cudaMemcpyAsync(iters_total, d_total.p, sizeof(int32_t) * B, cudaMemcpyDeviceToHost, b->stream));
+    if (pivot_hash) CU(cudaMemcpyAsync(pivot_hash, b->d_hash, sizeof(uint64_t) * B, cudaMemcpyDeviceToHost, b->stream));
+    if (status) CU(cudaMemcpyAsync(status, b->d_status, sizeof(uint32_t) * B, cudaMemcpyDeviceToHost, b->stream));
+    CU(cudaStreamSynchronize(b->stream));
+    CU(cudaEventElapsedTime(&b->last_ms, b->ev0, b->ev1));
+    return CSIM_OK;
+}
+
 int csim_host_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double* params, const double* x,
                         const double* x_prev, const double* src_val, double dt, double source_scale, double gmin,
                         double* vals, double* rhs) {
@@ -996,7 +1044,7 @@ int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_
     if (kind == 2) return csim_plan_generate_source(plan, perm, out, cap);
     if (kind != 3) return fail(CSIM_E_INVALID, "csim_plan_generate_source_kind: kind must be 2 or 3");
     try {
-        TpiHost th = generate_tran_tpi(plan->host, std::vector<int32_t>(perm, perm + plan->host.N));
+        TpiHost th = generate_tran_tpi(plan->host, std::vector<int32_t>(perm, perm + plan->host.N), tpi_options_from_env());
         if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", th.source.c_str());
         return (int)th.source.size();
     } catch (const std::exception& e) {

@@ -45,7 +45,7 @@ size_t spec_smem_bytes(const HostPlan& hp, const SpecHost& sh);
 struct TpiHost {
     std::vector<int32_t> perm;
     std::string source;  // entry: csim_tran_tpi
-    int32_t threads = 128, n_slots = 0, n_scratch_rows = 0;
+    int32_t threads = 32, replicas = 1, n_slots = 0, n_scratch_rows = 0;
     size_t smem_bytes = 0;
     uint32_t hash_lo = 0, hash_hi = 0;
     // statistics of the generated code (per Newton iteration, per instance)
@@ -57,6 +57,7 @@ struct TpiOptions {
     bool mos_in_smem = false;    // MOSFET parameters and linearisation values parked in shared memory
     bool q_in_smem = false;      // raw solution parked in the (dead) Y slots
     bool mos_branchless = false; // evaluate both MOSFET regions and select (measured slower on dbmixer)
+    int replicas = 1;            // instances advanced together by one thread (interleaved instruction streams)
 };
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt = TpiOptions());
 

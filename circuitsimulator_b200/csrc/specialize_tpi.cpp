@@ -31,7 +31,67 @@ namespace {
 constexpr size_t kMaxSmem = 232448;  // 227 KB dynamic shared memory per CTA on sm_100
 constexpr int kTpb = 32;             // one warp per CTA: the SM packs as many CTAs as shared memory allows
 
-std::string S(int slot) { return "sm[" + std::to_string(slot) + " * TPB + tid]"; }
+// Generated text is written for ONE instance with placeholders — identifier suffix '@' and replica
+// number '@R' — and then replicated (replicate() below) for the R instances a thread advances together.
+std::string S(int slot) { return "SM(" + std::to_string(slot) + ", @R)"; }
+
+// Lines containing '@' are emitted once per replica, back to back (so the instruction streams of the
+// replicas interleave at source level); regions between //@BEGIN and //@END lines are replicated as a
+// whole; ALL(x@) / ANY(x@) expand to the conjunction / disjunction over replicas.
+std::string replicate(const std::string& text, int R) {
+    auto subst = [](std::string l, int r) {
+        const std::string num = std::to_string(r), suf = "_" + std::to_string(r);
+        size_t p;
+        while ((p = l.find("@R")) != std::string::npos) l.replace(p, 2, num);
+        while ((p = l.find('@')) != std::string::npos) l.replace(p, 1, suf);
+        return l;
+    };
+    auto expand = [&](std::string l, const std::string& key, const std::string& op) {
+        size_t p;
+        while ((p = l.find(key + "(")) != std::string::npos) {
+            const size_t q = l.find(')', p);
+            const std::string inner = l.substr(p + key.size() + 1, q - p - key.size() - 1);
+            std::string rep = "(";
+            for (int r = 0; r < R; ++r) rep += (r ? op : "") + subst(inner, r);
+            l.replace(p, q - p + 1, rep + ")");
+        }
+        return l;
+    };
+    std::istringstream in(text);
+    std::ostringstream out;
+    std::string line, region;
+    bool in_region = false;
+    while (std::getline(in, line)) {
+        if (line.find("//@BEGIN") != std::string::npos) {
+            in_region = true;
+            region.clear();
+            continue;
+        }
+        if (line.find("//@END") != std::string::npos) {
+            in_region = false;
+            for (int r = 0; r < R; ++r) {
+                std::istringstream rin(region);
+                std::string l;
+                while (std::getline(rin, l)) out << subst(l, r) << "\n";
+            }
+            continue;
+        }
+        if (in_region) {
+            region += line + "\n";
+            continue;
+        }
+        if (line.find("ALL(") != std::string::npos || line.find("ANY(") != std::string::npos) {
+            out << expand(expand(line, "ALL", " && "), "ANY", " || ") << "\n";
+            continue;
+        }
+        if (line.find('@') == std::string::npos) {
+            out << line << "\n";
+            continue;
+        }
+        for (int r = 0; r < R; ++r) out << subst(line, r) << "\n";
+    }
+    return out.str();
+}
 
 std::string lit(double v) {  // exact literal
     if (v == 0.0) return std::signbit(v) ? "(-0.0)" : "0.0";
@@ -143,7 +203,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     }
     auto xrd = [&](int k) -> std::string {
         if (k < 0) return "0.0";
-        return opt.x_in_smem ? S(X0 + k) : "x" + std::to_string(k);
+        return opt.x_in_smem ? S(X0 + k) : "x" + std::to_string(k) + "@";
     };
     // static prefix sums: constant-folded, or one slot per distinct ordered term list
     std::map<std::vector<std::pair<int, bool>>, int> base_of;
@@ -193,29 +253,32 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
                 if (!prm_slot.count(m.param + t)) prm_slot[m.param + t] = alloc();
     auto val = [&](int v) -> Val {  // per-iteration operand
         if (is_const[v]) return Val::K(const_val[v]);
-        if (kind[v] == MOS) return opt.mos_in_smem ? Val::E(S(mos_slot.at(v))) : Val::E("m" + std::to_string(v));
+        if (kind[v] == MOS) return opt.mos_in_smem ? Val::E(S(mos_slot.at(v))) : Val::E("m" + std::to_string(v) + "@");
         return Val::E(S(val_slot.at(v)));
     };
 
-    std::ostringstream o;  // kernel body after the prologue (slot count is only known at the end)
-    o << "    unsigned long long h = (live && pivot_hash) ? pivot_hash[b] : CSIM_PIVOT_HASH_INIT;\n"
-         "    const unsigned long long F = 0x" << std::hex << (((unsigned long long)H.hash_hi << 32) | H.hash_lo) << std::dec << "ull;\n"
-         "    const double dt = T.dt;\n"
-         "    unsigned int st = 0, n_fallback = 0;\n"
-         "    int total = 0;\n"
-         "    bool dead = !live, degen = false;\n";
+
+    const int R = std::max(1, opt.replicas);
+    std::ostringstream o;  // kernel body after the prologue, written for one replica ('@' placeholders)
+    o << "    const long long b@ = (long long)blockIdx.x * (TPB * NREP) + @R * TPB + tid;\n"
+         "    const bool live@ = b@ < B && !(T.skip && T.skip[b@ < B ? b@ : B - 1]);\n"
+         "    const long long bb@ = b@ < B ? b@ : B - 1;  // idle lanes shadow an instance and never store\n"
+         "    unsigned long long h@ = (live@ && pivot_hash) ? pivot_hash[b@] : CSIM_PIVOT_HASH_INIT;\n"
+         "    unsigned int st@ = 0, n_fallback@ = 0;\n"
+         "    int total@ = 0;\n"
+         "    bool dead@ = !live@, degen@ = false;\n";
     for (int i = 0; i < N; ++i) {
-        if (opt.x_in_smem) o << "    " << S(X0 + i) << " = xio[(long long)" << i << " * B + bb];\n";
-        else o << "    double x" << i << " = xio[(long long)" << i << " * B + bb];\n";
+        if (opt.x_in_smem) o << "    " << S(X0 + i) << " = xio[(long long)" << i << " * B + bb@];\n";
+        else o << "    double x" << i << "@ = xio[(long long)" << i << " * B + bb@];\n";
     }
     // ---- one-off: static values, base sums ---------------------------------------------------------
     for (const auto& kv : prm_slot)
-        o << "    " << S(kv.second) << " = __ldg(params + (long long)" << kv.first << " * B + bb);\n";
-    o << "    {\n";
-    for (int p : ind_params) o << "        degen = degen || !(__ldg(params + (long long)" << p << " * B + bb) > 0.0);\n";
+        o << "    " << S(kv.second) << " = __ldg(params + (long long)" << kv.first << " * B + bb@);\n";
+    o << "    //@BEGIN\n    {\n";
+    for (int p : ind_params) o << "        degen@ = degen@ || !(__ldg(params + (long long)" << p << " * B + bb@) > 0.0);\n";
     for (const StaticOp& op : mp.static_ops) {
         o << "        const double v" << op.out << " = ";
-        const std::string P = "__ldg(params + (long long)" + std::to_string(op.param) + " * B + bb)";
+        const std::string P = "__ldg(params + (long long)" + std::to_string(op.param) + " * B + bb@)";
         if (is_const[op.out]) o << lit(const_val[op.out]);
         else switch (op.kind) {
             case SK_ONE: o << "1.0"; break;
@@ -229,7 +292,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         o << ";\n";
         if (val_slot.count(op.out)) o << "        " << S(val_slot[op.out]) << " = v" << op.out << ";\n";
         if (gs_row.count(op.out))
-            o << "        if (live) scratch[(long long)" << gs_row[op.out] << " * B + b] = v" << op.out << ";\n";
+            o << "        if (live@) scratch[(long long)" << gs_row[op.out] << " * B + b@] = v" << op.out << ";\n";
     }
     for (const auto& kv : base_of) {
         std::string acc = "0.0";
@@ -237,46 +300,46 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
             acc = std::string(t.second ? "d_sub(" : "d_add(") + acc + ", v" + std::to_string(t.first) + ")";
         o << "        " << S(kv.second) << " = " << acc << ";\n";
     }
-    o << "    }\n"
+    o << "    }\n    //@END\n"
          "    const int r0 = T.out_begin_step / T.out_stride;\n"
          "    for (int step = T.step_begin; step < T.step_end; ++step) {\n"
-         "        if (__all_sync(0xFFFFFFFFu, dead)) break;\n";
+         "        if (__all_sync(0xFFFFFFFFu, ALL(dead@))) break;\n";
     // ---- per step: x_prev -> scratch, companion history terms, source values -------------------------
     for (int i = 0; i < N; ++i)
-        o << "        if (live) scratch[(long long)" << (XP0 + i) << " * B + b] = " << xrd(i) << ";\n";
+        o << "        if (live@) scratch[(long long)" << (XP0 + i) << " * B + b@] = " << xrd(i) << ";\n";
     for (const StepOp& op : mp.step_ops) {
         if (!val_slot.count(op.out)) continue;
-        const std::string g = "scratch[(long long)" + std::to_string(gs_row[op.g]) + " * B + bb]";
+        const std::string g = "scratch[(long long)" + std::to_string(gs_row[op.g]) + " * B + bb@]";
         std::string e;
         if (op.kind == TK_CAP_HIST) e = "d_mul(-" + g + ", d_sub(" + xrd(op.a) + ", " + xrd(op.b) + "))";
         else e = "d_mul(" + g + ", " + xrd(op.a) + ")";
         o << "        " << S(val_slot[op.out]) << " = " << e << ";\n";
     }
     if (!mp.src_ops.empty()) {
-        o << "        {\n            const double tnow = d_mul((double)(step + 1), dt);  // tanalisis.cpp:256\n";
+        o << "        const double tnow = d_mul((double)(step + 1), dt);  // tanalisis.cpp:256\n";
         for (const SrcOp& op : mp.src_ops) {
             if (!val_slot.count(op.out)) continue;
-            o << "            " << S(val_slot[op.out]) << " = src_tran_value(T, params, B, bb, " << op.index << ", "
+            o << "        " << S(val_slot[op.out]) << " = src_tran_value(T, params, B, bb@, " << op.index << ", "
               << op.param << ", step, tnow);\n";
         }
-        o << "        }\n";
     }
-    o << "        int count = 0;\n"
-         "        bool done = dead;\n"
+    o << "        int count@ = 0;\n"
+         "        bool done@ = dead@;\n"
          "        for (int iter = 0; iter < " << C.tran_max_iters << "; ++iter) {\n"
-         "            if (__all_sync(0xFFFFFFFFu, done)) break;\n"
-         "            bool bad = degen;\n"
-         "            unsigned int glo = 0xFFFFFFFFu, ghi = 0u;\n";
+         "            if (__all_sync(0xFFFFFFFFu, ALL(done@))) break;\n"
+         "            bool bad@ = degen@;\n"
+         "            unsigned int glo@ = 0xFFFFFFFFu, ghi@ = 0u;\n";
     // ---- MOSFET linearisation -------------------------------------------------------------------------
     for (const MosOp& op : mp.mos_ops) {
-        auto prm = [&](int k) { return opt.mos_in_smem ? S(prm_slot.at(k)) : "PRM(" + std::to_string(k) + ")"; };
-        o << "            double m" << op.out << ", m" << op.out + 1 << ", m" << op.out + 2 << ", m" << op.out + 3 << ";\n"
+        auto prm = [&](int k) { return opt.mos_in_smem ? S(prm_slot.at(k)) : "PRM(" + std::to_string(k) + ", bb@)"; };
+        auto mn = [&](int t) { return "m" + std::to_string(op.out + t) + "@"; };
+        o << "            double " << mn(0) << ", " << mn(1) << ", " << mn(2) << ", " << mn(3) << ";\n"
           << "            " << (opt.mos_branchless ? "mos_eval_sel" : "mos_eval_pp") << "<" << (op.is_p ? -1 : 1) << ">("
           << prm(op.param) << ", " << prm(op.param + 1) << ", " << prm(op.param + 2) << ", " << lit(C.mos_off_gds) << ", "
-          << xrd(op.d) << ", " << xrd(op.g) << ", " << xrd(op.s) << ", m" << op.out << ", m" << op.out + 1 << ", m"
-          << op.out + 2 << ", m" << op.out + 3 << ");\n";
+          << xrd(op.d) << ", " << xrd(op.g) << ", " << xrd(op.s) << ", " << mn(0) << ", " << mn(1) << ", " << mn(2) << ", "
+          << mn(3) << ");\n";
         if (opt.mos_in_smem)
-            for (int t = 0; t < 4; ++t) o << "            " << S(mos_slot[op.out + t]) << " = m" << op.out + t << ";\n";
+            for (int t = 0; t < 4; ++t) o << "            " << S(mos_slot[op.out + t]) << " = " << mn(t) << ";\n";
     }
     // ---- rows: assemble, eliminate, park ----------------------------------------------------------------
     // generator-side description of the factorisation so far
@@ -290,7 +353,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         if (d.c && d.v == 1.0) return a;
         if (d.c && d.v == -1.0) return neg(a);
         if (a.c && d.c) return Val::K(a.v / d.v);
-        o << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo, ghi);\n";
+        o << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo@, ghi@);\n";
         H.n_lu_divs++;
         return Val::E(tmp);
     };
@@ -299,7 +362,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         std::map<int, Val> row;
         std::set<int> declared;
         auto assign = [&](int j, const Val& v) {  // j == N: right-hand side
-            const std::string name = j == N ? std::string("rb") : "r" + std::to_string(j);
+            const std::string name = (j == N ? std::string("rb") : "r" + std::to_string(j)) + "@";
             if (v.c) {
                 row[j] = v;
                 return;
@@ -323,12 +386,12 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
             const Val a = row[k];
             // the reference would have picked this row instead of the predicted pivot (solver.hpp:46-56)
             if (a.c && Dv[k].c) {
-                if (std::fabs(a.v) > std::fabs(Dv[k].v)) o << "                bad = true;\n";
+                if (std::fabs(a.v) > std::fabs(Dv[k].v)) o << "                bad@ = true;\n";
             } else {
-                o << "                bad = bad || (fabs(" << a.e << ") > " << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")")
-                  << ");\n";
+                o << "                bad@ = bad@ || (fabs(" << a.e << ") > "
+                  << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")") << ");\n";
             }
-            std::snprintf(num, sizeof num, "f%d_%d", i, k);
+            std::snprintf(num, sizeof num, "f%d_%d@", i, k);
             const Val f = divide(a, k, num, "                ");
             for (int j : A.cols_k[k]) {
                 assign(j, sub(row[j], mul(f, Uv[k].at(j))));
@@ -342,9 +405,9 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
             Dv[i] = d;
         } else {
             const int sd = alloc(), srd = alloc();
-            const std::string dn = "r" + std::to_string(i);
+            const std::string dn = "r" + std::to_string(i) + "@";
             if (d.c) o << "                const double " << dn << " = " << d.e << ";\n";
-            o << "                bad = bad || !(fabs(" << dn << ") >= " << lit(C.lu_eps) << " && fabs(" << dn
+            o << "                bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(C.lu_eps) << " && fabs(" << dn
               << ") <= 0x1.fffffffffffffp+1023);\n"
               << "                " << S(sd) << " = " << dn << ";\n"
               << "                " << S(srd) << " = rcp_seq(" << dn << ");\n";
@@ -365,130 +428,137 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         if (row[N].c) {
             Yv[i] = row[N];
         } else {
-            o << "                " << S(Y0 + i) << " = rb;\n";
+            o << "                " << S(Y0 + i) << " = rb@;\n";
             Yv[i] = Val::E(S(Y0 + i));
         }
         o << "            }\n";
     }
     // ---- back substitution (include/solver.hpp:116-128) ---------------------------------------------------
     std::vector<Val> Q(N);
-    if (!opt.q_in_smem)
-        for (int i = 0; i < N; ++i) o << "            double q" << i << ";\n";
+    for (int i = 0; i < N; ++i) o << "            double q" << i << "@;\n";
     for (int i = N - 1; i >= 0; --i) {
         o << "            {\n";
-        if (opt.q_in_smem) o << "                double q" << i << ";\n";
         Val s = Yv[i];
         int t = 0;
         for (int j : A.ucols[i]) {
             s = sub(s, mul(Uv[i].at(j), Q[j]));
             H.n_back_terms++;
             if (!s.c && (++t % 3) == 0) {  // keep expressions shallow
-                o << "                const double s" << t << " = " << s.e << ";\n";
-                s = Val::E("s" + std::to_string(t));
+                o << "                const double s" << t << "@ = " << s.e << ";\n";
+                s = Val::E("s" + std::to_string(t) + "@");
             }
         }
-        const Val q = divide(s, i, "qq", "                ");
-        o << "                q" << i << " = " << q.e << ";\n";
-        if (!Dv[i].c) o << "                if (fabs(" << Dv[i].e << ") < 1e-15) q" << i << " = 0.0;\n";
-        if (opt.q_in_smem) o << "                " << S(Y0 + i) << " = q" << i << ";\n";
+        const Val q = divide(s, i, "qq@", "                ");
+        o << "                q" << i << "@ = " << q.e << ";\n";
+        if (!Dv[i].c) o << "                if (fabs(" << Dv[i].e << ") < 1e-15) q" << i << "@ = 0.0;\n";
+        if (opt.q_in_smem) o << "                " << S(Y0 + i) << " = q" << i << "@;\n";
         o << "            }\n";
-        Q[i] = opt.q_in_smem ? Val::E(S(Y0 + i)) : Val::E("q" + std::to_string(i));
+        Q[i] = opt.q_in_smem ? Val::E(S(Y0 + i)) : Val::E("q" + std::to_string(i) + "@");
     }
     // ---- prediction check / per-lane generic redo ------------------------------------------------------------
-    o << "            const bool slow = (glo < 0x03600000u) || (ghi > 0x7FEFFFFFu);\n"
-         "            const bool redo = (bad || slow) && !done;\n"
-         "            if (__any_sync(0xFFFFFFFFu, redo)) {\n"
-         "                if (redo) {\n"
-         "                    ++n_fallback;\n"
+    o << "            const bool redo@ = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu)) && !done@;\n"
+         "            if (__any_sync(0xFFFFFFFFu, ANY(redo@))) {\n"
+         "                //@BEGIN\n"
+         "                if (redo@) {\n"
+         "                    ++n_fallback@;\n"
          "                    double xl[SPEC_N], xo[SPEC_N];\n";
     for (int i = 0; i < N; ++i) o << "                    xl[" << i << "] = " << xrd(i) << ";\n";
-    o << "                    tpi_generic_solve<SPEC_N, SPEC_NV>(P, T, params, B, bb, step, xl, scratch + (long long)" << XP0
-      << " * B, xo, h, st);\n";
-    for (int i = 0; i < N; ++i)
-        o << "                    " << (opt.q_in_smem ? S(Y0 + i) : "q" + std::to_string(i)) << " = xo[" << i << "];\n";
+    o << "                    tpi_generic_solve<SPEC_N, SPEC_NV>(P, T, params, B, bb@, step, xl, scratch + (long long)" << XP0
+      << " * B, xo, h@, st@);\n";
+    for (int i = 0; i < N; ++i) o << "                    q" << i << "@ = xo[" << i << "];\n";
     o << "                }\n"
+         "                //@END\n"
          "            }\n"
-         "            if (!redo && !done) h = (h ^ F) * 0x100000001B3ull;\n";
+         "            if (!redo@ && !done@) h@ = (h@ ^ F) * 0x100000001B3ull;\n";
     // ---- damping, norm, convergence (src/tanalisis.cpp:359-376) -----------------------------------------------
-    o << "            bool fin = true;\n";
-    if (opt.q_in_smem)
-        for (int i = 0; i < N; ++i) o << "            const double q" << i << " = " << S(Y0 + i) << ";\n";
-    for (int i = 0; i < N; ++i) o << "            fin = fin && finite_d(q" << i << ");\n";
-    o << "            if (!done) {\n"
-         "                ++count;\n"
-         "                if (!fin) {  // the reference throws here\n"
-         "                    st |= CSIM_ST_NONFINITE;\n"
-         "                    dead = true;\n"
-         "                    done = true;\n"
+    o << "            bool fin@ = true;\n";
+    for (int i = 0; i < N; ++i) o << "            fin@ = fin@ && finite_d(q" << i << "@);\n";
+    o << "            //@BEGIN\n"
+         "            if (!done@) {\n"
+         "                ++count@;\n"
+         "                if (!fin@) {  // the reference throws here\n"
+         "                    st@ |= CSIM_ST_NONFINITE;\n"
+         "                    dead@ = true;\n"
+         "                    done@ = true;\n"
          "                }\n"
          "            }\n"
-         "            const bool upd = !done;\n";
+         "            //@END\n"
+         "            const bool upd@ = !done@;\n";
     for (int i = 0; i < N; ++i) {
         const std::string xi = xrd(i), I = std::to_string(i);
-        if (opt.x_in_smem) o << "            const double xo" << I << " = " << xi << ";\n";
-        const std::string xv = opt.x_in_smem ? "xo" + I : xi;
-        o << "            const double n" << I << " = d_add(" << xv << ", d_mul(" << lit(C.tran_alpha) << ", d_sub(q" << I << ", "
-          << xv << ")));\n"
-          << "            double e" << I << " = d_sub(n" << I << ", " << xv << ");\n"
-          << "            e" << I << " = d_mul(e" << I << ", e" << I << ");\n";
-        if (opt.x_in_smem) o << "            if (upd) " << xi << " = n" << I << ";\n";
-        else o << "            x" << I << " = upd ? n" << I << " : x" << I << ";\n";
+        if (opt.x_in_smem) o << "            const double xo" << I << "@ = " << xi << ";\n";
+        const std::string xv = opt.x_in_smem ? "xo" + I + "@" : xi;
+        o << "            const double n" << I << "@ = d_add(" << xv << ", d_mul(" << lit(C.tran_alpha) << ", d_sub(q" << I
+          << "@, " << xv << ")));\n"
+          << "            double e" << I << "@ = d_sub(n" << I << "@, " << xv << ");\n"
+          << "            e" << I << "@ = d_mul(e" << I << "@, e" << I << "@);\n";
+        if (opt.x_in_smem) o << "            if (upd@) " << xi << " = n" << I << "@;\n";
+        else o << "            x" << I << "@ = upd@ ? n" << I << "@ : x" << I << "@;\n";
     }
     // 32-leaf pairwise tree (oracle/csim_norm2.h); leaves >= N are +0 and adding +0 to a square is exact
     {
         std::vector<std::string> leaf(32);
-        for (int i = 0; i < 32; ++i) leaf[i] = i < N ? "e" + std::to_string(i) : "";
+        for (int i = 0; i < 32; ++i) leaf[i] = i < N ? "e" + std::to_string(i) + "@" : "";
         for (int s = 16; s >= 1; s >>= 1)
             for (int i = 0; i < s; ++i) {
                 if (leaf[i + s].empty()) continue;
                 if (leaf[i].empty()) leaf[i] = leaf[i + s];
                 else leaf[i] = "d_add(" + leaf[i] + ", " + leaf[i + s] + ")";
             }
-        o << "            const double err = sqrt(" << leaf[0] << ");\n";
+        o << "            const double err@ = sqrt(" << leaf[0] << ");\n";
     }
-    o << "            if (upd) {\n"
-         "                if (err < " << lit(C.tran_tol) << ") done = true;\n"
-         "                else if (iter == " << C.tran_max_iters - 1 << ") st |= CSIM_ST_TRAN_UNCONVERGED;\n"
+    o << "            //@BEGIN\n"
+         "            if (upd@) {\n"
+         "                if (err@ < " << lit(C.tran_tol) << ") done@ = true;\n"
+         "                else if (iter == " << C.tran_max_iters - 1 << ") st@ |= CSIM_ST_TRAN_UNCONVERGED;\n"
          "            }\n"
+         "            //@END\n"
          "        }\n"
-         "        total += count;\n"
-         "        if (iters_step && live && count > 0) iters_step[(long long)step * B + b] = (unsigned char)count;\n"
-         "        if ((step + 1) % T.out_stride == 0 && step >= T.out_begin_step && T.n_probes > 0) {\n";
+         "        total@ += count@;\n"
+         "        if (iters_step && live@ && count@ > 0) iters_step[(long long)step * B + b@] = (unsigned char)count@;\n"
+         "        if ((step + 1) % T.out_stride == 0 && step >= T.out_begin_step && T.n_probes > 0) {\n"
+         "            const long long r = (step + 1) / T.out_stride - 1 - r0;\n";
     const int PB = opt.x_in_smem ? X0 : Y0;  // where the probes are read from
     if (!opt.x_in_smem)
-        for (int i = 0; i < N; ++i) o << "            " << S(Y0 + i) << " = x" << i << ";\n";
-    o << "            if (live && !dead) {\n"
-         "                const long long r = (step + 1) / T.out_stride - 1 - r0;\n"
+        for (int i = 0; i < N; ++i) o << "            " << S(Y0 + i) << " = x" << i << "@;\n";
+    o << "            //@BEGIN\n"
+         "            if (live@ && !dead@)\n"
          "                for (int p = 0; p < T.n_probes; ++p)\n"
-         "                    wave[((long long)b * T.n_probes + p) * T.wave_ld + r] = sm[(" << PB << " + T.probes[p]) * TPB + tid];\n"
-         "            }\n"
+         "                    wave[((long long)b@ * T.n_probes + p) * T.wave_ld + r] = SM(" << PB << " + T.probes[p], @R);\n"
+         "            //@END\n"
          "        }\n"
          "    }\n"
-         "    if (live) {\n";
-    for (int i = 0; i < N; ++i) o << "        xio[(long long)" << i << " * B + b] = " << xrd(i) << ";\n";
-    o << "        if (iters_total) iters_total[b] += total;\n"
-         "        if (pivot_hash) pivot_hash[b] = h;\n"
-         "        if (status) status[b] |= st;\n"
+         "    //@BEGIN\n"
+         "    if (live@) {\n";
+    for (int i = 0; i < N; ++i) o << "        xio[(long long)" << i << " * B + b@] = " << xrd(i) << ";\n";
+    o << "        if (iters_total) iters_total[b@] += total@;\n"
+         "        if (pivot_hash) pivot_hash[b@] = h@;\n"
+         "        if (status) status[b@] |= st@;\n"
          "        if (stats) {\n"
-         "            if (n_fallback) atomicAdd(stats, (unsigned long long)n_fallback);\n"
-         "            atomicAdd(stats + 1, (unsigned long long)total);\n"
+         "            if (n_fallback@) atomicAdd(stats, (unsigned long long)n_fallback@);\n"
+         "            atomicAdd(stats + 1, (unsigned long long)total@);\n"
          "        }\n"
          "    }\n"
+         "    //@END\n"
          "}\n";
 
     H.n_slots = n_slots;
-    H.smem_bytes = (size_t)n_slots * 8 * kTpb;
+    H.replicas = R;
+    H.smem_bytes = (size_t)n_slots * 8 * kTpb * R;
     if (H.smem_bytes > kMaxSmem) throw std::runtime_error("specialize: per-instance state exceeds shared memory");
     std::ostringstream pro;
     pro << "// generated by specialize_tpi.cpp — thread-per-instance transient kernel for one topology and one\n"
-           "// predicted pivot permutation; " << n_slots << " shared-memory doubles per instance, " << kTpb
-        << " instances per CTA.\n"
+           "// predicted pivot permutation; " << n_slots << " shared-memory doubles per instance, " << R
+        << " instance(s) per thread, " << kTpb << " threads per CTA.\n"
            "#include \"tpi_runtime.cuh\"\n"
            "using namespace csim;\n"
            "#define TPB " << kTpb << "\n"
+           "#define NREP " << R << "\n"
+           "#define NSLOTS " << n_slots << "\n"
            "#define SPEC_N " << N << "\n"
            "#define SPEC_NV " << mp.n_values << "\n"
-           "#define PRM(k) ld_nohoist(params + (long long)(k) * B + bb)\n"
+           "#define SM(k, r) sm[((k) + (r) * NSLOTS) * TPB + tid]\n"
+           "#define PRM(k, bb) ld_nohoist(params + (long long)(k) * B + (bb))\n"
            "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kMaxSmem / (H.smem_bytes + 1024)))
         << ")\n"
            "csim_tran_tpi(DevPlan P, DevTran T, long long B, const double* __restrict__ params,\n"
@@ -498,10 +568,10 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
            "              unsigned long long* __restrict__ stats) {\n"
            "    extern __shared__ double sm[];\n"
            "    const int tid = threadIdx.x;\n"
-           "    const long long b = (long long)blockIdx.x * TPB + tid;\n"
-           "    const bool live = b < B && !(T.skip && T.skip[b < B ? b : B - 1]);\n"
-           "    const long long bb = b < B ? b : B - 1;  // idle lanes shadow an instance and never store\n";
-    H.source = pro.str() + o.str();
+           "    const double dt = T.dt;\n"
+           "    const unsigned long long F = 0x" << std::hex << (((unsigned long long)H.hash_hi << 32) | H.hash_lo) << std::dec
+        << "ull;\n";
+    H.source = pro.str() + replicate(o.str(), R);
     return H;
 }
 

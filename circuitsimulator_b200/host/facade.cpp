@@ -6,7 +6,10 @@
 #include <string>
 
 #include "../../include/csim_host.h"
+#include <algorithm>
+
 #include "csim/lower.hpp"
+#include "csim/sstateanalysis.hpp"
 #include "csim/parser.hpp"
 #include "csim/tanalisis.hpp"
 
@@ -154,6 +157,37 @@ int csimh_run_tran_csv(const csimh_netlist* h, const char* path) {
     try {
         runTransientAnalysisBackwardEuler(h->ckt, h->sim, path);
         return 0;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return -1;
+    }
+}
+
+// runSteadyStateAnalysisBatch of the C++ host layer (include/csim/sstateanalysis.hpp); f0 / tstep > 0
+// override the netlist's `.hb` / `.TRAN` values.  Arrays as documented there; returns steps per period
+// (> 0) or -1 with csimh_last_error().
+int csimh_run_sstate(const csimh_netlist* h, int64_t B, const double* params, double f0, double tstep,
+                     int32_t max_periods, double tol, double* x_dc, double* x, int32_t* periods, double* delta,
+                     int32_t* iters_total) {
+    if (!h || !params || B <= 0) return -1;
+    try {
+        SimulationConfig sim = h->sim;
+        if (f0 > 0.0) {
+            sim.hb.enabled = true;
+            sim.hb.f0 = f0;
+        }
+        if (tstep > 0.0) sim.tran.tstep = tstep;
+        const std::vector<double> p(params, params + (size_t)h->low.n_params * B);
+        csim::SteadyStateResult R = csim::runSteadyStateAnalysisBatch(h->ckt, sim, p, B, max_periods, tol);
+        auto put = [](auto& v, auto* out) {
+            if (out) std::copy(v.begin(), v.end(), out);
+        };
+        put(R.x_dc, x_dc);
+        put(R.x, x);
+        put(R.periods, periods);
+        put(R.delta, delta);
+        put(R.iters_total, iters_total);
+        return R.steps_per_period;
     } catch (const std::exception& e) {
         g_herr = e.what();
         return -1;

@@ -1,6 +1,7 @@
 // lower.cpp — Circuit -> csim_topology lowering, host source tabulation, batched drivers,
 // and the device-backed Element::stamp.
 #include "csim/lower.hpp"
+#include "csim/sstateanalysis.hpp"
 
 #include <cmath>
 #include <cstdio>
@@ -212,6 +213,51 @@ BatchResult runTransientAnalysisBackwardEulerBatch(const Circuit& ckt, const Sim
     if (csim_batch_tran(bg.b, &a, R.x_dc.data(), R.x_final.data(), R.n_probes ? R.wave.data() : nullptr,
                         R.iters_total.data(), nullptr, R.pivot_hash.data(), R.status.data()))
         raise("csim_batch_tran");
+    R.kernel_ms = csim_batch_last_kernel_ms(bg.b);
+    return R;
+}
+
+SteadyStateResult runSteadyStateAnalysisBatch(const Circuit& ckt, const SimulationConfig& sim,
+                                              const std::vector<double>& params, int64_t B, int max_periods,
+                                              double tol, int device) {
+    if (!sim.hb.enabled || !(sim.hb.f0 > 0.0)) throw std::runtime_error("Steady state: .hb card with f0 > 0 required.");
+    if (!(sim.tran.tstep > 0.0)) throw std::runtime_error("Steady state: .TRAN card (tstep) required.");
+    Lowered L = lower(ckt);
+    if (static_cast<int64_t>(params.size()) != static_cast<int64_t>(L.n_params) * B)
+        throw std::runtime_error("runSteadyStateAnalysisBatch: params must hold P*B doubles");
+    SteadyStateResult R;
+    R.B = B;
+    R.steps_per_period = static_cast<int32_t>(std::llround(1.0 / sim.hb.f0 / sim.tran.tstep));
+    if (R.steps_per_period < 1) throw std::runtime_error("Steady state: period shorter than one timestep.");
+    const int64_t total = static_cast<int64_t>(R.steps_per_period) * max_periods;
+    if (total > 2147483647LL) throw std::runtime_error("Steady state: too many steps.");
+    SourceTables S = tabulate_sources(ckt, sim.tran.tstep, static_cast<int32_t>(total));
+    csim_topology t = L.view();
+    PlanGuard pg;
+    if (csim_plan_create(&t, nullptr, device, &pg.p)) raise("csim_plan_create");
+    BatchGuard bg;
+    if (csim_batch_create(pg.p, B, &bg.b)) raise("csim_batch_create");
+    if (csim_batch_set_params(bg.b, params.data())) raise("csim_batch_set_params");
+    const std::size_t NB = static_cast<std::size_t>(L.n_unknowns) * B;
+    R.x_dc.resize(NB);
+    R.x.resize(NB);
+    R.periods.resize(B);
+    R.delta.resize(B);
+    R.iters_total.resize(B);
+    R.pivot_hash.resize(B);
+    R.status.resize(B);
+    csim_tran_args a;
+    std::memset(&a, 0, sizeof(a));
+    a.dt = sim.tran.tstep;
+    a.n_groups = S.n_groups;
+    a.table_steps = static_cast<int32_t>(total);
+    a.src_table = S.table.data();
+    a.src_mode = S.mode.data();
+    a.src_group = S.group.data();
+    csim_sstate_args ss{R.steps_per_period, max_periods, tol};
+    if (csim_batch_sstate(bg.b, &a, &ss, R.x_dc.data(), R.x.data(), R.periods.data(), R.delta.data(),
+                          R.iters_total.data(), R.pivot_hash.data(), R.status.data()))
+        raise("csim_batch_sstate");
     R.kernel_ms = csim_batch_last_kernel_ms(bg.b);
     return R;
 }

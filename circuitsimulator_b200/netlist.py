@@ -143,6 +143,26 @@ class Netlist:
         out[lo:, mask] = self.params[mask] * (1.0 + rel * u[lo:, mask])
         return np.ascontiguousarray(out.T)
 
+    def steady_state(self, params, f0: float = 0.0, tstep: float = 0.0, max_periods: int = 20, tol: float = 1e-6):
+        """runSteadyStateAnalysisBatch of the C++ host layer: params [P, B] -> dict of numpy arrays."""
+        L = _hlib()
+        params = np.ascontiguousarray(params, np.float64)
+        B = params.shape[1]
+        N = self.n_unknowns
+        out = dict(x_dc=np.empty((N, B)), x=np.empty((N, B)), periods=np.empty(B, np.int32), delta=np.empty(B),
+                   iters_total=np.empty(B, np.int32))
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        L.csimh_run_sstate.restype = C.c_int
+        L.csimh_run_sstate.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_double, C.c_double, C.c_int32,
+                                       C.c_double] + [C.c_void_p] * 5
+        spp = L.csimh_run_sstate(C.c_void_p(self._h), B, vp(params), float(f0), float(tstep), int(max_periods),
+                                 float(tol), vp(out["x_dc"]), vp(out["x"]), vp(out["periods"]), vp(out["delta"]),
+                                 vp(out["iters_total"]))
+        if spp < 0:
+            raise capi.CsimError(L.csimh_last_error().decode(errors="replace"))
+        out["steps_per_period"] = spp
+        return out
+
     def run_reference_style_csv(self, path: str):
         """runTransientAnalysisBackwardEuler(ckt, sim, path) of the C++ host layer (B = 1 on the GPU)."""
         L = _hlib()

@@ -318,6 +318,13 @@ int csim_batch_dc(csim_batch* batch, double* x, int32_t* iters, uint64_t* pivot_
 int csim_batch_tran(csim_batch* batch, const csim_tran_args* args, double* x_dc, double* x_final, double* wave,
                     int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status);
 #endif
+/* DC operating point followed by csim_dev_sstate from it; tran->src_table / src_group_b are HOST
+ * pointers; x_dc, x [N][B], periods, delta, iters_total, pivot_hash, status: host (NULL ok except x). */
+#ifndef __CUDACC_RTC__
+int csim_batch_sstate(csim_batch* batch, const csim_tran_args* tran, const csim_sstate_args* ss, double* x_dc,
+                      double* x, int32_t* periods, double* delta, int32_t* iters_total, uint64_t* pivot_hash,
+                      uint32_t* status);
+#endif
 /* Host-pointer forms of the two standalone kernels (copies inside; for the C++ drop-in
  * classes Element::stamp and Solver::solveLinearSystemLU and for small tests).            */
 #ifndef __CUDACC_RTC__

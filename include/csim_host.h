@@ -29,6 +29,11 @@ int csimh_tabulate_sources(const csimh_netlist* h, double dt, int32_t n_steps, i
                            double* table, int32_t* n_groups);
 int csimh_sin_table(double freq, double td, double phi, double dt, int32_t n_steps, double* out);
 int csimh_run_tran_csv(const csimh_netlist* h, const char* path);
+/* runSteadyStateAnalysisBatch (include/csim/sstateanalysis.hpp); f0/tstep > 0 override .hb/.TRAN.
+ * Returns steps per period, or -1. */
+int csimh_run_sstate(const csimh_netlist* h, int64_t B, const double* params, double f0, double tstep,
+                     int32_t max_periods, double tol, double* x_dc, double* x, int32_t* periods, double* delta,
+                     int32_t* iters_total);
 #ifdef __cplusplus
 }
 #endif

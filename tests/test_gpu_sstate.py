@@ -69,3 +69,25 @@ def test_steady_state_gives_up_after_max_periods(torch):
     assert_same_bits(r["x"][:, 1].cpu().numpy(), o["x"], "state after max_periods")
     with pytest.raises(capi.CsimError):
         capi.sstate(plan, params, d["x"].clone(), setup, 0, K, 1e-6)
+
+
+def test_host_layer_driver_equals_device_api(torch):
+    """runSteadyStateAnalysisBatch (C++ host layer, host buffers, .hb/.TRAN cards) == csim_dev_sstate."""
+    from circuitsimulator_b200 import capi
+    from circuitsimulator_b200.netlist import Netlist
+    g, topo = load_golden("buffer")
+    nl = Netlist(str(g["netlist"]))
+    B, K, tol = 5, 4, 2e-8
+    P = nl.monte_carlo(B, 77)
+    h = nl.steady_state(P, f0=10e6, max_periods=K, tol=tol)  # buffer.sp's own .hb card says 1e-2 Hz
+    assert h["steps_per_period"] == 100
+    plan = nl.plan()
+    params = dev(torch, P)
+    d = capi.dc(plan, params)
+    m, grp, tab = nl.source_tables(n_steps=100 * K)
+    setup = capi.TranSetup(nl.tran["tstep"], 100 * K, m, grp, tab, probes=np.zeros(0, np.int32))
+    r = capi.sstate(plan, params, d["x"].clone(), setup, 100, K, tol)
+    assert np.array_equal(h["periods"], r["periods"].cpu().numpy()) and (h["periods"] > 0).all()
+    assert_same_bits(h["x"], r["x"].cpu().numpy(), "host-layer steady state")
+    assert_same_bits(h["x_dc"], d["x"].cpu().numpy(), "host-layer DC")
+    assert np.array_equal(h["iters_total"], r["iters_total"].cpu().numpy())
