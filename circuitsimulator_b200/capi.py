@@ -329,7 +329,8 @@ class TranSetup:
         self.probes = _i32(probes)
         self.out_stride = int(out_stride)
         self.out_begin_step = int(out_begin_step)
-        self.src_group_b = src_group_b
+        # per-instance source groups [n_sources, B] (numpy int32, or None: every instance uses src_group)
+        self.src_group_b = None if src_group_b is None else np.ascontiguousarray(src_group_b, np.int32)
         self.n_out = self.n_steps // self.out_stride - self.out_begin_step // self.out_stride
         self._dev_table = {}
 
@@ -338,6 +339,14 @@ class TranSetup:
         key = str(device)
         if key not in self._dev_table:
             self._dev_table[key] = torch.from_numpy(self.table).to(device)
+        return self._dev_table[key]
+
+    def device_group_b(self, device):
+        if self.src_group_b is None:
+            return None
+        key = "gb" + str(device)
+        if key not in self._dev_table:
+            self._dev_table[key] = _torch().from_numpy(self.src_group_b).to(device)
         return self._dev_table[key]
 
     def args(self, step_begin, step_end, table_ptr, group_b_ptr, wave_ld):
@@ -365,7 +374,7 @@ def tran(plan: Plan, params, x, setup: TranSetup, step_begin=0, step_end=None, w
     if iters_step is None and want_iters_step:
         iters_step = torch.zeros((setup.n_steps, B), dtype=torch.uint8, device=dev)
     table = setup.device_table(dev)
-    gb = setup.src_group_b
+    gb = setup.device_group_b(dev)
     a = setup.args(step_begin, step_end, table.data_ptr(), gb.data_ptr() if gb is not None else None,
                    wave.shape[2] if wave is not None else 0)
     _check(lib().csim_dev_tran(plan.handle, B, _ptr(params), C.byref(a), _ptr(x), _ptr(wave), _ptr(iters_total),
@@ -389,7 +398,7 @@ def sstate(plan: Plan, params, x, setup: TranSetup, steps_per_period: int, max_p
     periods = torch.empty((B,), dtype=torch.int32, device=dev)
     delta = torch.empty((B,), dtype=torch.float64, device=dev)
     table = setup.device_table(dev)
-    gb = setup.src_group_b
+    gb = setup.device_group_b(dev)
     a = setup.args(0, 0, table.data_ptr(), gb.data_ptr() if gb is not None else None, 0)
     ss = SstateArgsC(int(steps_per_period), int(max_periods), float(tol))
     _check(lib().csim_dev_sstate(plan.handle, B, _ptr(params), C.byref(a), C.byref(ss), _ptr(x), _ptr(periods),

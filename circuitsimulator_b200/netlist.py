@@ -143,6 +143,37 @@ class Netlist:
         out[lo:, mask] = self.params[mask] * (1.0 + rel * u[lo:, mask])
         return np.ascontiguousarray(out.T)
 
+    def sin_source_sweep(self, source_name: str, va_values, freq_values, n_steps: int, dt: float | None = None,
+                         out_stride: int = 1, probes=None):
+        """Sweep of one SIN source over amplitude x frequency (BASELINE config 4): instance b = ia*len(freq)+ifr
+        gets va = va_values[ia], freq = freq_values[ifr]; everything else nominal.  Frequencies need their own
+        host-tabulated sin rows, selected per instance through src_group_b.  Returns (params [P,B], TranSetup)."""
+        dt = self.tran["tstep"] if dt is None else dt
+        src = self.source_elems()
+        e = [k for k in src if self.elem_names[k].lower() == source_name.lower()]
+        if not e or not (self.elem_flags[e[0]] & capi.FLAG_SRC_SIN):
+            raise ValueError(f"{source_name}: not a SIN source of this netlist")
+        e = e[0]
+        s_idx = src.index(e)
+        po = int(self.elem_param[e])
+        va_values = np.asarray(va_values, np.float64)
+        freq_values = np.asarray(freq_values, np.float64)
+        B = va_values.size * freq_values.size
+        P = np.repeat(self.params[:, None], B, 1)
+        P[po + 2] = np.repeat(va_values, freq_values.size)
+        P[po + 3] = np.tile(freq_values, va_values.size)
+        mode, group, table = self.source_tables(dt, n_steps)
+        td, phi = self.params[po + 4], self.params[po + 5]
+        extra = np.stack([sin_table(f, td, phi, dt, n_steps) for f in freq_values])
+        g0 = table.shape[0]
+        table = np.ascontiguousarray(np.concatenate([table, extra], 0))
+        group_b = np.repeat(group[:, None].astype(np.int32), B, 1)
+        group_b[s_idx] = g0 + np.tile(np.arange(freq_values.size, dtype=np.int32), va_values.size)
+        probes = self.plot_probes if probes is None else probes
+        setup = capi.TranSetup(dt, n_steps, mode, group, table, probes, out_stride=out_stride,
+                               src_group_b=np.ascontiguousarray(group_b))
+        return np.ascontiguousarray(P), setup
+
     def steady_state(self, params, f0: float = 0.0, tstep: float = 0.0, max_periods: int = 20, tol: float = 1e-6):
         """runSteadyStateAnalysisBatch of the C++ host layer: params [P, B] -> dict of numpy arrays."""
         L = _hlib()

@@ -1,0 +1,106 @@
+"""GPU: BASELINE.json's configurations at (or near) full size — parity on subsets against per-instance
+oracle runs plus size-independent properties (a shard of a batch gives the bits the whole batch gives;
+instance 0 equals the golden nominal run; no status bits)."""
+import numpy as np
+import pytest
+
+from oracle import oraclelib as O
+from support import assert_same_bits, load_golden, n_steps_of
+
+pytestmark = pytest.mark.gpu
+SEED = 20261104
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    assert torch.cuda.is_available()
+    return torch
+
+
+def _topo_of(nl):
+    return O.Topology(nl.n_unknowns, nl.n_node_eq, nl.elem_type, nl.elem_flags, nl.elem_nodes, nl.elem_branch,
+                      nl.elem_param, nl.n_params, nl.params, nl.node_names, nl.elem_names)
+
+
+def test_config3_buffer_monte_carlo_65536(torch):
+    """tests/buffer.sp, 65,536 Monte-Carlo instances, full .TRAN."""
+    from circuitsimulator_b200 import capi
+    from circuitsimulator_b200.netlist import Netlist
+    g, _ = load_golden("buffer")
+    nl = Netlist(str(g["netlist"]))
+    topo = _topo_of(nl)
+    B, ns = 65536, n_steps_of(g)
+    assert ns == nl.n_steps == 300
+    P = nl.monte_carlo(B, SEED + 3)  # [P, B]
+    plan = nl.plan()
+    probes = np.arange(nl.n_unknowns, dtype=np.int32)
+    setup = nl.tran_setup(probes=probes, out_stride=10)  # every 10th point of every unknown: 13 x 30 doubles/instance
+    params = torch.from_numpy(P).cuda()
+    d = capi.dc(plan, params)
+    t = capi.tran(plan, params, d["x"].clone(), setup, pivot_hash=d["hash"].clone(), status=d["status"].clone())
+    torch.cuda.synchronize()
+    st = t["status"].cpu().numpy().astype(np.uint32)
+    assert not (st & (capi.ST_LU_SINGULAR | capi.ST_NONFINITE)).any()  # (DC_UNCONVERGED is the reference's own behaviour here)
+    wave = t["wave"].cpu().numpy()
+    assert np.isfinite(wave).all()
+    # instance 0 is the nominal circuit: equals the golden (reference-pinned) run
+    assert_same_bits(wave[0].T, g["wave"][9::10], "instance 0 vs golden")
+    # subset parity: first 128 + 128 random instances against the oracle, one instance at a time
+    rng = np.random.default_rng(1)
+    idx = np.concatenate([np.arange(128), rng.choice(np.arange(128, B), 128, replace=False)])
+    m, grp, tab = O.make_source_tables(topo, nl.params, setup.dt, ns)
+    hashes = t["hash"].cpu().numpy().view(np.uint64)
+    totals = t["iters_total"].cpu().numpy()
+    for b in idx:
+        od = O.dc(topo, P[:, b])
+        ot = O.tran(topo, P[:, b], setup.dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(wave[b].T, ot["wave"][9::10], f"instance {b}")
+        assert hashes[b] == np.uint64(ot["hash"]) and totals[b] == ot["total"]
+    # a shard run alone gives the bits the whole batch gave (no cross-instance coupling, any batch size)
+    lo, n = 40000, 1000
+    ps = params[:, lo:lo + n].contiguous()
+    d2 = capi.dc(plan, ps)
+    t2 = capi.tran(plan, ps, d2["x"].clone(), setup, pivot_hash=d2["hash"].clone(), status=d2["status"].clone())
+    assert_same_bits(t2["wave"].cpu().numpy(), wave[lo:lo + n], "shard vs whole batch")
+    assert np.array_equal(t2["hash"].cpu().numpy(), t["hash"][lo:lo + n].cpu().numpy())
+
+
+def test_config4_amplitude_frequency_sweep_per_instance_sources(torch):
+    """dbmixer.sp LO sweep (config 4's batch layout at 6 x 5 points): every instance has its own LO amplitude
+    (a parameter) and frequency (its own host-tabulated sin row, selected through src_group_b).  Transient
+    prefix and the steady-state driver against per-instance oracle runs."""
+    from circuitsimulator_b200 import capi
+    from circuitsimulator_b200.netlist import Netlist
+    g, _ = load_golden("dbmixer")
+    nl = Netlist(str(g["netlist"]))
+    topo = _topo_of(nl)
+    va = np.linspace(0.1, 1.0, 6)
+    fr = np.linspace(0.8e9, 1.0e9, 5)
+    ns = 240
+    probes = np.arange(nl.n_unknowns, dtype=np.int32)
+    P, setup = nl.sin_source_sweep("Vlo+", va, fr, ns, probes=probes)
+    B = P.shape[1]
+    assert B == 30 and setup.src_group_b.shape == (nl.n_sources, B)
+    plan = nl.plan()
+    params = torch.from_numpy(P).cuda()
+    d = capi.dc(plan, params)
+    t = capi.tran(plan, params, d["x"].clone(), setup, pivot_hash=d["hash"].clone(), status=d["status"].clone(),
+                  want_iters_step=True)
+    torch.cuda.synchronize()
+    wave = t["wave"].cpu().numpy()
+    for b in range(B):
+        m, grp, tab = O.make_source_tables(topo, P[:, b], setup.dt, ns)  # the oracle tabulates this instance's own sine
+        od = O.dc(topo, P[:, b])
+        ot = O.tran(topo, P[:, b], setup.dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(wave[b].T, ot["wave"], f"sweep point {b}")
+        assert np.array_equal(t["iters_step"][:, b].cpu().numpy(), ot["iters_step"])
+    assert not np.array_equal(wave[0], wave[1]) and not np.array_equal(wave[0], wave[5])  # both axes matter
+    # steady-state driver on the same batch (short "period" so the test stays small): composition check
+    spp, K = 60, 3
+    r = capi.sstate(plan, params, d["x"].clone(), setup, spp, K, 1e-3)
+    for b in (0, 7, 29):
+        m, grp, tab = O.make_source_tables(topo, P[:, b], setup.dt, ns)
+        o = O.sstate(topo, P[:, b], setup.dt, spp, K, 1e-3, m, grp, tab, O.dc(topo, P[:, b])["x"])
+        assert int(r["periods"][b]) == o["period"]
+        assert_same_bits(r["x"][:, b].cpu().numpy(), o["x"], f"sweep point {b} steady state")
