@@ -34,7 +34,7 @@ EXPORTS = [
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
-    "csim_dev_sstate", "csim_batch_sstate",
+    "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path",
 ]
 
 
@@ -183,6 +183,11 @@ class Plan:
     def jit_mode(self, mode: int):
         """0: generic kernels only; 1: automatic (default); 2: warp-per-instance; 3: thread-per-instance."""
         _check(lib().csim_plan_jit_mode(self.handle, int(mode)), "csim_plan_jit_mode")
+
+    def force_large_path(self, on: bool = True):
+        """Run this plan on the large-matrix (N > 32) kernels whatever its size."""
+        lib().csim_plan_force_large_path.argtypes = [C.c_void_p, C.c_int]
+        _check(lib().csim_plan_force_large_path(self.handle, int(bool(on))), "csim_plan_force_large_path")
 
     def specialize(self, perm):
         perm = _i32(perm)

@@ -95,6 +95,7 @@ struct csim_plan {
     mutable SpecState spec;
     mutable StampSpecState stamp_spec[2];
     mutable TpiState tpi;
+    bool force_big = false;
 };
 
 struct csim_batch {
@@ -485,13 +486,25 @@ int csim_plan_create(const csim_topology* topo, const csim_constants* consts, in
             CU(upload(mp.slot_entries, &dm.slot_entries, p->owned));
             std::vector<uint32_t> cw;
             std::vector<int32_t> cr;
-            for (const Contribution& c : mp.contribs) {
+            if (p->host.N <= 32) for (const Contribution& c : mp.contribs) {
                 cw.push_back(contrib_word(c.col >= 0 ? c.col : kRhsCol, c.sub != 0, c.value));
                 cr.push_back(c.row);
             }
             dm.n_contribs = (int)cw.size();
             CU(upload(cw, &dm.contrib_words, p->owned));
             CU(upload(cr, &dm.contrib_rows, p->owned));
+            std::vector<int32_t> srow, scol;
+            for (int i = 0; i < p->host.N; ++i)
+                for (int k = mp.rowptr[i]; k < mp.rowptr[i + 1]; ++k) {
+                    srow.push_back(i);
+                    scol.push_back(mp.colidx[k]);
+                }
+            for (int i = 0; i < p->host.N; ++i) {
+                srow.push_back(i);
+                scol.push_back(-1);
+            }
+            CU(upload(srow, &dm.slot_row, p->owned));
+            CU(upload(scol, &dm.slot_col, p->owned));
         }
     }
     *out = p.release();
@@ -538,9 +551,16 @@ static int need_device(const csim_plan* plan, const char* who) {
     if (e != cudaSuccess) return cuda_fail(e, "cudaSetDevice");
     return CSIM_OK;
 }
-static int need_small(const csim_plan* plan, const char* who) {
-    if (plan->host.N > 32)
-        return fail(CSIM_E_UNSUPPORTED, std::string(who) + ": N > 32 needs the large-matrix path (not in this build)");
+// N <= 32: warp / thread-per-instance kernels with the matrix on chip; larger systems (or force_big, a test
+// switch) take the large-matrix path of big_kernels.cu (matrix in HBM/L2, one warp per instance).
+static bool env_big() {
+    const char* e = std::getenv("CSIM_BIG");
+    return e && e[0] == '1';
+}
+static bool use_big(const csim_plan* plan) { return plan->host.N > 32 || plan->force_big || env_big(); }
+static int need_fits(const csim_plan* plan, const char* who) {
+    if (plan->host.N > kBigMaxN)
+        return fail(CSIM_E_UNSUPPORTED, std::string(who) + ": more than " + std::to_string(kBigMaxN) + " unknowns");
     return CSIM_OK;
 }
 
@@ -562,12 +582,13 @@ int csim_dev_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double*
 
 int csim_dev_lu_solve(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
                       int32_t* singular, double lu_eps, void* stream) {
-    if (n <= 0 || n > 32) return fail(CSIM_E_UNSUPPORTED, "csim_dev_lu_solve: 1 <= n <= 32 required");
+    if (n <= 0 || n > kBigMaxN) return fail(CSIM_E_UNSUPPORTED, "csim_dev_lu_solve: n out of range");
     if (B <= 0 || !A || !b || !x) return fail(CSIM_E_INVALID, "csim_dev_lu_solve: bad argument");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) return fail(CSIM_E_CUDA, "csim_dev_lu_solve: no CUDA device (no CPU fallback)");
-    CU(launch_lu_solve(n, B, A, b, x, perm, singular, lu_eps, (cudaStream_t)stream));
+    if (n > 32 || env_big()) CU(launch_lu_big(n, B, A, b, x, perm, singular, lu_eps, (cudaStream_t)stream));
+    else CU(launch_lu_solve(n, B, A, b, x, perm, singular, lu_eps, (cudaStream_t)stream));
     return CSIM_OK;
 }
 
@@ -575,9 +596,10 @@ int csim_dev_dc(const csim_plan* plan, int64_t B, const double* params, double* 
                 uint64_t* pivot_hash, uint32_t* status, void* stream) {
     int rc = need_device(plan, "csim_dev_dc");
     if (rc) return rc;
-    if ((rc = need_small(plan, "csim_dev_dc"))) return rc;
+    if ((rc = need_fits(plan, "csim_dev_dc"))) return rc;
     if (B <= 0 || !params || !x) return fail(CSIM_E_INVALID, "csim_dev_dc: bad argument");
-    CU(launch_dc(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
+    if (use_big(plan)) CU(launch_dc_big(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
+    else CU(launch_dc(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
     return CSIM_OK;
 }
 
@@ -586,13 +608,14 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
                   void* stream_v) {
     int rc = need_device(plan, "csim_dev_tran");
     if (rc) return rc;
-    if ((rc = need_small(plan, "csim_dev_tran"))) return rc;
+    if ((rc = need_fits(plan, "csim_dev_tran"))) return rc;
+    const bool big = use_big(plan);
     if (B <= 0 || !params || !a || !x) return fail(CSIM_E_INVALID, "csim_dev_tran: bad argument");
     const int ns = plan->host.n_sources;
     if (a->dt <= 0.0 || a->step_begin < 0 || a->step_end < a->step_begin)
         return fail(CSIM_E_INVALID, "csim_dev_tran: bad step range or dt");
-    if (a->n_probes < 0 || a->n_probes > 32 || (a->n_probes > 0 && (!a->probes || !wave || a->out_stride <= 0)))
-        return fail(CSIM_E_INVALID, "csim_dev_tran: bad probe specification (at most 32 probes)");
+    if (a->n_probes < 0 || (!big && a->n_probes > 32) || (a->n_probes > 0 && (!a->probes || !wave || a->out_stride <= 0)))
+        return fail(CSIM_E_INVALID, "csim_dev_tran: bad probe specification (at most 32 probes for N <= 32)");
     if (ns > 0 && (!a->src_mode || (!a->src_group && !a->src_group_b)))
         return fail(CSIM_E_INVALID, "csim_dev_tran: source modes/groups missing");
     bool uses_table = false;
@@ -615,7 +638,7 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
     }
     cudaStream_t stream = (cudaStream_t)stream_v;
     // small host-side descriptors -> stream-ordered device scratch
-    std::vector<int32_t> pack((size_t)2 * ns + 32, 0);
+    std::vector<int32_t> pack((size_t)2 * ns + 32 + (a->n_probes > 0 ? a->n_probes : 0), 0);
     for (int s = 0; s < ns; ++s) {
         pack[s] = a->src_mode[s];
         pack[ns + s] = a->src_group ? a->src_group[s] : 0;
@@ -641,8 +664,10 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
     T.probes = d_pack + 2 * ns;
     T.skip = g_tran_skip;
     cudaError_t e;
-    const int kind = spec_prepare(plan, B, params, x, a->dt, stream);
-    if (kind == 3) {
+    const int kind = big ? -1 : spec_prepare(plan, B, params, x, a->dt, stream);
+    if (big) {
+        e = launch_tran_big(plan->dev, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
+    } else if (kind == 3) {
         e = tpi_launch(plan, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
     } else if (kind == 2) {
         e = spec_launch(plan, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
@@ -943,7 +968,7 @@ int csim_host_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double
 
 int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
                        int32_t* singular, double lu_eps) {
-    if (n <= 0 || n > 32) return fail(CSIM_E_UNSUPPORTED, "csim_host_lu_solve: 1 <= n <= 32 required");
+    if (n <= 0 || n > kBigMaxN) return fail(CSIM_E_UNSUPPORTED, "csim_host_lu_solve: n out of range");
     if (B <= 0 || !A || !b || !x) return fail(CSIM_E_INVALID, "csim_host_lu_solve: bad argument");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
@@ -960,6 +985,12 @@ int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, d
     CU(cudaMemcpy(x, dx.p, sizeof(double) * (size_t)n * B, cudaMemcpyDeviceToHost));
     if (perm) CU(cudaMemcpy(perm, dp.p, sizeof(int32_t) * (size_t)n * B, cudaMemcpyDeviceToHost));
     if (singular) CU(cudaMemcpy(singular, ds.p, sizeof(int32_t) * (size_t)B, cudaMemcpyDeviceToHost));
+    return CSIM_OK;
+}
+
+int csim_plan_force_large_path(csim_plan* plan, int on) {
+    if (!plan) return fail(CSIM_E_INVALID, "csim_plan_force_large_path: null plan");
+    plan->force_big = on != 0;
     return CSIM_OK;
 }
 

@@ -18,8 +18,11 @@ struct DevMode {
     const uint32_t* slot_entries;  // contribution words per slot, reference order
     // every contribution in the reference's order: word = contrib_word(col | RHS, sub, value), row separately
     int32_t n_contribs, _pad;
-    const uint32_t* contrib_words;
+    const uint32_t* contrib_words;  // (N <= 32 only: the column field has 6 bits)
     const int32_t* contrib_rows;
+    // row / column of every slot (column -1: right-hand side), for the large-matrix path
+    const int32_t* slot_row;
+    const int32_t* slot_col;
 };
 
 struct DevPlan {

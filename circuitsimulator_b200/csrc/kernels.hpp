@@ -22,6 +22,17 @@ cudaError_t launch_tran(const DevPlan& P, const DevTran& T, int64_t B, const dou
                         int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status,
                         cudaStream_t stream);
 
+// large-matrix path (big_kernels.cu): any N whose per-warp vectors fit in shared memory (N <= ~1700)
+constexpr int kBigMaxN = 1536;
+cudaError_t launch_tran_big(const DevPlan& P, const DevTran& T, int64_t B, const double* params, double* x, double* wave,
+                            int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status,
+                            cudaStream_t stream);
+cudaError_t launch_dc_big(const DevPlan& P, int64_t B, const double* params, double* x, int32_t* iters,
+                          uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream);
+cudaError_t launch_lu_big(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                          int32_t* singular, double eps, cudaStream_t stream);
+size_t big_bytes_per_instance(int N, int n_values);
+
 cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double* x_prev, double tol, int period,
                                 uint8_t* skip, int32_t* periods, double* delta, unsigned long long* n_open,
                                 cudaStream_t stream);

@@ -201,6 +201,20 @@ class Netlist:
             raise capi.CsimError(L.csimh_last_error().decode(errors="replace"))
 
 
+def ladder_netlist(stages: int = 200, tstep: float = 1e-11, tstop: float = 2e-9) -> str:
+    """BASELINE config 5: a chain of `stages` CMOS inverters, each driving an R-C section,
+    written in the reference's netlist grammar.  Nodes: vdd, n0 (input), then o_i / n_{i+1} per stage;
+    N = 2*stages + 2 node equations + 2 branch equations (404 for 200 stages)."""
+    lines = ["* generated inverter / RC ladder", "VDD vdd 0 DC 3", "Vin n0 0 SIN 1.5 1.5 10e6 0"]
+    for i in range(stages):
+        lines += [f"MP{i} o{i} n{i} vdd p 30e-6 0.35e-6 1", f"MN{i} o{i} n{i} 0 n 10e-6 0.35e-6 2",
+                  f"R{i} o{i} n{i + 1} 100", f"C{i} n{i + 1} 0 10e-15"]
+    lines += [".MODEL 1 VT -0.75 MU 5e-2 COX 0.3e-4 LAMBDA 0.05 CJ0 4.0e-14",
+              ".MODEL 2 VT 0.83 MU 1.5e-1 COX 0.3e-4 LAMBDA 0.05 CJ0 4.0e-14",
+              f".PLOTNV n{stages}", f".TRAN {tstep:g} {tstop:g}"]
+    return "\n".join(lines) + "\n"
+
+
 def sin_table(freq, td, phi, dt, n_steps) -> np.ndarray:
     out = np.zeros(n_steps, np.float64)
     _hlib().csimh_sin_table(float(freq), float(td), float(phi), float(dt), int(n_steps), out.ctypes.data_as(C.c_void_p))

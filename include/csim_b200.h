@@ -184,6 +184,14 @@ int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* 
 int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_t* perm, char* out, int32_t cap);
 #endif
 
+/* Systems with more than 32 unknowns (the 200-stage ladder has 404) run on the large-matrix path:
+ * one warp per instance, the dense matrix in HBM/L2 (row- and column-major copies), the reference's
+ * partial pivoting with logical row exchanges and exact-zero skipping.  on != 0 forces that path for
+ * any N (used by the parity tests to run it on the small netlists); CSIM_BIG=1 does the same.    */
+#ifndef __CUDACC_RTC__
+int csim_plan_force_large_path(csim_plan* plan, int on);
+#endif
+
 /* The standalone assembly kernel (csim_dev_stamp_csr) is specialised the same way on first use
  * (straight-line code, every distinct input loaded once, values in registers); any N.
  * bytes_read / bytes_written: distinct input / output bytes ONE assembly of `mode` moves per
@@ -221,7 +229,7 @@ int csim_dev_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double*
 #endif
 
 /* Batched Solver::solveLinearSystemLU (include/solver.hpp:83-131) on dense
- * N x N systems, N <= 32: A [N*N][B] row-major over (i,j), b [N][B] ->
+ * N x N systems (N <= 32: matrix in shared memory; larger: the large-matrix path): A [N*N][B] row-major over (i,j), b [N][B] ->
  * x [N][B], perm [N][B] (perm[i] = original row now at position i,
  * solver.hpp:41-44,66), singular [B] (1 -> x is the zero vector).              */
 #ifndef __CUDACC_RTC__
