@@ -25,6 +25,9 @@ namespace csim {
 
 constexpr int kBigWarps = 4;      // instances per CTA
 constexpr int kBigFList = 64;     // rows eliminated per pass of one elimination step
+constexpr int kBigBatch = 8;      // independent 8-byte loads per lane issued before the first use (256 entries per batch)
+constexpr int kBigUList = 32 * kBigBatch;  // non-zero pivot-row entries compacted per pass (one batch of columns)
+constexpr int kBigPairs = 4;      // (row, column) updates per lane in flight at once
 
 struct BigWarp {  // per-warp shared memory
     int32_t* rowat;  // [N] position -> row
@@ -32,12 +35,14 @@ struct BigWarp {  // per-warp shared memory
     double* bs;      // [N] right-hand side by ROW (forward substitution is fused)
     double* xr;      // [N] raw solution
     double* xs;      // [N] Newton iterate
-    int32_t* frow;   // [kBigFList]
-    double* fval;    // [kBigFList]
+    int32_t* frow;   // [kBigFList] rows being eliminated in this pass
+    double* fval;    // [kBigFList] their multipliers
+    int32_t* ucol;   // [kBigUList] columns of the pivot row's non-zeros in the current batch of columns
+    double* uval;    // [kBigUList] their values
 };
 
 __host__ __device__ inline size_t big_warp_bytes(int N) {
-    return (size_t)N * (4 + 4 + 8 + 8 + 8) + (size_t)kBigFList * 12 + 64;
+    return (size_t)N * (4 + 4 + 8 + 8 + 8) + (size_t)(kBigFList + kBigUList) * 12 + 64;
 }
 
 __device__ __forceinline__ BigWarp big_carve(unsigned char* base, int N) {
@@ -47,10 +52,12 @@ __device__ __forceinline__ BigWarp big_carve(unsigned char* base, int N) {
     w.xr = d + N;
     w.xs = d + 2 * N;
     w.fval = d + 3 * N;
-    int32_t* q = reinterpret_cast<int32_t*>(d + 3 * N + kBigFList);
+    w.uval = d + 3 * N + kBigFList;
+    int32_t* q = reinterpret_cast<int32_t*>(d + 3 * N + kBigFList + kBigUList);
     w.rowat = q;
     w.pos = q + N;
     w.frow = q + 2 * N;
+    w.ucol = q + 2 * N + kBigFList;
     return w;
 }
 
@@ -123,16 +130,27 @@ __device__ bool big_lu_solve(const BigWarp& w, double* Ar, double* Ac, int32_t* 
         const double* colk = Ac + (size_t)k * N;
         double bestv = -1.0;  // larger |v| wins, then the lower position
         int bestpos = 0x7FFFFFFF;
-        for (int row = lane; row < N; row += 32) {
-            const int p = w.pos[row];
-            if (p < k) continue;
-            const double a = fabs(colk[row]);
-            // NaN never wins a '>' against the running maximum; a NaN already AT position k is never beaten
-            const bool nan = a != a;
-            const double key = nan ? (p == k ? CUDART_INF : -1.0) : a;
-            if (key > bestv || (key == bestv && p < bestpos)) {
-                bestv = key;
-                bestpos = p;
+        // kBigBatch independent loads per lane are in flight before the first compare: one memory latency per
+        // 32 * kBigBatch rows instead of one per 32 rows
+        for (int base = 0; base < N; base += 32 * kBigBatch) {
+            double v[kBigBatch];
+            int pp[kBigBatch];
+#pragma unroll
+            for (int c = 0; c < kBigBatch; ++c) {
+                const int row = base + c * 32 + lane;
+                pp[c] = row < N ? w.pos[row] : -1;
+                v[c] = pp[c] >= k ? colk[row] : 0.0;
+            }
+#pragma unroll
+            for (int c = 0; c < kBigBatch; ++c) {
+                if (pp[c] < k) continue;
+                const double a = fabs(v[c]);
+                // NaN never wins a '>' against the running maximum; a NaN already AT position k is never beaten
+                const double key = (a != a) ? (pp[c] == k ? CUDART_INF : -1.0) : a;
+                if (key > bestv || (key == bestv && pp[c] < bestpos)) {
+                    bestv = key;
+                    bestpos = pp[c];
+                }
             }
         }
 #pragma unroll
@@ -166,56 +184,106 @@ __device__ bool big_lu_solve(const BigWarp& w, double* Ar, double* Ac, int32_t* 
         const double pv = colk[prow];
         const double* rowk = Ar + (size_t)prow * N;
         const double bk = w.bs[prow];
-        // ---- rows below the pivot with a non-zero in column k, kBigFList at a time
-        int scan_from = 0;
-        while (scan_from < N) {
+        // ---- rows below the pivot with a non-zero in column k: (row, multiplier) list, kBigFList at a time;
+        //      then the pivot row, only columns whose entry is not exactly zero
+        int base = 0, c_next = 0;
+        double v[kBigBatch];
+        int pp[kBigBatch];
+        bool loaded = false;
+        while (base < N) {
             int n_f = 0;
-            int r0 = scan_from;
-            for (; r0 < N && n_f <= kBigFList - 32; r0 += 32) {
-                const int row = r0 + lane;
-                double a = 0.0;
-                bool take = false;
-                if (row < N && w.pos[row] > k) {
-                    a = colk[row];
-                    take = a != 0.0;  // f = 0 leaves the row unchanged (exact for finite data)
+            while (base < N && n_f <= kBigFList - 32) {
+                if (!loaded) {
+#pragma unroll
+                    for (int c = 0; c < kBigBatch; ++c) {
+                        const int row = base + c * 32 + lane;
+                        pp[c] = row < N ? w.pos[row] : -1;
+                        v[c] = pp[c] > k ? colk[row] : 0.0;
+                    }
+                    loaded = true;
+                    c_next = 0;
                 }
-                const unsigned mk = __ballot_sync(kFull, take);
-                if (take) {
-                    const int at = n_f + __popc(mk & ((1u << lane) - 1u));
-                    w.frow[at] = row;
-                    w.fval[at] = a / pv;  // solver.hpp:71
+#pragma unroll
+                for (int c = 0; c < kBigBatch; ++c) {
+                    if (c < c_next || n_f > kBigFList - 32) continue;  // (uniform across the warp)
+                    const bool take = pp[c] > k && v[c] != 0.0;  // f = 0 leaves the row unchanged (exact for finite data)
+                    const unsigned mk = __ballot_sync(kFull, take);
+                    if (take) {
+                        const int at = n_f + __popc(mk & ((1u << lane) - 1u));
+                        w.frow[at] = base + c * 32 + lane;
+                        w.fval[at] = v[c] / pv;  // solver.hpp:71
+                    }
+                    n_f += __popc(mk);
+                    c_next = c + 1;
                 }
-                n_f += __popc(mk);
+                if (c_next >= kBigBatch) {
+                    base += 32 * kBigBatch;
+                    loaded = false;
+                }
             }
-            scan_from = r0;
             __syncwarp();
             if (n_f == 0) continue;
-            // ---- pivot row, 32 columns at a time: only columns whose entry is not exactly zero
-            for (int j0 = k + 1; j0 < N; j0 += 32) {
-                const int j = j0 + lane;
-                const double u = j < N ? rowk[j] : 0.0;
-                if (__ballot_sync(kFull, u != 0.0) == 0u) continue;
-                const bool act = u != 0.0;
-                for (int t = 0; t < n_f; ++t) {
-                    const int row = w.frow[t];
-                    const size_t idx = (size_t)row * N + (act ? j : 0);
-                    double old = 1.0;
+            for (int j0 = k + 1; j0 < N; j0 += 32 * kBigBatch) {
+                // the pivot row's non-zeros in this batch of columns, compacted: (column, value) list
+                double u[kBigBatch];
+#pragma unroll
+                for (int c = 0; c < kBigBatch; ++c) {
+                    const int j = j0 + c * 32 + lane;
+                    u[c] = j < N ? rowk[j] : 0.0;
+                }
+                int n_u = 0;
+#pragma unroll
+                for (int c = 0; c < kBigBatch; ++c) {
+                    const bool act = u[c] != 0.0;
+                    const unsigned mk = __ballot_sync(kFull, act);
                     if (act) {
-                        old = Ar[idx];
-                        const double nv = d_sub(old, d_mul(w.fval[t], u));  // solver.hpp:74
-                        Ar[idx] = nv;
-                        Ac[(size_t)j * N + row] = nv;
+                        const int at = n_u + __popc(mk & ((1u << lane) - 1u));
+                        w.ucol[at] = j0 + c * 32 + lane;
+                        w.uval[at] = u[c];
                     }
-                    // an entry that was exactly zero may be new fill-in: log it for the clean-up
-                    const bool isnew = act && old == 0.0;
-                    const unsigned mk = __ballot_sync(kFull, isnew);
-                    if (mk) {
-                        const int at = n_fill + __popc(mk & ((1u << lane) - 1u));
-                        if (isnew && at < fill_cap) fill[at] = (int32_t)idx;
-                        n_fill += __popc(mk);
-                        if (n_fill > fill_cap) overflow = true;
+                    n_u += __popc(mk);
+                }
+                __syncwarp();
+                if (n_u == 0) continue;
+                // every (row, column) pair is a different matrix entry: a lane takes a pair, kBigPairs pairs per lane are
+                // loaded before the first is used (solver.hpp:74 per entry; the order between entries is free)
+                const int total = n_f * n_u;
+                for (int p0 = 0; p0 < total; p0 += 32 * kBigPairs) {
+                    double old[kBigPairs], prod[kBigPairs];
+                    int row[kBigPairs], col[kBigPairs];
+#pragma unroll
+                    for (int q = 0; q < kBigPairs; ++q) {
+                        const int p = p0 + q * 32 + lane;
+                        row[q] = -1;
+                        old[q] = 1.0;
+                        if (p < total) {
+                            const int t = p / n_u, c = p - t * n_u;
+                            row[q] = w.frow[t];
+                            col[q] = w.ucol[c];
+                            prod[q] = d_mul(w.fval[t], w.uval[c]);
+                            old[q] = Ar[(size_t)row[q] * N + col[q]];
+                        }
+                    }
+#pragma unroll
+                    for (int q = 0; q < kBigPairs; ++q) {
+                        if (p0 + q * 32 >= total) continue;  // (uniform)
+                        if (row[q] >= 0) {
+                            const double nv = d_sub(old[q], prod[q]);
+                            Ar[(size_t)row[q] * N + col[q]] = nv;
+                            Ac[(size_t)col[q] * N + row[q]] = nv;
+                        }
+                        // an entry that was exactly zero may be new fill-in: log it for the clean-up
+                        const bool isnew = old[q] == 0.0;
+                        const unsigned mk = __ballot_sync(kFull, isnew);
+                        if (mk) {
+                            const int at = n_fill + __popc(mk & ((1u << lane) - 1u));
+                            if (isnew && at < fill_cap) fill[at] = row[q] * N + col[q];
+                            n_fill += __popc(mk);
+                            if (n_fill > fill_cap) overflow = true;
+                        }
                     }
                 }
+                __syncwarp();
             }
             // forward substitution fused (solver.hpp:106-113): b_row -= f * b_pivot
             for (int t = lane; t < n_f; t += 32) w.bs[w.frow[t]] = d_sub(w.bs[w.frow[t]], d_mul(w.fval[t], bk));
@@ -248,15 +316,22 @@ __device__ bool big_lu_solve(const BigWarp& w, double* Ar, double* Ac, int32_t* 
         const int prow = w.rowat[i];
         const double* rowi = Ar + (size_t)prow * N;
         double sum = w.bs[prow];
-        for (int j0 = i + 1; j0 < N; j0 += 32) {
-            const int j = j0 + lane;
-            const double u = j < N ? rowi[j] : 0.0;
-            unsigned mk = __ballot_sync(kFull, u != 0.0);
-            while (mk) {
-                const int l = __ffs(mk) - 1;
-                mk &= mk - 1;
-                const double ul = __shfl_sync(kFull, u, l);
-                sum = d_sub(sum, d_mul(ul, w.xr[j0 + l]));
+        for (int j0 = i + 1; j0 < N; j0 += 32 * kBigBatch) {
+            double u[kBigBatch];
+#pragma unroll
+            for (int c = 0; c < kBigBatch; ++c) {
+                const int j = j0 + c * 32 + lane;
+                u[c] = j < N ? rowi[j] : 0.0;
+            }
+#pragma unroll
+            for (int c = 0; c < kBigBatch; ++c) {
+                unsigned mk = __ballot_sync(kFull, u[c] != 0.0);
+                while (mk) {
+                    const int l = __ffs(mk) - 1;
+                    mk &= mk - 1;
+                    const double ul = __shfl_sync(kFull, u[c], l);
+                    sum = d_sub(sum, d_mul(ul, w.xr[j0 + c * 32 + l]));
+                }
             }
         }
         const double diag = rowi[i];
