@@ -187,7 +187,7 @@ class Plan:
     def force_large_path(self, on: bool = True):
         """Run this plan on the large-matrix (N > 32) kernels whatever its size."""
         lib().csim_plan_force_large_path.argtypes = [C.c_void_p, C.c_int]
-        _check(lib().csim_plan_force_large_path(self.handle, int(bool(on))), "csim_plan_force_large_path")
+        _check(lib().csim_plan_force_large_path(self.handle, int(on)), "csim_plan_force_large_path")
 
     def specialize(self, perm):
         perm = _i32(perm)

@@ -95,7 +95,7 @@ struct csim_plan {
     mutable SpecState spec;
     mutable StampSpecState stamp_spec[2];
     mutable TpiState tpi;
-    bool force_big = false;
+    int force_big = 0;  // 0: by size; 1: large path (dense kernels); 2: large path (sparse-skipping warp kernels)
 };
 
 struct csim_batch {
@@ -552,12 +552,21 @@ static int need_device(const csim_plan* plan, const char* who) {
     return CSIM_OK;
 }
 // N <= 32: warp / thread-per-instance kernels with the matrix on chip; larger systems (or force_big, a test
-// switch) take the large-matrix path of big_kernels.cu (matrix in HBM/L2, one warp per instance).
+// switch) take the large-matrix path with the matrix in HBM/L2: the blocked dense kernels of dense_kernels.cu
+// (one CTA per instance; the default) or the sparse-skipping kernels of big_kernels.cu (one warp per instance;
+// CSIM_BIG_KIND=warp, force_big == 2, or N > kDenseMaxN).
 static bool env_big() {
     const char* e = std::getenv("CSIM_BIG");
     return e && e[0] == '1';
 }
+static bool env_big_warp() {
+    const char* e = std::getenv("CSIM_BIG_KIND");
+    return e && e[0] == 'w';
+}
 static bool use_big(const csim_plan* plan) { return plan->host.N > 32 || plan->force_big || env_big(); }
+static bool use_dense(const csim_plan* plan) {
+    return plan->force_big != 2 && !env_big_warp() && plan->host.N <= kDenseMaxN;
+}
 static int need_fits(const csim_plan* plan, const char* who) {
     if (plan->host.N > kBigMaxN)
         return fail(CSIM_E_UNSUPPORTED, std::string(who) + ": more than " + std::to_string(kBigMaxN) + " unknowns");
@@ -587,7 +596,9 @@ int csim_dev_lu_solve(int32_t n, int64_t B, const double* A, const double* b, do
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) return fail(CSIM_E_CUDA, "csim_dev_lu_solve: no CUDA device (no CPU fallback)");
-    if (n > 32 || env_big()) CU(launch_lu_big(n, B, A, b, x, perm, singular, lu_eps, (cudaStream_t)stream));
+    if ((n > 32 || env_big()) && n <= kDenseMaxN && !env_big_warp())
+        CU(launch_lu_dense(n, B, A, b, x, perm, singular, lu_eps, (cudaStream_t)stream));
+    else if (n > 32 || env_big()) CU(launch_lu_big(n, B, A, b, x, perm, singular, lu_eps, (cudaStream_t)stream));
     else CU(launch_lu_solve(n, B, A, b, x, perm, singular, lu_eps, (cudaStream_t)stream));
     return CSIM_OK;
 }
@@ -598,7 +609,9 @@ int csim_dev_dc(const csim_plan* plan, int64_t B, const double* params, double* 
     if (rc) return rc;
     if ((rc = need_fits(plan, "csim_dev_dc"))) return rc;
     if (B <= 0 || !params || !x) return fail(CSIM_E_INVALID, "csim_dev_dc: bad argument");
-    if (use_big(plan)) CU(launch_dc_big(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
+    if (use_big(plan) && use_dense(plan))
+        CU(launch_dc_dense(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
+    else if (use_big(plan)) CU(launch_dc_big(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
     else CU(launch_dc(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
     return CSIM_OK;
 }
@@ -665,7 +678,9 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
     T.skip = g_tran_skip;
     cudaError_t e;
     const int kind = big ? -1 : spec_prepare(plan, B, params, x, a->dt, stream);
-    if (big) {
+    if (big && use_dense(plan)) {
+        e = launch_tran_dense(plan->dev, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
+    } else if (big) {
         e = launch_tran_big(plan->dev, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
     } else if (kind == 3) {
         e = tpi_launch(plan, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
@@ -990,7 +1005,7 @@ int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, d
 
 int csim_plan_force_large_path(csim_plan* plan, int on) {
     if (!plan) return fail(CSIM_E_INVALID, "csim_plan_force_large_path: null plan");
-    plan->force_big = on != 0;
+    plan->force_big = on < 0 ? 0 : (on > 2 ? 1 : on);
     return CSIM_OK;
 }
 

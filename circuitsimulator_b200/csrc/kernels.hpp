@@ -33,6 +33,17 @@ cudaError_t launch_lu_big(int N, int64_t B, const double* A, const double* b, do
                           int32_t* singular, double eps, cudaStream_t stream);
 size_t big_bytes_per_instance(int N, int n_values);
 
+// large-matrix path, dense (dense_kernels.cu): one CTA per instance, blocked LU on [A | b] in HBM/L2; the default
+// for 32 < N <= kDenseMaxN (the 17-column panel of all N rows has to fit in shared memory)
+constexpr int kDenseMaxN = 1280;
+cudaError_t launch_tran_dense(const DevPlan& P, const DevTran& T, int64_t B, const double* params, double* x,
+                              double* wave, int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash,
+                              uint32_t* status, cudaStream_t stream);
+cudaError_t launch_dc_dense(const DevPlan& P, int64_t B, const double* params, double* x, int32_t* iters,
+                            uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream);
+cudaError_t launch_lu_dense(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                            int32_t* singular, double eps, cudaStream_t stream);
+
 cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double* x_prev, double tol, int period,
                                 uint8_t* skip, int32_t* periods, double* delta, unsigned long long* n_open,
                                 cudaStream_t stream);

@@ -89,8 +89,8 @@ __device__ __forceinline__ void eval_step(const DevMode& m, const double* xp, do
 
 // SourceSpec::evalDC (include/sim.hpp:152-158)
 __device__ __forceinline__ void eval_src_dc(const DevMode& m, const double* __restrict__ params, int64_t B, int64_t b,
-                                            double scale, double* vt, int lane) {
-    for (int i = lane; i < m.n_src; i += 32) {
+                                            double scale, double* vt, int lane, int stride = 32) {
+    for (int i = lane; i < m.n_src; i += stride) {
         SrcOp op = m.src_ops[i];
         double base = params[(int64_t)op.param * B + b];
         if (op.is_sin) base = d_add(base, params[(int64_t)(op.param + 1) * B + b]);

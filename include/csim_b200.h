@@ -184,10 +184,16 @@ int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* 
 int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_t* perm, char* out, int32_t cap);
 #endif
 
-/* Systems with more than 32 unknowns (the 200-stage ladder has 404) run on the large-matrix path:
- * one warp per instance, the dense matrix in HBM/L2 (row- and column-major copies), the reference's
- * partial pivoting with logical row exchanges and exact-zero skipping.  on != 0 forces that path for
- * any N (used by the parity tests to run it on the small netlists); CSIM_BIG=1 does the same.    */
+/* Systems with more than 32 unknowns (the 200-stage ladder has 404) run on the large-matrix path, the
+ * matrix in HBM/L2 and the reference's partial pivoting with logical row exchanges.  Two kernel families:
+ *   dense (default, N <= 1280): one CTA per instance, blocked right-looking LU on [A | b], 16-column panel
+ *     and a strip of U staged in shared memory, 4 x 4 register tiles for the trailing update, no zero
+ *     skipping (the ladder's factorisation is fully dense under the reference's unknown order);
+ *   warp (CSIM_BIG_KIND=warp, or N > 1280): one warp per instance, row- and column-major copies,
+ *     exact-zero skipping and a fill-in log (pays off only when the factorisation stays sparse).
+ * on = 1 forces the large path (dense kernels) for any N, on = 2 forces it with the warp kernels,
+ * on = 0 returns to the choice by size; CSIM_BIG=1 forces it process-wide (tests run the small
+ * netlists through it).                                                                             */
 #ifndef __CUDACC_RTC__
 int csim_plan_force_large_path(csim_plan* plan, int on);
 #endif

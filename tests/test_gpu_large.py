@@ -1,6 +1,8 @@
-"""GPU: the large-matrix path (big_kernels.cu; N > 32, matrix in HBM/L2) against the oracle — forced onto
-the two reference netlists, on generated inverter/RC ladders (BASELINE config 5's topology) and on dense
-random systems.  Same bar as everywhere: bit-identical doubles, Newton counts and pivot sequences."""
+"""GPU: the large-matrix path (N > 32, matrix in HBM/L2) against the oracle — both kernel families (dense:
+dense_kernels.cu, one CTA per instance, blocked LU; warp: big_kernels.cu, one warp per instance, zero
+skipping) forced onto the two reference netlists, on generated inverter/RC ladders (BASELINE config 5's
+topology) and on dense random systems.  Same bar as everywhere: bit-identical doubles, Newton counts and
+pivot sequences."""
 import numpy as np
 import pytest
 
@@ -48,20 +50,25 @@ def _run_and_compare(torch, capi, plan, topo, P, dt, ns, what, insts=None):
     return t
 
 
+DENSE, WARP = 1, 2  # csim_plan_force_large_path
+
+
+@pytest.mark.parametrize("kind", [DENSE, WARP])
 @pytest.mark.parametrize("name,B,ns", [("buffer", 10, None), ("dbmixer", 6, 150)])
-def test_large_path_forced_on_reference_netlists(torch, name, B, ns):
+def test_large_path_forced_on_reference_netlists(torch, name, B, ns, kind):
     from circuitsimulator_b200 import capi
     g, topo = load_golden(name)
     ns = ns or n_steps_of(g)
     P = perturb(topo.params, topo, B, 99)
     plan = make_plan(topo)
-    plan.force_large_path()
-    _run_and_compare(torch, capi, plan, topo, P, float(g["dt"]), ns, name + " (large path)")
+    plan.force_large_path(kind)
+    _run_and_compare(torch, capi, plan, topo, P, float(g["dt"]), ns, name + f" (large path, kind {kind})")
     assert not plan.spec_info()["active"]  # the on-chip kernels were never built
 
 
+@pytest.mark.parametrize("kind", [DENSE, WARP])
 @pytest.mark.parametrize("stages", [12, 20, 40])
-def test_inverter_ladder(torch, stages):
+def test_inverter_ladder(torch, stages, kind):
     """12 stages: N = 28, the on-chip path and the large path must agree with the oracle and with each other;
     20 / 40 stages: N = 44 / 84 > 32, only the large path applies."""
     from circuitsimulator_b200 import capi
@@ -75,22 +82,27 @@ def test_inverter_ladder(torch, stages):
     if stages == 12:
         a = _run_and_compare(torch, capi, plan, topo, P, nl.tran["tstep"], ns, "ladder-12 on chip")
         big = nl.plan()
-        big.force_large_path()
+        big.force_large_path(kind)
         b = _run_and_compare(torch, capi, big, topo, P, nl.tran["tstep"], ns, "ladder-12 large path")
         assert_same_bits(a["wave"].cpu().numpy(), b["wave"].cpu().numpy(), "on-chip vs large path")
     else:
+        plan.force_large_path(kind)
         _run_and_compare(torch, capi, plan, topo, P, nl.tran["tstep"], ns, f"ladder-{stages}", insts=(0, B - 1))
 
 
-@pytest.mark.parametrize("n", [33, 64, 100])
-def test_large_lu_solve_bit_exact(torch, n):
+@pytest.mark.parametrize("kind", ["dense", "warp"])
+@pytest.mark.parametrize("n", [33, 64, 100, 177])
+def test_large_lu_solve_bit_exact(torch, n, kind, monkeypatch):
     from circuitsimulator_b200 import capi
+    monkeypatch.setenv("CSIM_BIG_KIND", kind)
     rng = np.random.default_rng(n)
     B = 7
     A = rng.normal(size=(B, n, n))
     A[rng.random(size=A.shape) < 0.7] = 0.0  # sparse-ish: exercises zero skipping and fill-in logging
     for b in range(B):
         A[b] += np.diag(rng.normal(size=n))
+    A[5] = rng.normal(size=(n, n))  # fully dense
+    A[6, :, :] = np.round(A[6] * 2) / 2  # many exact ties in the pivot search: first maximum wins
     A[1, :, 3] = 0.0  # singular: zero vector (include/solver.hpp:94-97)
     A[2, 5, :] = A[2, 9, :]  # dependent rows: a pivot falls below eps (or rounds to something tiny)
     A[3, 0, 0] = 0.0  # forces a row exchange at the first step
