@@ -34,6 +34,23 @@ constexpr int kDnNB = 16;            // panel width
 constexpr int kDnLDP = kDnNB + 1;    // panel row stride in shared memory (odd: column reads are conflict-free)
 constexpr int kDnCW = 128;           // columns of U staged per pass (strip = kDnNB x kDnCW)
 constexpr int kDnRM = 4, kDnCN = 4;  // register tile of the trailing update: rows x columns per thread
+constexpr int kDnRB = 16;            // rows per block of the back substitution (kDnRB * (N + 1) <= N * kDnLDP)
+
+#ifdef CSIM_DN_PROF  // tools/dn_prof.cu: cycles per phase of dn_lu_solve, summed over CTAs (thread 0's clock)
+__device__ unsigned long long dn_prof[8];
+#define DN_T(i)                                  \
+    do {                                         \
+        if (tid == 0) {                          \
+            const long long t_ = clock64();      \
+            prof_acc[i] += t_ - prof_t;          \
+            prof_t = t_;                         \
+        }                                        \
+    } while (0)
+#else
+#define DN_T(i) \
+    do {        \
+    } while (0)
+#endif
 
 struct DnSmem {
     double* xs;      // [N] Newton iterate
@@ -85,6 +102,9 @@ __device__ __forceinline__ void dn_assemble(const DevMode& m, const double* vt, 
 // h updated.  Returns true when singular (uniform over the CTA).
 __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem& S, double eps, int tid, uint64_t& h) {
     const int lane = tid & 31, warp = tid >> 5;
+#ifdef CSIM_DN_PROF
+    long long prof_acc[6] = {0, 0, 0, 0, 0, 0}, prof_t = clock64();
+#endif
     for (int i = tid; i < N; i += kDnThreads) S.rowat[i] = i;
     __syncthreads();
     bool singular = false;
@@ -96,6 +116,7 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
             if (c < nb) S.Pn[r * kDnLDP + c] = A[(size_t)S.rowat[k0 + r] * LD + k0 + c];
         }
         __syncthreads();
+        DN_T(0);
         for (int kk = 0; kk < nb; ++kk) {
             // pivot search down column kk from the diagonal: first maximum in position order (solver.hpp:46-56)
             const double akk = fabs(S.Pn[kk * kDnLDP + kk]);
@@ -164,6 +185,7 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
             __syncthreads();
         }
         if (singular) break;
+        DN_T(1);
         // the U part of the panel's own rows goes back to the matrix (back substitution reads it)
         for (int e = tid; e < nb * kDnNB; e += kDnThreads) {
             const int t = e / kDnNB, c = e - t * kDnNB;
@@ -193,6 +215,7 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
                 }
             }
             __syncthreads();
+            DN_T(2);
             // trailing update: rows at positions >= k0+nb (only reached with a full panel, nb == kDnNB)
             const int tx = tid & 31, ty = tid >> 5;
             for (int p0 = k0 + nb; p0 < N; p0 += (kDnThreads / 32) * kDnRM) {
@@ -232,6 +255,7 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
                     }
             }
             __syncthreads();
+            DN_T(3);
         }
     }
     __syncthreads();  // (a singular break leaves the pivot-search slots still being read)
@@ -261,22 +285,41 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
         __syncthreads();
         return true;
     }
-    // ---- back substitution (solver.hpp:116-128): positions bottom-up; per row the products u(i,j) * x(j) are formed
-    //      by the whole CTA, the subtraction chain runs in ascending j on one thread (the reference's order)
-    double* prod = S.Pn;
-    for (int i = N - 1; i >= 0; --i) {
-        const double* rowi = A + (size_t)S.rowat[i] * LD;
-        for (int j = i + 1 + tid; j < N; j += kDnThreads) prod[j] = d_mul(rowi[j], S.xr[j]);
+    // ---- back substitution (solver.hpp:116-128): positions bottom-up, per row the subtraction chain runs in
+    //      ascending column order on one thread (the reference's order; the chain cannot start before x(i+1) is
+    //      known, so it is the critical path whatever the thread count).  Rows are taken kDnRB at a time: the
+    //      whole CTA loads them (one memory latency per block, coalesced) and pre-multiplies the columns whose
+    //      x is already known; the chain then runs out of shared memory.
+    double* Ub = S.Pn;  // [kDnRB][N + 1]
+    const int ldu = N + 1;
+    for (int hi = N - 1; hi >= 0; hi -= kDnRB) {
+        const int lo = hi - kDnRB + 1 > 0 ? hi - kDnRB + 1 : 0, nr = hi - lo + 1, ncol = N + 1 - lo;
+#pragma unroll 4
+        for (int e = tid; e < nr * ncol; e += kDnThreads) {
+            const int r = e / ncol, j = lo + (e - r * ncol);
+            double v = A[(size_t)S.rowat[lo + r] * LD + j];
+            if (j > hi && j < N) v = d_mul(v, S.xr[j]);
+            Ub[r * ldu + j] = v;
+        }
         __syncthreads();
         if (tid == 0) {
-            double sum = rowi[N];
+            for (int i = hi; i >= lo; --i) {
+                const double* u = Ub + (i - lo) * ldu;
+                double sum = u[N];
+                for (int j = i + 1; j <= hi; ++j) sum = d_sub(sum, d_mul(u[j], S.xr[j]));
 #pragma unroll 8
-            for (int j = i + 1; j < N; ++j) sum = d_sub(sum, prod[j]);
-            const double diag = rowi[i];
-            S.xr[i] = (fabs(diag) < 1e-15) ? 0.0 : sum / diag;
+                for (int j = hi + 1; j < N; ++j) sum = d_sub(sum, u[j]);
+                const double diag = u[i];
+                S.xr[i] = (fabs(diag) < 1e-15) ? 0.0 : sum / diag;
+            }
         }
         __syncthreads();
     }
+    DN_T(4);
+#ifdef CSIM_DN_PROF
+    if (tid == 0)
+        for (int i = 0; i < 5; ++i) atomicAdd(&dn_prof[i], (unsigned long long)prof_acc[i]);
+#endif
     return false;
 }
 
@@ -562,5 +605,9 @@ cudaError_t launch_lu_dense(int N, int64_t B, const double* A, const double* b, 
     dn_free(M, stream);
     return e;
 }
+
+#ifdef CSIM_DN_PROF
+cudaError_t dn_prof_read(unsigned long long* out) { return cudaMemcpyFromSymbol(out, dn_prof, sizeof(dn_prof)); }
+#endif
 
 }  // namespace csim
