@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """BASELINE.json config 5 at full size: generated 200-stage inverter/RC ladder (N = 404 unknowns),
-.TRAN 1e-11 2e-9 (200 steps), 4,096 Monte-Carlo instances, on the large-matrix path (big_kernels.cu).
+.TRAN 1e-11 2e-9 (200 steps), 4,096 Monte-Carlo instances, on the large-matrix path (dense_kernels.cu:
+one CTA per instance, blocked LU; CSIM_BIG_KIND=warp selects big_kernels.cu instead).
 The CPU side is the oracle's dense restatement on a bounded sample (O(N^3) per Newton iteration).
 Prints one JSON line.   usage: tools/run_config5.py [--stages 200] [--instances 4096] [--steps 0]"""
 import argparse
@@ -55,15 +56,20 @@ dc_solves = int(d["iters"].sum().item())
 N = nl.n_unknowns
 line = {
     "config": f"{args.stages}-stage inverter/RC ladder, N = {N}, {B} Monte-Carlo instances, {ns} steps of "
-              f"{setup.dt:g} s, large-matrix path (one warp per instance, matrix in HBM/L2)",
+              f"{setup.dt:g} s, large-matrix path ("
+              + ("warp per instance, zero skipping" if os.environ.get("CSIM_BIG_KIND", "").startswith("w")
+                 else "CTA per instance, blocked dense LU") + ", matrix in HBM/L2)",
     "dc_ms": dc_ms, "tran_ms": tran_ms, "instance_timepoints_per_s": B * ns / ((dc_ms + tran_ms) / 1e3),
     "tran_newton_iterations": newton, "dc_newton_iterations": dc_solves,
     "solves_per_s": (newton + dc_solves) / ((dc_ms + tran_ms) / 1e3),
-    "approx_matrix_bytes_scanned_per_solve": 8 * N * N * 3 // 2,
     "status_or": int(t["status"].max().item()),
-    "device_bytes_per_instance": 2 * N * N * 8,
 }
-line["approx_scan_GBps"] = line["solves_per_s"] * line["approx_matrix_bytes_scanned_per_solve"] / 1e9
+# FP64 pipe roofline of the dense factorisation: (N^3 - N)/3 multiply-subtract pairs per solve (the reference executes
+# exactly these; FMA is forbidden), against the measured 18.46 T separate mul/add per second (profiles/r1_microbench_fp64.txt)
+pairs = (N ** 3 - N) // 3
+line["roofline"] = {"kernel": "tran_dense_kernel / dc_dense_kernel", "bound": "fp64 pipe (separate mul and add, no FMA)",
+                    "achieved": line["solves_per_s"] * 2 * pairs / 1e12, "peak": 18.46, "unit": "Tflop/s",
+                    "frac": line["solves_per_s"] * 2 * pairs / 18.46e12, "pairs_per_solve": pairs}
 if args.cpu_steps > 0:
     from oracle import oraclelib as O
     topo = O.Topology(nl.n_unknowns, nl.n_node_eq, nl.elem_type, nl.elem_flags, nl.elem_nodes, nl.elem_branch,
