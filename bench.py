@@ -351,9 +351,19 @@ def run_ours(args):
     sinfo = plan.stamp_info(capi.MODE_TRAN, True)
     bytes_per_inst = sinfo["bytes_read"] + sinfo["bytes_written"]
     achieved = bytes_per_inst * Bs / (stamp_ms / 1e3) / 1e9
+    # dram bytes read + written per launch, from the committed ncu --set full capture of this kernel at this
+    # launch size (profiles/stamp_traffic.json, written by tools/stamp_traffic.py); null when it does not apply
+    traffic, traffic_src = None, None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "stamp_traffic.json")))
+        if sinfo["active"] and tj["netlist"] == args.netlist and int(tj["instances"]) == Bs:
+            traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
+    except Exception:
+        pass
     roofline = {"kernel": "csim_stamp_spec<TRAN>" if sinfo["active"] else "stamp_csr_kernel<TRAN>", "bound": "hbm",
                 "achieved": achieved, "peak": peaks["hbm_gbs"],
-                "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_kind": peak_kind,
+                "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_src,
+                "algorithmic_bytes_per_launch": bytes_per_inst * Bs, "peak_kind": peak_kind,
                 "bytes_per_instance": bytes_per_inst, "bytes_per_instance_survey_formula": 8 * (P + N + N + nnz + N),
                 "instances": Bs, "ms": stamp_ms,
                 "l2": "inputs+outputs %.2f GB > 126 MB L2" % (bytes_per_inst * Bs / 1e9)}
@@ -362,7 +372,9 @@ def run_ours(args):
     fl = symbolic_flops(nl, plan, capi, torch)
     newton_per_s = world * newton_total / (ms_step / 1e3)
     fp64_peak = 18.46  # Tflop/s, separate DMUL+DADD (FMA is not allowed on this path), measured: profiles/r1_microbench_fp64.txt
-    roofline_fused = {"kernel": "tran_kernel (+dc_kernel)", "bound": "fp64-latency",
+    fused_kind = plan.spec_info().get("kind", 0)
+    roofline_fused = {"kernel": {3: "csim_tran_tpi (NVRTC, thread per instance)", 2: "csim_tran_spec (NVRTC, warp per instance)"}
+                      .get(fused_kind, "tran_kernel (generic)") + " + dc_kernel", "bound": "fp64-latency",
                       "useful_tflops": newton_per_s / world * fl["useful"] / 1e12,
                       "dense_equiv_tflops": newton_per_s / world * fl["dense"] / 1e12,
                       "peak": fp64_peak, "unit": "TFLOP/s (separate mul/add, per GPU)",
