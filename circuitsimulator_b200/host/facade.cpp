@@ -8,6 +8,7 @@
 #include "../../include/csim_host.h"
 #include <algorithm>
 
+#include "csim/batchio.hpp"
 #include "csim/lower.hpp"
 #include "csim/sstateanalysis.hpp"
 #include "csim/parser.hpp"
@@ -188,6 +189,61 @@ int csimh_run_sstate(const csimh_netlist* h, int64_t B, const double* params, do
         put(R.delta, delta);
         put(R.iters_total, iters_total);
         return R.steps_per_period;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return -1;
+    }
+}
+
+int csimh_write_instance_csv(const csimh_netlist* h, const char* path, int64_t B, int64_t instance, int32_t n_probes,
+                             const int32_t* probes, int32_t n_steps, int32_t n_out, int32_t out_stride,
+                             const double* x_dc, const double* wave, const uint32_t* status) {
+    if (!h || !path || !wave || (n_probes > 0 && !probes) || instance < 0 || instance >= B) return -1;
+    try {
+        csim::BatchResult R;  // a one-instance view of the caller's batch
+        R.B = 1;
+        R.n_steps = n_steps;
+        R.n_probes = n_probes;
+        R.n_out = n_out;
+        if (x_dc) {
+            R.x_dc.resize(static_cast<std::size_t>(h->low.n_unknowns));
+            for (int32_t i = 0; i < h->low.n_unknowns; ++i)
+                R.x_dc[static_cast<std::size_t>(i)] = x_dc[static_cast<int64_t>(i) * B + instance];
+        }
+        const double* w = wave + static_cast<std::size_t>(instance) * n_probes * n_out;
+        R.wave.assign(w, w + static_cast<std::size_t>(n_probes) * n_out);
+        R.status.assign(1, status ? status[instance] : 0u);
+        csim::writeInstanceCsv(h->low, h->sim, R, std::vector<int32_t>(probes, probes + n_probes), out_stride, 0, path);
+        return 0;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return -1;
+    }
+}
+
+int csimh_n_dc_sweeps(const csimh_netlist* h) { return h ? static_cast<int>(h->sim.dcSweeps.size()) : -1; }
+
+int csimh_run_dc_sweep(const csimh_netlist* h, int32_t index, const double* base, int32_t cap_points, double* values,
+                       double* x, int32_t* iters, uint32_t* status) {
+    if (!h || index < 0 || index >= static_cast<int32_t>(h->sim.dcSweeps.size())) {
+        g_herr = "csimh_run_dc_sweep: no such .DC card";
+        return -1;
+    }
+    try {
+        const DCSweepConfig& sw = h->sim.dcSweeps[static_cast<std::size_t>(index)];
+        if (!values) {  // size query
+            if (!(sw.step != 0.0) || (sw.stop - sw.start) / sw.step < 0.0) throw std::runtime_error("invalid .DC range");
+            return static_cast<int>(std::floor((sw.stop - sw.start) / sw.step + 1e-9)) + 1;
+        }
+        std::vector<double> b = base ? std::vector<double>(base, base + h->low.n_params) : h->low.nominal;
+        csim::DcSweepResult R = csim::runDcSweepBatch(h->ckt, sw, b);
+        const int K = static_cast<int>(R.values.size());
+        if (K > cap_points) throw std::runtime_error("csimh_run_dc_sweep: output arrays too small");
+        std::memcpy(values, R.values.data(), R.values.size() * 8);
+        if (x) std::memcpy(x, R.x.data(), R.x.size() * 8);
+        if (iters) std::memcpy(iters, R.iters.data(), R.iters.size() * 4);
+        if (status) std::memcpy(status, R.status.data(), R.status.size() * 4);
+        return K;
     } catch (const std::exception& e) {
         g_herr = e.what();
         return -1;

@@ -17,11 +17,17 @@ def _hlib():
         L.csimh_parse.argtypes = [C.c_char_p]
         L.csimh_free.argtypes = [C.c_void_p]
         for name in ("csimh_dims", "csimh_topology", "csimh_node_name", "csimh_elem_name", "csimh_csv_header",
-                     "csimh_tran_cfg", "csimh_hb_cfg", "csimh_plot_probes", "csimh_run_tran_csv"):
+                     "csimh_tran_cfg", "csimh_hb_cfg", "csimh_plot_probes", "csimh_run_tran_csv",
+                     "csimh_write_instance_csv", "csimh_n_dc_sweeps", "csimh_run_dc_sweep"):
             getattr(L, name).restype = C.c_int
         L.csimh_tabulate_sources.argtypes = [C.c_void_p, C.c_double, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_void_p]
         L.csimh_sin_table.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, C.c_void_p]
+        L.csimh_write_instance_csv.argtypes = [C.c_void_p, C.c_char_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p,
+                                               C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.csimh_n_dc_sweeps.argtypes = [C.c_void_p]
+        L.csimh_run_dc_sweep.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p]
         L._csimh_ready = True
     return L
 
@@ -192,6 +198,51 @@ class Netlist:
         if spp < 0:
             raise capi.CsimError(L.csimh_last_error().decode(errors="replace"))
         out["steps_per_period"] = spp
+        return out
+
+    def csv_columns(self) -> np.ndarray:
+        """Equation indices in the reference's CSV column order (node rows, then V / L branch currents)."""
+        cols = list(range(self.n_node_eq))
+        cols += [int(self.elem_branch[e]) for e in range(self.n_elems)
+                 if int(self.elem_type[e]) in (capi.ELEM_V, capi.ELEM_L)]
+        return np.asarray(cols, np.int32)
+
+    def write_instance_csv(self, path: str, instance: int, setup: "capi.TranSetup", wave, x_dc=None, status=None):
+        """One instance of a batched transient in the reference's CSV layout (src/tanalisis.cpp:183-231): `wave`
+        [B][n_probes][n_out] and optionally `x_dc` [N][B] (the t = 0 row) and `status` [B], host arrays (numpy).
+        With setup.probes == csv_columns() and out_stride 1 the file is what the reference writes for that instance."""
+        wave = np.ascontiguousarray(wave, np.float64)
+        B, n_probes, n_out = wave.shape
+        probes = np.ascontiguousarray(setup.probes, np.int32)
+        assert probes.size == n_probes
+        vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        xd = None if x_dc is None else np.ascontiguousarray(x_dc, np.float64)
+        stt = None if status is None else np.ascontiguousarray(status, np.uint32)
+        L = _hlib()
+        if L.csimh_write_instance_csv(C.c_void_p(self._h), path.encode(), B, int(instance), n_probes, vp(probes),
+                                      int(setup.n_steps), n_out, int(setup.out_stride), vp(xd), vp(wave), vp(stt)) != 0:
+            raise capi.CsimError("csimh_write_instance_csv: " + L.csimh_last_error().decode(errors="replace"))
+
+    @property
+    def n_dc_sweeps(self) -> int:
+        return int(_hlib().csimh_n_dc_sweeps(C.c_void_p(self._h)))
+
+    def dc_sweep(self, index: int = 0, base=None) -> dict:
+        """The netlist's index-th `.DC src start stop step` card as one batch of DC operating points on the GPU
+        (runDcSweepBatch, include/csim/batchio.hpp): values [K], x [N][K], iters [ramp][K], status [K]."""
+        L = _hlib()
+        h = C.c_void_p(self._h)
+        K = L.csimh_run_dc_sweep(h, int(index), None, 0, None, None, None, None)
+        if K < 0:
+            raise capi.CsimError("csimh_run_dc_sweep: " + L.csimh_last_error().decode(errors="replace"))
+        ramp = capi.default_constants().dc_ramp_steps
+        out = {"values": np.zeros(K, np.float64), "x": np.zeros((self.n_unknowns, K), np.float64),
+               "iters": np.zeros((ramp, K), np.int32), "status": np.zeros(K, np.uint32)}
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        b = None if base is None else np.ascontiguousarray(base, np.float64)
+        if L.csimh_run_dc_sweep(h, int(index), None if b is None else vp(b), K, vp(out["values"]), vp(out["x"]),
+                                vp(out["iters"]), vp(out["status"])) != K:
+            raise capi.CsimError("csimh_run_dc_sweep: " + L.csimh_last_error().decode(errors="replace"))
         return out
 
     def run_reference_style_csv(self, path: str):

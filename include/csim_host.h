@@ -34,6 +34,18 @@ int csimh_run_tran_csv(const csimh_netlist* h, const char* path);
 int csimh_run_sstate(const csimh_netlist* h, int64_t B, const double* params, double f0, double tstep,
                      int32_t max_periods, double tol, double* x_dc, double* x, int32_t* periods, double* delta,
                      int32_t* iters_total);
+/* Row (f)1: one instance of a batched transient in the reference's CSV layout (csim::writeInstanceCsv,
+ * include/csim/batchio.hpp).  x_dc: [N][B] or NULL (no t = 0 row); wave: [B][n_probes][n_out]; status: [B] or NULL.
+ * Recorded rows are the last n_out multiples of out_stride among n_steps steps of the netlist's .TRAN tstep. */
+int csimh_write_instance_csv(const csimh_netlist* h, const char* path, int64_t B, int64_t instance, int32_t n_probes,
+                             const int32_t* probes, int32_t n_steps, int32_t n_out, int32_t out_stride,
+                             const double* x_dc, const double* wave, const uint32_t* status);
+/* Row (f)3: the netlist's index-th `.DC src start stop step` card as one batch of DC operating points
+ * (csim::runDcSweepBatch).  Returns the number of points K (also with NULL outputs, to size them), -1 on error.
+ * base: [P] parameters of every point or NULL for the nominal ones; values [K], x [N][K], iters [ramp][K], status [K]. */
+int csimh_n_dc_sweeps(const csimh_netlist* h);
+int csimh_run_dc_sweep(const csimh_netlist* h, int32_t index, const double* base, int32_t cap_points, double* values,
+                       double* x, int32_t* iters, uint32_t* status);
 #ifdef __cplusplus
 }
 #endif
