@@ -34,7 +34,7 @@ EXPORTS = [
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
-    "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path",
+    "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics",
 ]
 
 
@@ -410,6 +410,38 @@ def sstate(plan: Plan, params, x, setup: TranSetup, steps_per_period: int, max_p
                                  _ptr(delta), _ptr(iters_total), _ptr(pivot_hash), _ptr(status), _stream()),
            "csim_dev_sstate")
     return dict(x=x, periods=periods, delta=delta, iters_total=iters_total, hash=pivot_hash, status=status)
+
+
+def twiddle_tables(n_samples: int):
+    """cos/sin(2*pi*n/M) tabulated by the host layer with the host libm (csimh_twiddle_table)."""
+    c, s = np.zeros(n_samples, np.float64), np.zeros(n_samples, np.float64)
+    L = lib()
+    L.csimh_twiddle_table.argtypes = [C.c_int32, C.c_void_p, C.c_void_p]
+    if L.csimh_twiddle_table(int(n_samples), c.ctypes.data_as(C.c_void_p), s.ctypes.data_as(C.c_void_p)) != 0:
+        raise CsimError("csimh_twiddle_table failed")
+    return c, s
+
+
+def harmonics(wave, n_samples: int, n_harm: int, tables=None):
+    """csim_dev_harmonics over the LAST n_samples columns of every row of `wave` (device, [..., n_out], e.g. the
+    wave of csim_dev_tran with the last period recorded).  Returns (re, im), each [n_harm+1, *wave.shape[:-1]]."""
+    torch = _torch()
+    assert wave.is_cuda and wave.dtype == torch.float64 and wave.is_contiguous()
+    n_out = wave.shape[-1]
+    assert 0 < n_samples <= n_out
+    n_sig = wave.numel() // n_out
+    c, s = tables if tables is not None else twiddle_tables(n_samples)
+    ct, st = torch.from_numpy(c).to(wave.device), torch.from_numpy(s).to(wave.device)
+    re = torch.empty((n_harm + 1, n_sig), dtype=torch.float64, device=wave.device)
+    im = torch.empty_like(re)
+    L = lib()
+    L.csim_dev_harmonics.argtypes = [C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p]
+    first = wave.data_ptr() + 8 * (n_out - n_samples)
+    _check(L.csim_dev_harmonics(n_sig, int(n_samples), n_out, C.c_void_p(first), int(n_harm), _ptr(ct), _ptr(st),
+                                _ptr(re), _ptr(im), _stream()), "csim_dev_harmonics")
+    shape = (n_harm + 1,) + tuple(wave.shape[:-1])
+    return re.reshape(shape), im.reshape(shape)
 
 
 class Batch:

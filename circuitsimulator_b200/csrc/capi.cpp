@@ -1003,6 +1003,18 @@ int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, d
     return CSIM_OK;
 }
 
+int csim_dev_harmonics(int64_t n_signals, int32_t n_samples, int64_t ld, const double* samples, int32_t n_harm,
+                       const double* cos_tab, const double* sin_tab, double* re, double* im, void* stream) {
+    if (n_signals <= 0 || n_samples <= 0 || ld < n_samples || !samples || !cos_tab || !sin_tab || !re || !im)
+        return fail(CSIM_E_INVALID, "csim_dev_harmonics: bad argument");
+    if (n_harm < 0 || n_harm > kHarmonicsMax) return fail(CSIM_E_UNSUPPORTED, "csim_dev_harmonics: n_harm out of range (0..16)");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(CSIM_E_CUDA, "csim_dev_harmonics: no CUDA device (no CPU fallback)");
+    CU(launch_harmonics(n_signals, n_samples, ld, samples, n_harm, cos_tab, sin_tab, re, im, (cudaStream_t)stream));
+    return CSIM_OK;
+}
+
 int csim_plan_force_large_path(csim_plan* plan, int on) {
     if (!plan) return fail(CSIM_E_INVALID, "csim_plan_force_large_path: null plan");
     plan->force_big = on < 0 ? 0 : (on > 2 ? 1 : on);

@@ -361,6 +361,84 @@ cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double*
 }
 
 // =============================================================================
+// harmonic extraction over one period (row (f)2 of SURVEY 8: the `.hb f0 nharm` card's nHarm)
+// =============================================================================
+// X_h = (1/M) sum_{n<M} x[n] (c[(h n) mod M] - j s[(h n) mod M]),  h = 0..H, c/s tabulated on the host.
+// Summation order (part of the definition, include/csim_b200.h): lane l adds n = l, l+32, ... in ascending
+// order, each product and each sum separately rounded; the 32 partial sums are combined by the xor
+// butterfly 16, 8, 4, 2, 1; the result is divided by M.  One warp per 8 signals and 4 harmonics per pass: a
+// lane loads its sample of each of the 8 signals (coalesced 256-byte rows from HBM) and the 4 + 4 table values
+// of its sample index (L1/L2) before the first use, then does 64 multiply-adds; per signal the order of the
+// definition is untouched.
+static_assert(kHarmonicsMax == 16, "csim_b200.h documents n_harm <= 16");
+constexpr int kHarmSig = 8;   // signals per warp: one table value serves 8 samples
+constexpr int kHarmGrp = 4;   // harmonics per pass over the samples (H <= 3: one pass = 8 bytes of HBM per sample)
+
+__global__ void __launch_bounds__(128)
+harmonics_kernel(int64_t n_signals, int M, int64_t ld, const double* __restrict__ x, int H,
+                 const double* __restrict__ ct, const double* __restrict__ st, double* __restrict__ re,
+                 double* __restrict__ im) {
+    const int lane = threadIdx.x & 31;
+    const int64_t sig0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * kHarmSig;
+    if (sig0 >= n_signals) return;
+    const double* row[kHarmSig];
+#pragma unroll
+    for (int s = 0; s < kHarmSig; ++s) row[s] = x + (sig0 + s < n_signals ? sig0 + s : sig0) * ld;
+    for (int h0 = 0; h0 <= H; h0 += kHarmGrp) {
+        double ar[kHarmSig][kHarmGrp], ai[kHarmSig][kHarmGrp];
+        int idx[kHarmGrp], inc[kHarmGrp];
+#pragma unroll
+        for (int g = 0; g < kHarmGrp; ++g) {
+            idx[g] = (int)(((long long)(h0 + g) * lane) % M);
+            inc[g] = (int)(((long long)(h0 + g) * 32) % M);
+#pragma unroll
+            for (int s = 0; s < kHarmSig; ++s) ar[s][g] = ai[s][g] = 0.0;
+        }
+        for (int n = lane; n < M; n += 32) {
+            double v[kHarmSig], c[kHarmGrp], sn[kHarmGrp];
+#pragma unroll
+            for (int s = 0; s < kHarmSig; ++s) v[s] = row[s][n];  // all loads of the iteration first
+#pragma unroll
+            for (int g = 0; g < kHarmGrp; ++g) {
+                c[g] = ct[idx[g]];
+                sn[g] = st[idx[g]];
+                idx[g] += inc[g];
+                if (idx[g] >= M) idx[g] -= M;
+            }
+#pragma unroll
+            for (int s = 0; s < kHarmSig; ++s)
+#pragma unroll
+                for (int g = 0; g < kHarmGrp; ++g) {
+                    ar[s][g] = d_add(ar[s][g], d_mul(v[s], c[g]));
+                    ai[s][g] = d_add(ai[s][g], d_mul(v[s], sn[g]));
+                }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int s = 0; s < kHarmSig; ++s)
+#pragma unroll
+            for (int g = 0; g < kHarmGrp; ++g) {
+                double a = ar[s][g], b = ai[s][g];
+#pragma unroll
+                for (int t = 16; t >= 1; t >>= 1) {
+                    a = d_add(a, __shfl_xor_sync(kFull, a, t));
+                    b = d_add(b, __shfl_xor_sync(kFull, b, t));
+                }
+                if (lane == 0 && h0 + g <= H && sig0 + s < n_signals) {
+                    re[(int64_t)(h0 + g) * n_signals + sig0 + s] = a / (double)M;
+                    im[(int64_t)(h0 + g) * n_signals + sig0 + s] = -(b / (double)M);
+                }
+            }
+    }
+}
+
+cudaError_t launch_harmonics(int64_t n_signals, int M, int64_t ld, const double* x, int H, const double* ct,
+                             const double* st, double* re, double* im, cudaStream_t stream) {
+    harmonics_kernel<<<(unsigned)((n_signals + 4 * kHarmSig - 1) / (4 * kHarmSig)), 128, 0, stream>>>(n_signals, M, ld, x, H, ct, st, re, im);
+    return cudaGetLastError();
+}
+
+// =============================================================================
 // self-test of the split IEEE division used by the specialised kernels
 // =============================================================================
 __global__ void div_selftest_kernel(int64_t n, const double* __restrict__ a, const double* __restrict__ b,

@@ -48,6 +48,10 @@ cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double*
                                 uint8_t* skip, int32_t* periods, double* delta, unsigned long long* n_open,
                                 cudaStream_t stream);
 
+constexpr int kHarmonicsMax = 16;
+cudaError_t launch_harmonics(int64_t n_signals, int M, int64_t ld, const double* x, int H, const double* ct,
+                             const double* st, double* re, double* im, cudaStream_t stream);
+
 cudaError_t launch_div_selftest(int64_t n, const double* a, const double* b, double* q_split, double* q_ref,
                                 cudaStream_t stream);
 

@@ -221,6 +221,17 @@ int csimh_write_instance_csv(const csimh_netlist* h, const char* path, int64_t B
     }
 }
 
+// cos/sin(2*pi*n/M), n = 0..M-1, host libm (csim_dev_harmonics' tables)
+int csimh_twiddle_table(int32_t M, double* cos_out, double* sin_out) {
+    if (M <= 0 || !cos_out || !sin_out) return -1;
+    for (int32_t n = 0; n < M; ++n) {
+        const double a = 2.0 * M_PI * static_cast<double>(n) / static_cast<double>(M);
+        cos_out[n] = std::cos(a);
+        sin_out[n] = std::sin(a);
+    }
+    return 0;
+}
+
 int csimh_n_dc_sweeps(const csimh_netlist* h) { return h ? static_cast<int>(h->sim.dcSweeps.size()) : -1; }
 
 int csimh_run_dc_sweep(const csimh_netlist* h, int32_t index, const double* base, int32_t cap_points, double* values,

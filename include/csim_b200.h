@@ -198,6 +198,21 @@ int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_
 int csim_plan_force_large_path(csim_plan* plan, int on);
 #endif
 
+/* Harmonic extraction over one period (the `.hb f0 nharm` card the reference parses at
+ * src/parser.cpp:551-572 and never uses; row (f)2 of SURVEY 8).  For every signal (a row of n_samples
+ * doubles, row stride ld; e.g. the last period of one probe of one instance in csim_dev_tran's wave)
+ *     X_h = (1/M) * sum_{n=0}^{M-1} x[n] * (cos_tab[(h*n) mod M] - j * sin_tab[(h*n) mod M]),  h = 0..n_harm,
+ * M = n_samples, cos_tab/sin_tab [M] = cos/sin(2*pi*n/M) tabulated on the HOST (csimh_twiddle_table: host
+ * libm, like the source tables).  The amplitude of harmonic h >= 1 is 2*|X_h|, X_0 is the mean.
+ * Summation order (part of the definition): partial sum l (l = 0..31) adds the samples n = l, l+32, ... in
+ * ascending order, every product and sum separately rounded (no FMA); the 32 partial sums are combined
+ * pairwise by the xor butterfly with strides 16, 8, 4, 2, 1; then one division by M.
+ * re, im: [n_harm+1][n_signals] device.  n_harm <= 16.  The reference has no counterpart: parity unpinned. */
+#ifndef __CUDACC_RTC__
+int csim_dev_harmonics(int64_t n_signals, int32_t n_samples, int64_t ld, const double* samples, int32_t n_harm,
+                       const double* cos_tab, const double* sin_tab, double* re, double* im, void* stream);
+#endif
+
 /* The standalone assembly kernel (csim_dev_stamp_csr) is specialised the same way on first use
  * (straight-line code, every distinct input loaded once, values in registers); any N.
  * bytes_read / bytes_written: distinct input / output bytes ONE assembly of `mode` moves per

@@ -44,6 +44,8 @@ int csimh_write_instance_csv(const csimh_netlist* h, const char* path, int64_t B
  * (csim::runDcSweepBatch).  Returns the number of points K (also with NULL outputs, to size them), -1 on error.
  * base: [P] parameters of every point or NULL for the nominal ones; values [K], x [N][K], iters [ramp][K], status [K]. */
 int csimh_n_dc_sweeps(const csimh_netlist* h);
+/* cos/sin(2*pi*n/M), n = 0..M-1, with the host libm: the tables csim_dev_harmonics takes */
+int csimh_twiddle_table(int32_t M, double* cos_out, double* sin_out);
 int csimh_run_dc_sweep(const csimh_netlist* h, int32_t index, const double* base, int32_t cap_points, double* values,
                        double* x, int32_t* iters, uint32_t* status);
 #ifdef __cplusplus

@@ -320,6 +320,33 @@ def sstate(topo: Topology, params, dt, steps_per_period, max_periods, tol, src_m
 
 # -------------------------------------------------------------- reference API
 
+def harmonics(x, n_harm: int, cos_tab, sin_tab):
+    """CPU restatement of csim_dev_harmonics' definition (include/csim_b200.h) for ONE signal x[M]: 32 lane-strided
+    partial sums in ascending n with separately rounded products and sums, xor butterfly 16..1, division by M.
+    The reference has no harmonic extraction (its .hb card is parsed and unused): parity unpinned."""
+    x = np.asarray(x, np.float64)
+    M = x.size
+    rows = (M + 31) // 32
+    xp = np.zeros(rows * 32, np.float64)
+    xp[:M] = x
+    valid = (np.arange(rows * 32) < M).reshape(rows, 32)
+    xp = xp.reshape(rows, 32)
+    n = np.arange(rows * 32, dtype=np.int64).reshape(rows, 32)
+    re, im = np.zeros(n_harm + 1), np.zeros(n_harm + 1)
+    for h in range(n_harm + 1):
+        idx = (h * n) % M
+        pc, ps = xp * cos_tab[idx], xp * sin_tab[idx]
+        ar, ai = np.zeros(32), np.zeros(32)
+        for r in range(rows):  # lanes past the end of the signal add nothing (the kernel skips them)
+            ar = np.where(valid[r], ar + pc[r], ar)
+            ai = np.where(valid[r], ai + ps[r], ai)
+        for s in (16, 8, 4, 2, 1):
+            ar = ar + ar[np.arange(32) ^ s]
+            ai = ai + ai[np.arange(32) ^ s]
+        re[h], im[h] = ar[0] / M, -(ai[0] / M)
+    return re, im
+
+
 class Ref:
     """The unmodified reference (oracle/_ref) on one netlist text."""
 

@@ -63,3 +63,41 @@ def test_dc_sweep_points_equal_oracle(torch):
         assert_same_bits(r["x"][:, k], od["x"], f"sweep point {k}")
         assert np.array_equal(r["iters"][:, k], od["iters"]) and int(r["status"][k]) == od["status"]
     assert not np.array_equal(r["x"][:, 0], r["x"][:, K - 1])
+
+
+def test_harmonics_match_definition_and_dft(torch):
+    """csim_dev_harmonics against the CPU restatement of its definition (bit for bit) and against numpy's FFT
+    (to rounding), on the last period of buffer.sp's probes (Vin is a 10 MHz sine: T = 100 steps of 1 ns)."""
+    from circuitsimulator_b200 import capi
+    from circuitsimulator_b200.netlist import Netlist
+    g, _ = load_golden("buffer")
+    nl = Netlist(str(g["netlist"]))
+    B, spp, H = 5, 100, 4
+    P = nl.monte_carlo(B, 3)
+    setup = nl.tran_setup(probes=nl.csv_columns()[:6])
+    plan = nl.plan()
+    params = torch.from_numpy(P).cuda()
+    d = capi.dc(plan, params)
+    t = capi.tran(plan, params, d["x"].clone(), setup)
+    tables = capi.twiddle_tables(spp)
+    assert np.allclose(tables[0], np.cos(2 * np.pi * np.arange(spp) / spp), atol=1e-15)
+    re, im = capi.harmonics(t["wave"], spp, H, tables)
+    torch.cuda.synchronize()
+    wave = t["wave"].cpu().numpy()
+    re, im = re.cpu().numpy(), im.cpu().numpy()
+    assert re.shape == (H + 1, B, 6)
+    for b in (0, 4):
+        for p in range(6):
+            x = wave[b, p, -spp:]
+            ore, oim = O.harmonics(x, H, *tables)
+            assert_same_bits(re[:, b, p], ore, f"re inst {b} probe {p}")
+            assert_same_bits(im[:, b, p], oim, f"im inst {b} probe {p}")
+            F = np.fft.fft(x)[: H + 1] / spp
+            assert np.allclose(re[:, b, p], F.real, atol=1e-12) and np.allclose(im[:, b, p], F.imag, atol=1e-12)
+    # ragged length (not a multiple of 32, shorter than one unrolled pass) and the n_harm limit
+    re2, im2 = capi.harmonics(t["wave"], 37, 2)
+    ore, oim = O.harmonics(wave[1, 2, -37:], 2, *capi.twiddle_tables(37))
+    assert_same_bits(re2[:, 1, 2].cpu().numpy(), ore, "ragged re")
+    assert_same_bits(im2[:, 1, 2].cpu().numpy(), oim, "ragged im")
+    with pytest.raises(capi.CsimError):
+        capi.harmonics(t["wave"], spp, 17)
