@@ -307,8 +307,24 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
                 const double* u = Ub + (i - lo) * ldu;
                 double sum = u[N];
                 for (int j = i + 1; j <= hi; ++j) sum = d_sub(sum, d_mul(u[j], S.xr[j]));
-#pragma unroll 8
-                for (int j = hi + 1; j < N; ++j) sum = d_sub(sum, u[j]);
+                // the long part of the chain: 8 values are loaded while the previous 8 are being subtracted, so the
+                // loop runs at the latency of the dependent subtraction, not of shared memory
+                int j = hi + 1;
+                double nx[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) nx[q] = (j + q < N) ? u[j + q] : 0.0;
+                for (; j + 8 <= N; j += 8) {
+                    double cu[8];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) cu[q] = nx[q];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) nx[q] = (j + 8 + q < N) ? u[j + 8 + q] : 0.0;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) sum = d_sub(sum, cu[q]);
+                }
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    if (j + q < N) sum = d_sub(sum, nx[q]);
                 const double diag = u[i];
                 S.xr[i] = (fabs(diag) < 1e-15) ? 0.0 : sum / diag;
             }

@@ -42,3 +42,19 @@ def test_dc_sweep_card_is_parsed():
     g, _ = load_golden("buffer")
     nl = Netlist(str(g["netlist"]) + "\n.DC Vin 0 3 0.25\n")
     assert nl.n_dc_sweeps == 1 and Netlist(str(g["netlist"])).n_dc_sweeps == 0
+
+
+def test_oracle_harmonics_restatement_is_a_dft():
+    """oracle.harmonics (the CPU statement of csim_dev_harmonics' summation order) equals numpy's FFT to rounding,
+    for lengths that are and are not multiples of 32; the host twiddle tables are cos/sin(2*pi*n/M)."""
+    from circuitsimulator_b200 import capi
+    from oracle import oraclelib as O
+    rng = np.random.default_rng(5)
+    for M in (100, 37, 256):
+        c, s = capi.twiddle_tables(M)
+        assert np.allclose(c, np.cos(2 * np.pi * np.arange(M) / M), atol=1e-15)
+        assert np.allclose(s, np.sin(2 * np.pi * np.arange(M) / M), atol=1e-15)
+        x = rng.normal(size=M)
+        re, im = O.harmonics(x, 5, c, s)
+        F = np.fft.fft(x)[:6] / M
+        assert np.allclose(re, F.real, atol=1e-13) and np.allclose(im, F.imag, atol=1e-13)
