@@ -34,7 +34,7 @@ EXPORTS = [
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
-    "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics",
+    "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
 ]
 
 
@@ -410,6 +410,22 @@ def sstate(plan: Plan, params, x, setup: TranSetup, steps_per_period: int, max_p
                                  _ptr(delta), _ptr(iters_total), _ptr(pivot_hash), _ptr(status), _stream()),
            "csim_dev_sstate")
     return dict(x=x, periods=periods, delta=delta, iters_total=iters_total, hash=pivot_hash, status=status)
+
+
+def gauss_seidel(A, b, x0=None, max_iters: int = 1000, tol: float = 1e-10):
+    """csim_dev_gauss_seidel: A [n*n, B], b [n, B] (device, instance-minor).  Returns (x [n, B], sweeps [B])."""
+    torch = _torch()
+    n, B = b.shape
+    _dev_f64(A, (n * n, B))
+    _dev_f64(b, (n, B))
+    x = torch.zeros_like(b) if x0 is None else x0.clone()
+    sweeps = torch.empty((B,), dtype=torch.int32, device=b.device)
+    L = lib()
+    L.csim_dev_gauss_seidel.argtypes = [C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double,
+                                        C.c_void_p, C.c_void_p]
+    _check(L.csim_dev_gauss_seidel(int(n), int(B), _ptr(A), _ptr(b), _ptr(x), int(max_iters), float(tol), _ptr(sweeps),
+                                   _stream()), "csim_dev_gauss_seidel")
+    return x, sweeps
 
 
 def twiddle_tables(n_samples: int):

@@ -1003,6 +1003,37 @@ int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, d
     return CSIM_OK;
 }
 
+int csim_dev_gauss_seidel(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t max_iters,
+                          double tol, int32_t* sweeps, void* stream) {
+    if (n <= 0 || n > kGaussSeidelMaxN) return fail(CSIM_E_UNSUPPORTED, "csim_dev_gauss_seidel: n out of range (1..200)");
+    if (B <= 0 || !A || !b || !x || max_iters < 0) return fail(CSIM_E_INVALID, "csim_dev_gauss_seidel: bad argument");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(CSIM_E_CUDA, "csim_dev_gauss_seidel: no CUDA device (no CPU fallback)");
+    CU(launch_gauss_seidel(n, B, A, b, x, max_iters, tol, sweeps, (cudaStream_t)stream));
+    return CSIM_OK;
+}
+
+int csim_host_gauss_seidel(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t max_iters,
+                           double tol, int32_t* sweeps) {
+    if (n <= 0 || n > kGaussSeidelMaxN) return fail(CSIM_E_UNSUPPORTED, "csim_host_gauss_seidel: n out of range (1..200)");
+    if (B <= 0 || !A || !b || !x) return fail(CSIM_E_INVALID, "csim_host_gauss_seidel: bad argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(CSIM_E_CUDA, "csim_host_gauss_seidel: no CUDA device (no CPU fallback)");
+    DevBuf dA, db, dx, ds;
+    CU(dA.put(A, sizeof(double) * (size_t)n * n * B));
+    CU(db.put(b, sizeof(double) * (size_t)n * B));
+    CU(dx.put(x, sizeof(double) * (size_t)n * B));
+    CU(ds.put(nullptr, sizeof(int32_t) * (size_t)B));
+    int rc = csim_dev_gauss_seidel(n, B, dA.as<double>(), db.as<double>(), dx.as<double>(), max_iters, tol,
+                                   ds.as<int32_t>(), nullptr);
+    if (rc) return rc;
+    CU(cudaMemcpy(x, dx.p, sizeof(double) * (size_t)n * B, cudaMemcpyDeviceToHost));
+    if (sweeps) CU(cudaMemcpy(sweeps, ds.p, sizeof(int32_t) * (size_t)B, cudaMemcpyDeviceToHost));
+    return CSIM_OK;
+}
+
 int csim_dev_harmonics(int64_t n_signals, int32_t n_samples, int64_t ld, const double* samples, int32_t n_harm,
                        const double* cos_tab, const double* sin_tab, double* re, double* im, void* stream) {
     if (n_signals <= 0 || n_samples <= 0 || ld < n_samples || !samples || !cos_tab || !sin_tab || !re || !im)

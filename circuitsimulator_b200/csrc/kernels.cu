@@ -361,6 +361,73 @@ cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double*
 }
 
 // =============================================================================
+// Solver::solveLinearSystemGaussSeidel (include/solver.hpp:139-192), batched: row (f)4 of SURVEY 8
+// =============================================================================
+// A sweep is one sequential chain under the reference's order (row i subtracts a(i,j) x(j) for ascending j, the
+// newest x for j < i), so the parallelism is across systems only: one THREAD per system, the two iterates in
+// shared memory at [j][tid] (conflict-free), the matrix streamed from HBM/L2 every sweep (instance-minor:
+// consecutive threads read consecutive addresses).  ||x - xOld||_2 in the order of oracle/csim_norm2.h.
+constexpr int kGsThreads = 64;
+
+__global__ void __launch_bounds__(kGsThreads)
+gauss_seidel_kernel(int n, int64_t B, const double* __restrict__ A, const double* __restrict__ rhs,
+                    double* __restrict__ xio, int max_iters, double tol, int32_t* __restrict__ sweeps) {
+    extern __shared__ double gs_sm[];
+    const int tid = threadIdx.x;
+    const int64_t b = (int64_t)blockIdx.x * kGsThreads + tid;
+    if (b >= B) return;
+    double* x = gs_sm + tid;                          // x[j] at x[j * kGsThreads]
+    double* xo = gs_sm + (size_t)n * kGsThreads + tid;
+    for (int j = 0; j < n; ++j) x[j * kGsThreads] = xio[(int64_t)j * B + b];
+    const double diagEps = 1e-12;  // solver.hpp:160
+    int done = 0;
+    for (int iter = 0; iter < max_iters; ++iter) {  // solver.hpp:162
+        for (int j = 0; j < n; ++j) xo[j * kGsThreads] = x[j * kGsThreads];
+        for (int i = 0; i < n; ++i) {
+            const double* row = A + (int64_t)i * n * B + b;
+            double diag = row[(int64_t)i * B];
+            if (fabs(diag) < diagEps) diag = (diag >= 0.0 ? 1.0 : -1.0) * diagEps;  // solver.hpp:169-173
+            double sum = rhs[(int64_t)i * B + b];
+#pragma unroll 4
+            for (int j = 0; j < i; ++j) sum = d_sub(sum, d_mul(row[(int64_t)j * B], x[j * kGsThreads]));
+#pragma unroll 4
+            for (int j = i + 1; j < n; ++j) sum = d_sub(sum, d_mul(row[(int64_t)j * B], xo[j * kGsThreads]));
+            x[i * kGsThreads] = sum / diag;
+        }
+        // || x - xOld ||_2: 32 leaves (element k goes to leaf k mod 32, ascending k), then the pairwise tree
+        // 16, 8, 4, 2, 1 — leaf 0's path, evaluated by this one thread
+        double leaf[32];
+#pragma unroll
+        for (int l = 0; l < 32; ++l) {
+            double acc = 0.0;
+            for (int k = l; k < n; k += 32) {
+                const double d = d_sub(x[k * kGsThreads], xo[k * kGsThreads]);
+                acc = d_add(acc, d_mul(d, d));
+            }
+            leaf[l] = acc;
+        }
+#pragma unroll
+        for (int s = 16; s >= 1; s >>= 1)
+#pragma unroll
+            for (int l = 0; l < s; ++l) leaf[l] = d_add(leaf[l], leaf[l + s]);
+        done = iter + 1;
+        if (sqrt(leaf[0]) < tol) break;  // solver.hpp:188-192
+    }
+    for (int j = 0; j < n; ++j) xio[(int64_t)j * B + b] = x[j * kGsThreads];
+    if (sweeps) sweeps[b] = done;
+}
+
+cudaError_t launch_gauss_seidel(int n, int64_t B, const double* A, const double* rhs, double* x, int max_iters,
+                                double tol, int32_t* sweeps, cudaStream_t stream) {
+    const size_t smem = (size_t)2 * n * kGsThreads * sizeof(double);
+    cudaError_t e = cudaFuncSetAttribute(gauss_seidel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    gauss_seidel_kernel<<<(unsigned)((B + kGsThreads - 1) / kGsThreads), kGsThreads, smem, stream>>>(
+        n, B, A, rhs, x, max_iters, tol, sweeps);
+    return cudaGetLastError();
+}
+
+// =============================================================================
 // harmonic extraction over one period (row (f)2 of SURVEY 8: the `.hb f0 nharm` card's nHarm)
 // =============================================================================
 // X_h = (1/M) sum_{n<M} x[n] (c[(h n) mod M] - j s[(h n) mod M]),  h = 0..H, c/s tabulated on the host.

@@ -48,6 +48,10 @@ cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double*
                                 uint8_t* skip, int32_t* periods, double* delta, unsigned long long* n_open,
                                 cudaStream_t stream);
 
+constexpr int kGaussSeidelMaxN = 200;  // two iterates of n doubles for 64 systems per CTA in shared memory
+cudaError_t launch_gauss_seidel(int n, int64_t B, const double* A, const double* rhs, double* x, int max_iters,
+                                double tol, int32_t* sweeps, cudaStream_t stream);
+
 constexpr int kHarmonicsMax = 16;
 cudaError_t launch_harmonics(int64_t n_signals, int M, int64_t ld, const double* x, int H, const double* ct,
                              const double* st, double* re, double* im, cudaStream_t stream);

@@ -63,9 +63,27 @@ VectorXd solveLinearSystemLU(const MatrixXd& A, const VectorXd& b) {
     return x;
 }
 
-VectorXd solveLinearSystemGaussSeidel(const MatrixXd&, const VectorXd&, const VectorXd&, int, double) {
-    throw std::runtime_error("Solver::solveLinearSystemGaussSeidel: not implemented on the device "
-                             "(off the reference's default path; SURVEY.md §8(f) rank 4)");
+// include/solver.hpp:139-192 of the reference, one system on the device (csim_host_gauss_seidel); same dimension
+// checks and messages; systems with more than 200 unknowns are refused (CSIM_E_UNSUPPORTED -> exception).
+VectorXd solveLinearSystemGaussSeidel(const MatrixXd& A, const VectorXd& b, const VectorXd& x0, int maxIters, double tol) {
+    const int n = static_cast<int>(A.rows());
+    VectorXd x = x0;
+    if (n == 0) return x;
+    if (A.cols() != n || b.size() != n) {
+        std::cerr << "Gauss-Seidel: dimension mismatch.\n";
+        return VectorXd::Zero(std::max(n, 0));
+    }
+    if (x.size() != n) x = VectorXd::Zero(n);
+    std::vector<double> a(static_cast<std::size_t>(n) * n), rhs(n), sol(n);
+    for (int i = 0; i < n; ++i) {
+        rhs[i] = b(i);
+        sol[i] = x(i);
+        for (int j = 0; j < n; ++j) a[static_cast<std::size_t>(i) * n + j] = A(i, j);
+    }
+    if (csim_host_gauss_seidel(n, 1, a.data(), rhs.data(), sol.data(), maxIters, tol, nullptr))
+        throw std::runtime_error(std::string("Solver: ") + csim_last_error());
+    for (int i = 0; i < n; ++i) x(i) = sol[i];
+    return x;
 }
 VectorXd solveLinearSystemGaussSeidel(const MatrixXd& A, const VectorXd& b, int maxIters, double tol) {
     return solveLinearSystemGaussSeidel(A, b, VectorXd::Zero(b.size()), maxIters, tol);

@@ -3,8 +3,8 @@
 // vector + message on std::cerr, no exceptions for singular systems) but run the batched
 // CUDA LU (csim_dev_lu_solve) with B = 1; n <= 32.  They throw std::runtime_error only when
 // there is no CUDA device (there is no CPU solver in this library).
-// solveLinearSystemGaussSeidel is on the reference's interface but off its default path
-// (src/dcanalysis.cpp:260-262) and is not implemented on the device yet: it throws.
+// solveLinearSystemGaussSeidel (on the reference's interface, off its default path:
+// src/dcanalysis.cpp:260-262) runs csim_dev_gauss_seidel with B = 1, n <= 200, bit-identical sweeps.
 #pragma once
 #include <vector>
 

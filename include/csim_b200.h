@@ -198,6 +198,20 @@ int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_
 int csim_plan_force_large_path(csim_plan* plan, int on);
 #endif
 
+/* Batched Solver::solveLinearSystemGaussSeidel (include/solver.hpp:139-192; on the Solver interface, off the
+ * reference's default path: dcSolve -> LU, src/dcanalysis.cpp:260-262).  A [n*n][B] row-major per system, b [n][B],
+ * x [n][B] in: the initial iterate x0, out: the last iterate (the reference returns it whether or not it converged);
+ * sweeps [B] (NULL ok): sweeps executed.  Per system exactly the reference's sweep: row i subtracts a(i,j)*x(j) in
+ * ascending j, newest values for j < i; |diag| < 1e-12 is replaced by +-1e-12; stop when ||x - xOld||_2 < tol
+ * (norm order: oracle/csim_norm2.h).  n <= 200.  The reference's defaults: max_iters 1000, tol 1e-10. */
+#ifndef __CUDACC_RTC__
+int csim_dev_gauss_seidel(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t max_iters,
+                          double tol, int32_t* sweeps, void* stream);
+/* the same with host buffers (copies inside); used by the host layer's Solver::solveLinearSystemGaussSeidel */
+int csim_host_gauss_seidel(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t max_iters,
+                           double tol, int32_t* sweeps);
+#endif
+
 /* Harmonic extraction over one period (the `.hb f0 nharm` card the reference parses at
  * src/parser.cpp:551-572 and never uses; row (f)2 of SURVEY 8).  For every signal (a row of n_samples
  * doubles, row stride ld; e.g. the last period of one probe of one instance in csim_dev_tran's wave)

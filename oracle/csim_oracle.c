@@ -341,6 +341,36 @@ int oracle_lu_solve(int32_t n, const double* A, const double* b, double* x, int3
     return failed;
 }
 
+/* Solver::solveLinearSystemGaussSeidel, include/solver.hpp:139-192 */
+int32_t oracle_gauss_seidel(int32_t n, const double* A, const double* b, double* x, int32_t max_iters, double tol) {
+    if (n <= 0) return 0;
+    double* xOld = (double*)malloc(sizeof(double) * (size_t)n);
+    double* d = (double*)malloc(sizeof(double) * (size_t)n);
+    const double diagEps = 1e-12; /* 160 */
+    int32_t done = 0;
+    for (int iter = 0; iter < max_iters; ++iter) { /* 162 */
+        memcpy(xOld, x, sizeof(double) * (size_t)n);
+        for (int i = 0; i < n; ++i) {
+            double diag = A[i * n + i];
+            if (fabs(diag) < diagEps) { /* 169-173 */
+                double sign = (diag >= 0.0 ? 1.0 : -1.0);
+                diag = sign * diagEps;
+            }
+            double sum = b[i];
+            for (int j = 0; j < i; ++j) sum -= A[i * n + j] * x[j];        /* 178-180: newest values */
+            for (int j = i + 1; j < n; ++j) sum -= A[i * n + j] * xOld[j]; /* 181-183: previous sweep */
+            x[i] = sum / diag;
+        }
+        for (int i = 0; i < n; ++i) d[i] = x[i] - xOld[i];
+        double err = oracle_norm2(d, n); /* 188 */
+        done = iter + 1;
+        if (err < tol) break;
+    }
+    free(xOld);
+    free(d);
+    return done;
+}
+
 static int all_finite(const double* v, int n) {
     for (int i = 0; i < n; ++i)
         if (!isfinite(v[i])) return 0;

@@ -54,6 +54,8 @@ void oracle_sin_table(double freq, double td, double phi, double dt, int32_t n_s
 /* Solver::solveLinearSystemLU (include/solver.hpp:30-131). A is row-major N*N
  * (not modified), returns 1 when the factorisation failed (x = 0 then). */
 int oracle_lu_solve(int32_t n, const double* A, const double* b, double* x, int32_t* perm, double lu_eps);
+/* Solver::solveLinearSystemGaussSeidel (include/solver.hpp:139-192): x in = x0, out = last iterate; returns sweeps done */
+int32_t oracle_gauss_seidel(int32_t n, const double* A, const double* b, double* x, int32_t max_iters, double tol);
 
 /* dcSolveLU (src/dcanalysis.cpp:242-248). iters[dc_ramp_steps] (NULL ok). */
 void oracle_dc(const csim_topology* t, const csim_constants* c, const double* params, double* x,

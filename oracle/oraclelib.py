@@ -445,6 +445,31 @@ def ref_lu_solve(A, b):
     return x, perm
 
 
+def gauss_seidel(A, b, x0=None, max_iters=1000, tol=1e-10):
+    """oracle_gauss_seidel (restatement of include/solver.hpp:139-192): returns (x, sweeps done)."""
+    L = oracle_lib()
+    A = np.ascontiguousarray(A, np.float64)
+    b = np.ascontiguousarray(b, np.float64)
+    n = b.size
+    x = np.zeros(n, np.float64) if x0 is None else np.array(x0, np.float64)
+    L.oracle_gauss_seidel.restype = C.c_int32
+    it = L.oracle_gauss_seidel(C.c_int32(n), _p(A, C.c_double), _p(b, C.c_double), _p(x, C.c_double),
+                               C.c_int32(int(max_iters)), C.c_double(float(tol)))
+    return x, int(it)
+
+
+def ref_gauss_seidel(A, b, x0=None, max_iters=1000, tol=1e-10):
+    """The unmodified reference's Solver::solveLinearSystemGaussSeidel through oracle/_ref."""
+    L = ref_lib()
+    A = np.ascontiguousarray(A, np.float64)
+    b = np.ascontiguousarray(b, np.float64)
+    n = b.size
+    x = np.zeros(n, np.float64) if x0 is None else np.array(x0, np.float64)
+    L.ref_gauss_seidel(C.c_int(n), _p(A, C.c_double), _p(b, C.c_double), _p(x, C.c_double), C.c_int(int(max_iters)),
+                       C.c_double(float(tol)))
+    return x
+
+
 def ref_run_batch(netlists, n_threads: int):
     """Timed CPU baseline: returns (wall_seconds, total_timepoints)."""
     L = ref_lib()

@@ -348,6 +348,21 @@ int ref_lu_solve(int n, const double* A, const double* b, double* x, int32_t* pe
     return 0;
 }
 
+// Solver::solveLinearSystemGaussSeidel (include/solver.hpp:139-192), x in: x0, out: the last iterate
+int ref_gauss_seidel(int n, const double* A, const double* b, double* x, int max_iters, double tol) {
+    Silence s;
+    Eigen::MatrixXd Am(n, n);
+    Eigen::VectorXd bv(n), x0(n);
+    for (int i = 0; i < n; ++i) {
+        bv(i) = b[i];
+        x0(i) = x[i];
+        for (int j = 0; j < n; ++j) Am(i, j) = A[i * n + j];
+    }
+    Eigen::VectorXd xs = Solver::solveLinearSystemGaussSeidel(Am, bv, x0, max_iters, tol);
+    for (int i = 0; i < n; ++i) x[i] = xs(i);
+    return 0;
+}
+
 // SourceSpec::evalTran of the idx-th independent source (V and I in netlist order)
 double ref_source_tran(void* hv, int idx, double t) {
     auto* h = static_cast<Handle*>(hv);

@@ -101,3 +101,55 @@ def test_harmonics_match_definition_and_dft(torch):
     assert_same_bits(im2[:, 1, 2].cpu().numpy(), oim, "ragged im")
     with pytest.raises(capi.CsimError):
         capi.harmonics(t["wave"], spp, 17)
+
+
+def test_gauss_seidel_batch_bit_exact(torch):
+    """csim_dev_gauss_seidel against the oracle's restatement (itself pinned to the unmodified reference in
+    tests/test_gauss_seidel_cpu.py): iterates and sweep counts, converging, non-converging and regularised."""
+    from circuitsimulator_b200 import capi
+    rng = np.random.default_rng(9)
+    for n in (1, 13, 31, 40, 77):
+        B = 70  # more than one CTA of 64 threads
+        A = rng.normal(size=(B, n, n))
+        for b in range(B):
+            A[b] += np.diag(np.abs(A[b]).sum(1) + 1.0)
+        rhs = rng.normal(size=(B, n))
+        x0 = rng.normal(size=(B, n))
+        if n >= 5:
+            A[2, 1, 1], A[2, 3, 3] = 0.0, -1e-13  # regularised diagonals: diverges, every sweep still defined
+            A[3] = rng.normal(size=(n, n))  # not dominant: runs to max_iters
+        dA = torch.from_numpy(np.ascontiguousarray(A.reshape(B, n * n).T)).cuda()
+        db = torch.from_numpy(np.ascontiguousarray(rhs.T)).cuda()
+        dx0 = torch.from_numpy(np.ascontiguousarray(x0.T)).cuda()
+        for kwargs, start in ((dict(max_iters=200, tol=1e-10), None), (dict(max_iters=4, tol=1e-30), dx0)):
+            x, sweeps = capi.gauss_seidel(dA, db, start, **kwargs)
+            torch.cuda.synchronize()
+            x, sweeps = x.cpu().numpy(), sweeps.cpu().numpy()
+            for b in (0, 1, 2, 3, 63, 64, B - 1):
+                with np.errstate(all="ignore"):
+                    ox, osw = O.gauss_seidel(A[b], rhs[b], None if start is None else x0[b], **kwargs)
+                assert sweeps[b] == osw, f"n={n} system {b}: sweeps {sweeps[b]} vs {osw}"
+                assert_same_bits(x[:, b], ox, f"n={n} system {b}")
+    with pytest.raises(capi.CsimError):
+        capi.gauss_seidel(torch.zeros((201 * 201, 1), dtype=torch.float64, device="cuda"),
+                          torch.zeros((201, 1), dtype=torch.float64, device="cuda"))
+
+
+def test_gauss_seidel_host_buffers(torch):
+    """csim_host_gauss_seidel (what the host layer's Solver::solveLinearSystemGaussSeidel calls) == the oracle."""
+    import ctypes as C
+    from circuitsimulator_b200 import capi
+    rng = np.random.default_rng(2)
+    n = 13
+    A = rng.normal(size=(n, n)) + np.diag(np.full(n, 20.0))
+    b = rng.normal(size=n)
+    x = np.zeros(n)
+    sweeps = np.zeros(1, np.int32)
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+    L = capi.lib()
+    L.csim_host_gauss_seidel.argtypes = [C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_double,
+                                         C.c_void_p]
+    assert L.csim_host_gauss_seidel(n, 1, vp(np.ascontiguousarray(A)), vp(b), vp(x), 1000, 1e-10, vp(sweeps)) == 0
+    ox, osw = O.gauss_seidel(A, b)
+    assert sweeps[0] == osw
+    assert_same_bits(x, ox, "host-buffer Gauss-Seidel")
