@@ -433,24 +433,58 @@ cudaError_t launch_gauss_seidel(int n, int64_t B, const double* A, const double*
 // X_h = (1/M) sum_{n<M} x[n] (c[(h n) mod M] - j s[(h n) mod M]),  h = 0..H, c/s tabulated on the host.
 // Summation order (part of the definition, include/csim_b200.h): lane l adds n = l, l+32, ... in ascending
 // order, each product and each sum separately rounded; the 32 partial sums are combined by the xor
-// butterfly 16, 8, 4, 2, 1; the result is divided by M.  One warp per 8 signals and 4 harmonics per pass: a
-// lane loads its sample of each of the 8 signals (coalesced 256-byte rows from HBM) and the 4 + 4 table values
-// of its sample index (L1/L2) before the first use, then does 64 multiply-adds; per signal the order of the
-// definition is untouched.
+// butterfly 16, 8, 4, 2, 1; the result is divided by M.
+// Mapping: one warp per 8 signals, 4 harmonics per pass.  The accumulators (8 x 4 x re/im doubles per lane) fill
+// the register file, so loads held in registers could keep only ~20 KB per SM in flight (2.3 TB/s measured);
+// instead every lane copies ITS OWN samples with 8-byte cp.async into a private 3-stage ring in shared memory
+// (8 signals x 4 rows per stage; no barrier needed, a lane reads back only what it copied itself) and waits
+// on the oldest group: ~128 KB per SM in flight.  Table values come through L1/L2.  Per signal the order of
+// the definition is untouched.
 static_assert(kHarmonicsMax == 16, "csim_b200.h documents n_harm <= 16");
-constexpr int kHarmSig = 8;   // signals per warp: one table value serves 8 samples
-constexpr int kHarmGrp = 4;   // harmonics per pass over the samples (H <= 3: one pass = 8 bytes of HBM per sample)
+constexpr int kHarmSig = 8;     // signals per warp
+constexpr int kHarmGrp = 4;     // harmonics per pass over the samples (H <= 3: one pass = 8 bytes of HBM per sample)
+constexpr int kHarmWarps = 4;   // warps per CTA
+constexpr int kHarmRows = 4;    // 32-sample rows per stage
+constexpr int kHarmStages = 3;
+constexpr int kHarmStageDoubles = kHarmSig * kHarmRows * 32;  // per warp
 
-__global__ void __launch_bounds__(128)
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+__global__ void __launch_bounds__(kHarmWarps * 32)
 harmonics_kernel(int64_t n_signals, int M, int64_t ld, const double* __restrict__ x, int H,
                  const double* __restrict__ ct, const double* __restrict__ st, double* __restrict__ re,
                  double* __restrict__ im) {
-    const int lane = threadIdx.x & 31;
-    const int64_t sig0 = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * kHarmSig;
+    extern __shared__ double harm_sm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t sig0 = ((int64_t)blockIdx.x * kHarmWarps + warp) * kHarmSig;
     if (sig0 >= n_signals) return;
+    double* ring = harm_sm + (size_t)warp * kHarmStages * kHarmStageDoubles + lane;  // [stage][s][k][lane]
     const double* row[kHarmSig];
 #pragma unroll
     for (int s = 0; s < kHarmSig; ++s) row[s] = x + (sig0 + s < n_signals ? sig0 + s : sig0) * ld;
+    const int n_rows = (M + 31) / 32, n_chunks = (n_rows + kHarmRows - 1) / kHarmRows;
+    auto issue = [&](int chunk) {  // this lane's samples of chunk -> stage chunk % kHarmStages (nothing past the end)
+        if (chunk < n_chunks) {
+            double* dst = ring + (size_t)(chunk % kHarmStages) * kHarmStageDoubles;
+#pragma unroll
+            for (int k = 0; k < kHarmRows; ++k) {
+                const int n = (chunk * kHarmRows + k) * 32 + lane;
+                if (n < M) {
+#pragma unroll
+                    for (int s = 0; s < kHarmSig; ++s) cp_async8(dst + (s * kHarmRows + k) * 32, row[s] + n);
+                }
+            }
+        }
+        cp_async_commit();  // (an empty group keeps the wait count uniform)
+    };
     for (int h0 = 0; h0 <= H; h0 += kHarmGrp) {
         double ar[kHarmSig][kHarmGrp], ai[kHarmSig][kHarmGrp];
         int idx[kHarmGrp], inc[kHarmGrp];
@@ -461,25 +495,36 @@ harmonics_kernel(int64_t n_signals, int M, int64_t ld, const double* __restrict_
 #pragma unroll
             for (int s = 0; s < kHarmSig; ++s) ar[s][g] = ai[s][g] = 0.0;
         }
-        for (int n = lane; n < M; n += 32) {
-            double v[kHarmSig], c[kHarmGrp], sn[kHarmGrp];
 #pragma unroll
-            for (int s = 0; s < kHarmSig; ++s) v[s] = row[s][n];  // all loads of the iteration first
+        for (int c = 0; c < kHarmStages - 1; ++c) issue(c);
+        for (int chunk = 0; chunk < n_chunks; ++chunk) {
+            issue(chunk + kHarmStages - 1);         // refills the stage consumed in the previous iteration
+            cp_async_wait<kHarmStages - 1>();       // this chunk's group has landed
+            const double* src = ring + (size_t)(chunk % kHarmStages) * kHarmStageDoubles;
 #pragma unroll
-            for (int g = 0; g < kHarmGrp; ++g) {
-                c[g] = ct[idx[g]];
-                sn[g] = st[idx[g]];
-                idx[g] += inc[g];
-                if (idx[g] >= M) idx[g] -= M;
-            }
-#pragma unroll
-            for (int s = 0; s < kHarmSig; ++s)
+            for (int k = 0; k < kHarmRows; ++k) {
+                const int n = (chunk * kHarmRows + k) * 32 + lane;
+                if (n >= M) break;
+                double c[kHarmGrp], sn[kHarmGrp];
 #pragma unroll
                 for (int g = 0; g < kHarmGrp; ++g) {
-                    ar[s][g] = d_add(ar[s][g], d_mul(v[s], c[g]));
-                    ai[s][g] = d_add(ai[s][g], d_mul(v[s], sn[g]));
+                    c[g] = ct[idx[g]];
+                    sn[g] = st[idx[g]];
+                    idx[g] += inc[g];
+                    if (idx[g] >= M) idx[g] -= M;
                 }
+#pragma unroll
+                for (int s = 0; s < kHarmSig; ++s) {
+                    const double v = src[(s * kHarmRows + k) * 32];
+#pragma unroll
+                    for (int g = 0; g < kHarmGrp; ++g) {
+                        ar[s][g] = d_add(ar[s][g], d_mul(v, c[g]));
+                        ai[s][g] = d_add(ai[s][g], d_mul(v, sn[g]));
+                    }
+                }
+            }
         }
+        cp_async_wait<0>();
         __syncwarp();
 #pragma unroll
         for (int s = 0; s < kHarmSig; ++s)
@@ -501,7 +546,12 @@ harmonics_kernel(int64_t n_signals, int M, int64_t ld, const double* __restrict_
 
 cudaError_t launch_harmonics(int64_t n_signals, int M, int64_t ld, const double* x, int H, const double* ct,
                              const double* st, double* re, double* im, cudaStream_t stream) {
-    harmonics_kernel<<<(unsigned)((n_signals + 4 * kHarmSig - 1) / (4 * kHarmSig)), 128, 0, stream>>>(n_signals, M, ld, x, H, ct, st, re, im);
+    const int64_t per_cta = (int64_t)kHarmWarps * kHarmSig;
+    const size_t smem = (size_t)kHarmWarps * kHarmStages * kHarmStageDoubles * sizeof(double);
+    cudaError_t e = cudaFuncSetAttribute(harmonics_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    harmonics_kernel<<<(unsigned)((n_signals + per_cta - 1) / per_cta), kHarmWarps * 32, smem, stream>>>(
+        n_signals, M, ld, x, H, ct, st, re, im);
     return cudaGetLastError();
 }
 
