@@ -437,16 +437,19 @@ cudaError_t launch_gauss_seidel(int n, int64_t B, const double* A, const double*
 // Mapping: one warp per 8 signals, 4 harmonics per pass.  The accumulators (8 x 4 x re/im doubles per lane) fill
 // the register file, so loads held in registers could keep only ~20 KB per SM in flight (2.3 TB/s measured);
 // instead every lane copies ITS OWN samples with 8-byte cp.async into a private 3-stage ring in shared memory
-// (8 signals x 4 rows per stage; no barrier needed, a lane reads back only what it copied itself) and waits
-// on the oldest group: ~128 KB per SM in flight.  Table values come through L1/L2.  Per signal the order of
-// the definition is untouched.
+// (8 signals x 2 rows per stage; no barrier needed, a lane reads back only what it copied itself) and waits
+// on the oldest group.  The 4 + 4 table values of each of its sample indices travel the same way (they come out
+// of L1/L2, but a load-then-use in the compute loop stalled every row on the L2 latency: ncu long-scoreboard
+// 4.3 per issue), so the compute loop touches shared memory only.  Per signal the order of the definition is
+// untouched.
 static_assert(kHarmonicsMax == 16, "csim_b200.h documents n_harm <= 16");
 constexpr int kHarmSig = 8;     // signals per warp
 constexpr int kHarmGrp = 4;     // harmonics per pass over the samples (H <= 3: one pass = 8 bytes of HBM per sample)
 constexpr int kHarmWarps = 4;   // warps per CTA
-constexpr int kHarmRows = 4;    // 32-sample rows per stage
+constexpr int kHarmRows = 2;    // 32-sample rows per stage
 constexpr int kHarmStages = 3;
-constexpr int kHarmStageDoubles = kHarmSig * kHarmRows * 32;  // per warp
+constexpr int kHarmSlots = kHarmSig + 2 * kHarmGrp;  // per row and lane: 8 samples + 4 cos + 4 sin table values
+constexpr int kHarmStageDoubles = kHarmSlots * kHarmRows * 32;  // per warp
 
 __device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc) {
     const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -471,7 +474,8 @@ harmonics_kernel(int64_t n_signals, int M, int64_t ld, const double* __restrict_
 #pragma unroll
     for (int s = 0; s < kHarmSig; ++s) row[s] = x + (sig0 + s < n_signals ? sig0 + s : sig0) * ld;
     const int n_rows = (M + 31) / 32, n_chunks = (n_rows + kHarmRows - 1) / kHarmRows;
-    auto issue = [&](int chunk) {  // this lane's samples of chunk -> stage chunk % kHarmStages (nothing past the end)
+    int idx[kHarmGrp], inc[kHarmGrp];
+    auto issue = [&](int chunk) {  // this lane's samples + table values of chunk -> stage chunk % kHarmStages
         if (chunk < n_chunks) {
             double* dst = ring + (size_t)(chunk % kHarmStages) * kHarmStageDoubles;
 #pragma unroll
@@ -480,6 +484,13 @@ harmonics_kernel(int64_t n_signals, int M, int64_t ld, const double* __restrict_
                 if (n < M) {
 #pragma unroll
                     for (int s = 0; s < kHarmSig; ++s) cp_async8(dst + (s * kHarmRows + k) * 32, row[s] + n);
+#pragma unroll
+                    for (int g = 0; g < kHarmGrp; ++g) {
+                        cp_async8(dst + ((kHarmSig + g) * kHarmRows + k) * 32, ct + idx[g]);
+                        cp_async8(dst + ((kHarmSig + kHarmGrp + g) * kHarmRows + k) * 32, st + idx[g]);
+                        idx[g] += inc[g];  // index of this lane's next sample: (h * (n + 32)) mod M
+                        if (idx[g] >= M) idx[g] -= M;
+                    }
                 }
             }
         }
@@ -487,7 +498,6 @@ harmonics_kernel(int64_t n_signals, int M, int64_t ld, const double* __restrict_
     };
     for (int h0 = 0; h0 <= H; h0 += kHarmGrp) {
         double ar[kHarmSig][kHarmGrp], ai[kHarmSig][kHarmGrp];
-        int idx[kHarmGrp], inc[kHarmGrp];
 #pragma unroll
         for (int g = 0; g < kHarmGrp; ++g) {
             idx[g] = (int)(((long long)(h0 + g) * lane) % M);
@@ -508,10 +518,8 @@ harmonics_kernel(int64_t n_signals, int M, int64_t ld, const double* __restrict_
                 double c[kHarmGrp], sn[kHarmGrp];
 #pragma unroll
                 for (int g = 0; g < kHarmGrp; ++g) {
-                    c[g] = ct[idx[g]];
-                    sn[g] = st[idx[g]];
-                    idx[g] += inc[g];
-                    if (idx[g] >= M) idx[g] -= M;
+                    c[g] = src[((kHarmSig + g) * kHarmRows + k) * 32];
+                    sn[g] = src[((kHarmSig + kHarmGrp + g) * kHarmRows + k) * 32];
                 }
 #pragma unroll
                 for (int s = 0; s < kHarmSig; ++s) {
