@@ -29,7 +29,7 @@ EXPORTS = [
     "csim_plan_create", "csim_plan_destroy", "csim_plan_pattern", "csim_plan_dims",
     "csim_dev_stamp_csr", "csim_dev_lu_solve", "csim_dev_dc", "csim_dev_tran",
     "csim_batch_create", "csim_batch_destroy", "csim_batch_set_params", "csim_batch_dc",
-    "csim_batch_tran", "csim_batch_last_kernel_ms", "csim_pivot_hash_update",
+    "csim_batch_tran", "csim_batch_tran_from", "csim_batch_last_kernel_ms", "csim_pivot_hash_update",
     "csim_host_stamp_csr", "csim_host_lu_solve",
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",

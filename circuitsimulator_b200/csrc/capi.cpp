@@ -832,8 +832,10 @@ int csim_batch_dc(csim_batch* b, double* x, int32_t* iters, uint64_t* pivot_hash
     return CSIM_OK;
 }
 
-int csim_batch_tran(csim_batch* b, const csim_tran_args* a, double* x_dc, double* x_final, double* wave,
-                    int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status) {
+// x_start == nullptr: DC operating point first (csim_batch_tran); else the transient starts from x_start [N][B]
+static int batch_tran_impl(csim_batch* b, const csim_tran_args* a, const double* x_start, double* x_dc, double* x_final,
+                           double* wave, int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash,
+                           uint32_t* status) {
     if (!b || !a) return fail(CSIM_E_INVALID, "csim_batch_tran: null argument");
     const csim_plan* plan = b->plan;
     CU(cudaSetDevice(plan->device));
@@ -889,8 +891,13 @@ int csim_batch_tran(csim_batch* b, const csim_tran_args* a, double* x_dc, double
     da.src_table = d_table;
     da.src_group_b = d_group_b;
     CUC(cudaEventRecord(b->ev0, b->stream));
-    // runTransientAnalysisBackwardEuler: DC operating point first (src/tanalisis.cpp:112) ...
-    rc = csim_dev_dc(plan, B, b->d_params, b->d_x, nullptr, b->d_hash, b->d_status, b->stream);
+    if (x_start) {
+        CUC(cudaMemcpyAsync(b->d_x, x_start, sizeof(double) * (size_t)N * B, cudaMemcpyHostToDevice, b->stream));
+        rc = 0;
+    } else {
+        // runTransientAnalysisBackwardEuler: DC operating point first (src/tanalisis.cpp:112) ...
+        rc = csim_dev_dc(plan, B, b->d_params, b->d_x, nullptr, b->d_hash, b->d_status, b->stream);
+    }
     if (rc) {
         cleanup();
         return rc;
@@ -916,6 +923,16 @@ int csim_batch_tran(csim_batch* b, const csim_tran_args* a, double* x_dc, double
     return CSIM_OK;
 }
 
+int csim_batch_tran(csim_batch* b, const csim_tran_args* a, double* x_dc, double* x_final, double* wave,
+                    int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status) {
+    return batch_tran_impl(b, a, nullptr, x_dc, x_final, wave, iters_total, iters_step, pivot_hash, status);
+}
+
+int csim_batch_tran_from(csim_batch* b, const csim_tran_args* a, double* x, double* wave, int32_t* iters_total,
+                         uint64_t* pivot_hash, uint32_t* status) {
+    if (!x) return fail(CSIM_E_INVALID, "csim_batch_tran_from: null state");
+    return batch_tran_impl(b, a, x, nullptr, x, wave, iters_total, nullptr, pivot_hash, status);
+}
 
 int csim_batch_sstate(csim_batch* b, const csim_tran_args* a, const csim_sstate_args* ss, double* x_dc, double* x,
                       int32_t* periods, double* delta, int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status) {

@@ -195,6 +195,33 @@ int csimh_run_sstate(const csimh_netlist* h, int64_t B, const double* params, do
     }
 }
 
+// runSteadyStateShootingBatch (include/csim/sstateanalysis.hpp); f0 / tstep > 0 override `.hb` / `.TRAN`.
+// x_dc, x: [N][C]; iterations [C]; residual [C].  Returns steps per period (> 0) or -1 with csimh_last_error().
+int csimh_run_shooting(const csimh_netlist* h, int64_t C, const double* params, double f0, double tstep,
+                       int32_t max_iters, double tol, double rel_step, double* x_dc, double* x, int32_t* iterations,
+                       double* residual, int64_t* transient_instances) {
+    if (!h || !params || C <= 0) return -1;
+    try {
+        SimulationConfig sim = h->sim;
+        if (f0 > 0.0) {
+            sim.hb.enabled = true;
+            sim.hb.f0 = f0;
+        }
+        if (tstep > 0.0) sim.tran.tstep = tstep;
+        std::vector<double> p(params, params + static_cast<std::size_t>(h->low.n_params) * C);
+        csim::ShootingResult R = csim::runSteadyStateShootingBatch(h->ckt, sim, p, C, max_iters, tol, rel_step);
+        if (x_dc) std::memcpy(x_dc, R.x_dc.data(), R.x_dc.size() * 8);
+        if (x) std::memcpy(x, R.x.data(), R.x.size() * 8);
+        if (iterations) std::memcpy(iterations, R.iterations.data(), R.iterations.size() * 4);
+        if (residual) std::memcpy(residual, R.residual.data(), R.residual.size() * 8);
+        if (transient_instances) *transient_instances = R.transient_instances;
+        return R.steps_per_period;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return -1;
+    }
+}
+
 int csimh_write_instance_csv(const csimh_netlist* h, const char* path, int64_t B, int64_t instance, int32_t n_probes,
                              const int32_t* probes, int32_t n_steps, int32_t n_out, int32_t out_stride,
                              const double* x_dc, const double* wave, const uint32_t* status) {

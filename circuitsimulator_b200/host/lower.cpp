@@ -3,6 +3,7 @@
 #include "csim/lower.hpp"
 #include "csim/sstateanalysis.hpp"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -259,6 +260,100 @@ SteadyStateResult runSteadyStateAnalysisBatch(const Circuit& ckt, const Simulati
                           R.iters_total.data(), R.pivot_hash.data(), R.status.data()))
         raise("csim_batch_sstate");
     R.kernel_ms = csim_batch_last_kernel_ms(bg.b);
+    return R;
+}
+
+ShootingResult runSteadyStateShootingBatch(const Circuit& ckt, const SimulationConfig& sim,
+                                           const std::vector<double>& params, int64_t C, int max_iters, double tol,
+                                           double rel_step, int device) {
+    if (!sim.hb.enabled || !(sim.hb.f0 > 0.0)) throw std::runtime_error("Steady state: .hb card with f0 > 0 required.");
+    if (!(sim.tran.tstep > 0.0)) throw std::runtime_error("Steady state: .TRAN card (tstep) required.");
+    Lowered L = lower(ckt);
+    const int N = L.n_unknowns, P = L.n_params;
+    if (static_cast<int64_t>(params.size()) != static_cast<int64_t>(P) * C)
+        throw std::runtime_error("runSteadyStateShootingBatch: params must hold P*C doubles");
+    ShootingResult R;
+    R.C = C;
+    R.steps_per_period = static_cast<int32_t>(std::llround(1.0 / sim.hb.f0 / sim.tran.tstep));
+    if (R.steps_per_period < 1) throw std::runtime_error("Steady state: period shorter than one timestep.");
+    SourceTables S = tabulate_sources(ckt, sim.tran.tstep, R.steps_per_period);
+    csim_topology t = L.view();
+    PlanGuard pg;
+    if (csim_plan_create(&t, nullptr, device, &pg.p)) raise("csim_plan_create");
+    // operating points of the C circuits
+    {
+        BatchGuard dc;
+        if (csim_batch_create(pg.p, C, &dc.b)) raise("csim_batch_create");
+        if (csim_batch_set_params(dc.b, params.data())) raise("csim_batch_set_params");
+        R.x_dc.resize(static_cast<std::size_t>(N) * C);
+        if (csim_batch_dc(dc.b, R.x_dc.data(), nullptr, nullptr, nullptr)) raise("csim_batch_dc");
+    }
+    R.x = R.x_dc;
+    R.iterations.assign(static_cast<std::size_t>(C), -1);
+    R.residual.assign(static_cast<std::size_t>(C), 0.0);
+    // the big batch: circuit c owns instances c*(N+1) .. c*(N+1)+N (candidate first, then one column per unknown)
+    const int64_t W = N + 1, Bt = C * W;
+    std::vector<double> pb(static_cast<std::size_t>(P) * Bt);
+    for (int p = 0; p < P; ++p)
+        for (int64_t c = 0; c < C; ++c)
+            for (int64_t k = 0; k < W; ++k) pb[static_cast<std::size_t>(p) * Bt + c * W + k] = params[static_cast<std::size_t>(p) * C + c];
+    BatchGuard bg;
+    if (csim_batch_create(pg.p, Bt, &bg.b)) raise("csim_batch_create");
+    if (csim_batch_set_params(bg.b, pb.data())) raise("csim_batch_set_params");
+    csim_tran_args a;
+    std::memset(&a, 0, sizeof(a));
+    a.dt = sim.tran.tstep;
+    a.step_end = R.steps_per_period;
+    a.n_groups = S.n_groups;
+    a.table_steps = R.steps_per_period;
+    a.src_table = S.table.data();
+    a.src_mode = S.mode.data();
+    a.src_group = S.group.data();
+    a.out_stride = 1;
+    std::vector<double> X(static_cast<std::size_t>(N) * Bt), h(static_cast<std::size_t>(N) * C);
+    std::vector<double> J(static_cast<std::size_t>(N) * N * C), rhs(static_cast<std::size_t>(N) * C), delta(rhs.size());
+    std::vector<uint8_t> open(static_cast<std::size_t>(C), 1);
+    for (int it = 0; it <= max_iters; ++it) {
+        for (int64_t c = 0; c < C; ++c)
+            for (int i = 0; i < N; ++i) {
+                const double xi = R.x[static_cast<std::size_t>(i) * C + c];
+                h[static_cast<std::size_t>(i) * C + c] = rel_step * std::max(std::fabs(xi), 1.0);
+                for (int64_t k = 0; k < W; ++k)
+                    X[static_cast<std::size_t>(i) * Bt + c * W + k] = xi + (k == i + 1 ? h[static_cast<std::size_t>(i) * C + c] : 0.0);
+            }
+        if (csim_batch_tran_from(bg.b, &a, X.data(), nullptr, nullptr, nullptr, nullptr)) raise("csim_batch_tran_from");
+        R.transient_instances += Bt;
+        bool any_open = false;
+        for (int64_t c = 0; c < C; ++c) {
+            double ss = 0.0;
+            for (int i = 0; i < N; ++i) {
+                const double f = X[static_cast<std::size_t>(i) * Bt + c * W] - R.x[static_cast<std::size_t>(i) * C + c];
+                rhs[static_cast<std::size_t>(i) * C + c] = -f;
+                ss += f * f;
+            }
+            if (!open[static_cast<std::size_t>(c)]) continue;
+            R.residual[static_cast<std::size_t>(c)] = std::sqrt(ss);
+            if (R.residual[static_cast<std::size_t>(c)] < tol) {
+                R.iterations[static_cast<std::size_t>(c)] = it;
+                open[static_cast<std::size_t>(c)] = 0;
+            } else {
+                any_open = true;
+            }
+        }
+        if (!any_open || it == max_iters) break;
+        // (dPhi - I) delta = -F, one system per circuit, solved on the device (csim_host_lu_solve, A [N*N][C])
+        for (int64_t c = 0; c < C; ++c)
+            for (int i = 0; i < N; ++i)
+                for (int j = 0; j < N; ++j) {
+                    const double phi0 = X[static_cast<std::size_t>(i) * Bt + c * W];
+                    const double phij = X[static_cast<std::size_t>(i) * Bt + c * W + 1 + j];
+                    J[(static_cast<std::size_t>(i) * N + j) * C + c] = (phij - phi0) / h[static_cast<std::size_t>(j) * C + c] - (i == j ? 1.0 : 0.0);
+                }
+        if (csim_host_lu_solve(N, C, J.data(), rhs.data(), delta.data(), nullptr, nullptr, 1e-15)) raise("csim_host_lu_solve");
+        for (int64_t c = 0; c < C; ++c)
+            if (open[static_cast<std::size_t>(c)])
+                for (int i = 0; i < N; ++i) R.x[static_cast<std::size_t>(i) * C + c] += delta[static_cast<std::size_t>(i) * C + c];
+    }
     return R;
 }
 

@@ -245,6 +245,28 @@ class Netlist:
             raise capi.CsimError("csimh_run_dc_sweep: " + L.csimh_last_error().decode(errors="replace"))
         return out
 
+    def shooting(self, params, f0=None, tstep=None, max_iters: int = 10, tol: float = 1e-9, rel_step: float = 1e-6):
+        """runSteadyStateShootingBatch of the C++ host layer: Newton shooting on Phi_T(x) = x for C circuits
+        (params [P, C]); every iteration integrates C * (N + 1) instances for one period on the GPU."""
+        L = _hlib()
+        L.csimh_run_shooting.restype = C.c_int
+        L.csimh_run_shooting.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_double, C.c_double, C.c_int32, C.c_double,
+                                         C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        params = np.ascontiguousarray(params, np.float64)
+        Cn = params.shape[1]
+        out = {"x_dc": np.zeros((self.n_unknowns, Cn)), "x": np.zeros((self.n_unknowns, Cn)),
+               "iterations": np.zeros(Cn, np.int32), "residual": np.zeros(Cn)}
+        n_inst = C.c_int64(0)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        spp = L.csimh_run_shooting(C.c_void_p(self._h), Cn, vp(params), float(f0 or 0.0), float(tstep or 0.0),
+                                   int(max_iters), float(tol), float(rel_step), vp(out["x_dc"]), vp(out["x"]),
+                                   vp(out["iterations"]), vp(out["residual"]), C.byref(n_inst))
+        if spp < 0:
+            raise capi.CsimError(L.csimh_last_error().decode(errors="replace"))
+        out["steps_per_period"] = spp
+        out["transient_instances"] = int(n_inst.value)
+        return out
+
     def run_reference_style_csv(self, path: str):
         """runTransientAnalysisBackwardEuler(ckt, sim, path) of the C++ host layer (B = 1 on the GPU)."""
         L = _hlib()

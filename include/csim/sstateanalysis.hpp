@@ -30,4 +30,25 @@ SteadyStateResult runSteadyStateAnalysisBatch(const Circuit& ckt, const Simulati
                                               const std::vector<double>& params, int64_t B, int max_periods = 20,
                                               double tol = 1e-6, int device = 0);
 
+// Shooting (the method the north-star names "steady-state shooting candidates"): find x* with Phi_T(x*) = x*, where
+// Phi_T integrates one period with the reference's backward-Euler transient, by Newton on F(x) = Phi_T(x) - x.
+// The Jacobian dPhi_T/dx is taken by forward differences whose N perturbation columns are BATCH INSTANCES: every
+// shooting iteration is one batched transient of C * (N + 1) instances (candidate + N perturbed copies per
+// circuit), followed by one batched LU solve of the C systems (dPhi - I) delta = -F on the device.
+//   x_{m+1} = x_m + delta,  column j: (Phi_T(x_m + h_j e_j) - Phi_T(x_m)) / h_j,  h_j = rel_step * max(|x_m,j|, 1).
+// Requires sources that are T-periodic (time restarts at 0 every period).  Converged when ||F(x_m)||_2 < tol.
+// No counterpart in the reference (empty src/sstateanalysis.cpp): parity unpinned; the tests check periodicity of
+// the result and agreement with runSteadyStateAnalysisBatch.
+struct ShootingResult {
+    int64_t C = 0;
+    int32_t steps_per_period = 0;
+    std::vector<double> x_dc, x;      // [N][C]
+    std::vector<int32_t> iterations;  // [C] shooting iterations used, -1 = not converged within max_iters
+    std::vector<double> residual;     // [C] ||Phi_T(x) - x||_2 at the returned x
+    int64_t transient_instances = 0;  // instances integrated for one period, summed over the iterations
+};
+ShootingResult runSteadyStateShootingBatch(const Circuit& ckt, const SimulationConfig& sim,
+                                           const std::vector<double>& params, int64_t C, int max_iters = 10,
+                                           double tol = 1e-9, double rel_step = 1e-6, int device = 0);
+
 }  // namespace csim

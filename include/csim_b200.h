@@ -361,6 +361,13 @@ int csim_batch_dc(csim_batch* batch, double* x, int32_t* iters, uint64_t* pivot_
 int csim_batch_tran(csim_batch* batch, const csim_tran_args* args, double* x_dc, double* x_final, double* wave,
                     int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status);
 #endif
+/* The transient alone, from given states: x [N][B] in = the state at step_begin (t = step_begin * dt), out = the
+ * state after step_end.  What the shooting driver (include/csim/sstateanalysis.hpp) integrates its candidates and
+ * perturbation columns with.  Other arguments as csim_batch_tran.                                    */
+#ifndef __CUDACC_RTC__
+int csim_batch_tran_from(csim_batch* batch, const csim_tran_args* args, double* x, double* wave,
+                         int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status);
+#endif
 /* DC operating point followed by csim_dev_sstate from it; tran->src_table / src_group_b are HOST
  * pointers; x_dc, x [N][B], periods, delta, iters_total, pivot_hash, status: host (NULL ok except x). */
 #ifndef __CUDACC_RTC__

@@ -34,6 +34,11 @@ int csimh_run_tran_csv(const csimh_netlist* h, const char* path);
 int csimh_run_sstate(const csimh_netlist* h, int64_t B, const double* params, double f0, double tstep,
                      int32_t max_periods, double tol, double* x_dc, double* x, int32_t* periods, double* delta,
                      int32_t* iters_total);
+/* runSteadyStateShootingBatch (include/csim/sstateanalysis.hpp): Newton shooting on Phi_T(x) = x with the
+ * perturbation columns as batch instances.  Returns steps per period, or -1. */
+int csimh_run_shooting(const csimh_netlist* h, int64_t C, const double* params, double f0, double tstep,
+                       int32_t max_iters, double tol, double rel_step, double* x_dc, double* x, int32_t* iterations,
+                       double* residual, int64_t* transient_instances);
 /* Row (f)1: one instance of a batched transient in the reference's CSV layout (csim::writeInstanceCsv,
  * include/csim/batchio.hpp).  x_dc: [N][B] or NULL (no t = 0 row); wave: [B][n_probes][n_out]; status: [B] or NULL.
  * Recorded rows are the last n_out multiples of out_stride among n_steps steps of the netlist's .TRAN tstep. */

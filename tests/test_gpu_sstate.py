@@ -91,3 +91,35 @@ def test_host_layer_driver_equals_device_api(torch):
     assert_same_bits(h["x"], r["x"].cpu().numpy(), "host-layer steady state")
     assert_same_bits(h["x_dc"], d["x"].cpu().numpy(), "host-layer DC")
     assert np.array_equal(h["iters_total"], r["iters_total"].cpu().numpy())
+
+
+def test_shooting_finds_the_periodic_state(torch):
+    """Newton shooting with the perturbation columns as batch instances (runSteadyStateShootingBatch): the returned
+    state is periodic (one more period of the pinned transient returns to it) and agrees with period-by-period
+    integration.  Floating-point algorithm without a reference counterpart: tolerances stated here."""
+    from circuitsimulator_b200 import capi
+    from circuitsimulator_b200.netlist import Netlist
+    g, topo = load_golden("buffer")
+    nl = Netlist(str(g["netlist"]))
+    C_, spp = 4, 100  # Vin is a 10 MHz sine: T = 100 steps of 1 ns
+    P = nl.monte_carlo(C_, 21)
+    r = nl.shooting(P, f0=10e6, max_iters=8, tol=1e-9)
+    assert r["steps_per_period"] == spp
+    assert (r["iterations"] >= 0).all() and (r["iterations"] <= 8).all(), r["iterations"]
+    assert (r["residual"] < 1e-9).all()
+    assert r["transient_instances"] == (int(r["iterations"].max()) + 1) * C_ * (nl.n_unknowns + 1)
+    # independent check of periodicity with the device API
+    plan = nl.plan()
+    params = dev(torch, P)
+    m, grp, tab = nl.source_tables(nl.tran["tstep"], spp)
+    setup = capi.TranSetup(nl.tran["tstep"], spp, m, grp, tab, probes=np.zeros(0, np.int32))
+    x = dev(torch, r["x"])
+    t = capi.tran(plan, params, x.clone(), setup)
+    assert np.linalg.norm(t["x"].cpu().numpy() - r["x"], axis=0).max() < 1e-9
+    # brute force: many periods of plain integration end at the same orbit
+    K = 12
+    m, grp, tab = nl.source_tables(nl.tran["tstep"], spp * K)
+    setup = capi.TranSetup(nl.tran["tstep"], spp * K, m, grp, tab, probes=np.zeros(0, np.int32))
+    d = capi.dc(plan, params)
+    s = capi.sstate(plan, params, d["x"].clone(), setup, spp, K, 1e-12)
+    assert np.abs(s["x"].cpu().numpy() - r["x"]).max() < 1e-6
