@@ -178,7 +178,7 @@ int spec_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     return CSIM_OK;
 }
 
-// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bits 8-9: replicas - 1); unset = defaults.
+// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bits 8-9: replicas - 1, bits 12-14: warps per CTA); unset = defaults.
 TpiOptions tpi_options_from_env() {
     TpiOptions opt;
     if (const char* env = std::getenv("CSIM_TPI_OPTS")) {
@@ -189,42 +189,57 @@ TpiOptions tpi_options_from_env() {
         opt.q_in_smem = m & 8;
         opt.mos_branchless = m & 16;
         opt.replicas = 1 + ((m >> 8) & 3);
+        opt.warps_per_cta = (m >> 12) & 7;
     }
     return opt;
 }
 
 // Generates, compiles and loads the thread-per-instance kernel specialised to `perm`.
+// The generator sizes the CTA so that an SM's shared memory holds as many warps as possible; the driver's
+// occupancy answer for the loaded kernel is checked against the plain one-warp CTA and the kernel is rebuilt
+// that way if the wider CTA does not deliver (the answer is in the log either way).
 int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     TpiState& tp = plan->tpi;
     tp.ready = false;
     if (tp.d_stats) cudaFree(tp.d_stats);
     tp.d_stats = nullptr;
-    jit_unload(tp.k);
-    try {
-        const TpiOptions opt = tpi_options_from_env();
-        tp.host = generate_tran_tpi(plan->host, perm, opt);
-    } catch (const std::exception& e) {
-        tp.log = e.what();
-        return fail(CSIM_E_UNSUPPORTED, tp.log);
-    }
-    std::vector<char> cubin;
+    TpiOptions opt = tpi_options_from_env();
     std::string log;
-    if (!jit_compile(tp.host.source, "csim_tran_tpi.cu", jit_library_dir() + "/csrc", cubin, log)) {
-        tp.log = "NVRTC: " + log;
-        return fail(CSIM_E_CUDA, tp.log);
+    int warps_per_sm = 0;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        jit_unload(tp.k);
+        try {
+            tp.host = generate_tran_tpi(plan->host, perm, opt);
+        } catch (const std::exception& e) {
+            tp.log = e.what();
+            return fail(CSIM_E_UNSUPPORTED, tp.log);
+        }
+        std::vector<char> cubin;
+        if (!jit_compile(tp.host.source, "csim_tran_tpi.cu", jit_library_dir() + "/csrc", cubin, log)) {
+            tp.log = "NVRTC: " + log;
+            return fail(CSIM_E_CUDA, tp.log);
+        }
+        CU(jit_load(cubin, "csim_tran_tpi", tp.k));
+        CU(cudaKernelSetAttributeForDevice(tp.k.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)tp.host.smem_bytes, plan->device));
+        int ctas = 0;
+        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas, reinterpret_cast<const void*>(tp.k.kernel),
+                                                         tp.host.threads, tp.host.smem_bytes));
+        warps_per_sm = ctas * (tp.host.threads / 32);
+        const size_t warp_bytes = tp.host.smem_bytes / (size_t)(tp.host.threads / 32);
+        const int one_warp_ctas = (int)std::min<size_t>(32, 233472 / (warp_bytes + 1024));
+        if (tp.host.threads == 32 || opt.warps_per_cta > 0 || warps_per_sm > one_warp_ctas) break;
+        opt.warps_per_cta = 1;
     }
-    CU(jit_load(cubin, "csim_tran_tpi", tp.k));
-    CU(cudaKernelSetAttributeForDevice(tp.k.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)tp.host.smem_bytes, plan->device));
     CU(cudaMalloc((void**)&tp.d_stats, 2 * sizeof(unsigned long long)));
     CU(cudaMemset(tp.d_stats, 0, 2 * sizeof(unsigned long long)));
     tp.log = "thread-per-instance: " + std::to_string(tp.host.n_slots) + " shared doubles per instance, " +
              std::to_string(tp.host.replicas) + " instance(s) per thread, " + std::to_string(tp.host.threads) +
-             " threads per CTA; per Newton iteration: " +
+             " threads per CTA, " + std::to_string(warps_per_sm) + " warps resident per SM; per Newton iteration: " +
              std::to_string(tp.host.n_lu_divs) + " multipliers, " + std::to_string(tp.host.n_elim_updates) +
              " row updates, " + std::to_string(tp.host.n_back_terms) + " back-substitution terms, " +
-             std::to_string(tp.host.n_g_adds) + "+" + std::to_string(tp.host.n_rhs_adds) + " assembly adds" +
-             (log.size() > 1 ? "\n" + log : "");
+             std::to_string(tp.host.n_g_adds) + "+" + std::to_string(tp.host.n_rhs_adds) + " assembly adds; longest dependency chain " +
+             std::to_string(tp.host.crit_cycles) + " cycles" + (log.size() > 1 ? "\n" + log : "");
     tp.ready = true;
     return CSIM_OK;
 }

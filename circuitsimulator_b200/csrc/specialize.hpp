@@ -50,6 +50,9 @@ struct TpiHost {
     uint32_t hash_lo = 0, hash_hi = 0;
     // statistics of the generated code (per Newton iteration, per instance)
     int32_t n_elim_updates = 0, n_lu_divs = 0, n_back_terms = 0, n_g_adds = 0, n_rhs_adds = 0, n_rcp = 0;
+    // longest dependency chain of one Newton iteration in cycles (operation latencies of
+    // profiles/r1_microbench_fp64.txt): what one thread cannot go below however its code is scheduled
+    int32_t crit_cycles = 0, crit_lu_cycles = 0;
 };
 struct TpiOptions {
     bool const_prop = true;  // track +-1 / gmin entries symbolically (exact rewrites only)
@@ -57,6 +60,7 @@ struct TpiOptions {
     bool mos_in_smem = false;    // MOSFET parameters and linearisation values parked in shared memory
     bool q_in_smem = false;      // raw solution parked in the (dead) Y slots
     bool mos_branchless = false; // evaluate both MOSFET regions and select (measured slower on dbmixer)
+    int warps_per_cta = 0;       // 0 = whatever packs most warps into an SM's shared memory (1, 2 or 4)
     int replicas = 1;            // instances advanced together by one thread (interleaved instruction streams)
 };
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt = TpiOptions());

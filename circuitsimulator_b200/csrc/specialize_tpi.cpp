@@ -28,8 +28,27 @@ namespace csim {
 
 namespace {
 
-constexpr size_t kMaxSmem = 232448;  // 227 KB dynamic shared memory per CTA on sm_100
-constexpr int kTpb = 32;             // one warp per CTA: the SM packs as many CTAs as shared memory allows
+constexpr size_t kMaxSmem = 232448;    // 227 KB dynamic shared memory per CTA on sm_100
+constexpr size_t kSmemPerSm = 233472;  // 228 KB per SM, of which every resident CTA reserves 1 KB
+constexpr size_t kCtaReserve = 1024;
+
+// Warps never talk to each other (no CTA barrier), so the CTA size is free: pick the one that packs the
+// most warps into an SM's shared memory.  dbmixer: 226 doubles x 32 lanes = 57,856 B per warp — three
+// 1-warp CTAs (1 KB reserve each) but FOUR warps as two 2-warp CTAs (2 x 116,736 B = 228 KB exactly),
+// i.e. one warp per SM sub-partition.
+int pick_warps_per_cta(size_t warp_bytes) {
+    int best_w = 1;
+    size_t best = 0;
+    for (int w : {1, 2, 4}) {
+        if (warp_bytes * w > kMaxSmem) break;
+        const size_t warps = std::min<size_t>(32, kSmemPerSm / (warp_bytes * w + kCtaReserve)) * w;
+        if (warps > best) {
+            best = warps;
+            best_w = w;
+        }
+    }
+    return best_w;
+}
 
 // Generated text is written for ONE instance with placeholders — identifier suffix '@' and replica
 // number '@R' — and then replicated (replicate() below) for the R instances a thread advances together.
@@ -108,6 +127,7 @@ struct Val {
     bool c = false;
     double v = 0.0;
     std::string e;
+    int t = 0;  // dependency-chain estimate: cycle at which the value is available (kLat* below)
     static Val K(double x) {
         Val r;
         r.c = true;
@@ -115,26 +135,32 @@ struct Val {
         r.e = lit(x);
         return r;
     }
-    static Val E(const std::string& s) {
+    static Val E(const std::string& s, int t = 0) {
         Val r;
         r.e = s;
+        r.t = t;
         return r;
     }
 };
 
+// latencies of the dependency-chain estimate (profiles/r1_microbench_fp64.txt): one dependent FP64
+// operation, the three-operation quotient of tdiv plus its select, rcp_seq (MUFU + five dependent
+// DFMA), one MOSFET linearisation from the iterate, a shared-memory store -> load round trip
+constexpr int kLatOp = 8, kLatDiv = 28, kLatRcp = 64, kLatMos = 96, kLatSmem = 35, kLatSqrt = 92;
+
 Val neg(const Val& a) {
     if (a.c) return Val::K(-a.v);
     if (a.e.size() > 3 && a.e.compare(0, 2, "(-") == 0 && a.e.back() == ')' && a.e.find('(', 1) == std::string::npos)
-        return Val::E(a.e.substr(2, a.e.size() - 3));
-    return Val::E("(-" + a.e + ")");
+        return Val::E(a.e.substr(2, a.e.size() - 3), a.t);
+    return Val::E("(-" + a.e + ")", a.t);
 }
 Val add(const Val& a, const Val& b) {
     if (a.c && b.c) return Val::K(a.v + b.v);
-    return Val::E("d_add(" + a.e + ", " + b.e + ")");
+    return Val::E("d_add(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp);
 }
 Val sub(const Val& a, const Val& b) {
     if (a.c && b.c) return Val::K(a.v - b.v);
-    return Val::E("d_sub(" + a.e + ", " + b.e + ")");
+    return Val::E("d_sub(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp);
 }
 Val mul(const Val& a, const Val& b) {
     if (a.c && b.c) return Val::K(a.v * b.v);
@@ -142,7 +168,7 @@ Val mul(const Val& a, const Val& b) {
     if (b.c && b.v == 1.0) return a;
     if (a.c && a.v == -1.0) return neg(b);
     if (b.c && b.v == -1.0) return neg(a);
-    return Val::E("d_mul(" + a.e + ", " + b.e + ")");
+    return Val::E("d_mul(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp);
 }
 
 }  // namespace
@@ -156,7 +182,6 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     const int N = A.N;
     TpiHost H;
     H.perm = perm;
-    H.threads = kTpb;
     for (int i = 0; i < N; ++i) {  // pivot-hash contribution of the predicted permutation
         uint32_t key = (uint32_t)i * 1024u + (uint32_t)perm[i] + 1u;
         uint32_t lo = key * 0x9E3779B1u;
@@ -253,7 +278,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
                 if (!prm_slot.count(m.param + t)) prm_slot[m.param + t] = alloc();
     auto val = [&](int v) -> Val {  // per-iteration operand
         if (is_const[v]) return Val::K(const_val[v]);
-        if (kind[v] == MOS) return opt.mos_in_smem ? Val::E(S(mos_slot.at(v))) : Val::E("m" + std::to_string(v) + "@");
+        if (kind[v] == MOS)
+            return opt.mos_in_smem ? Val::E(S(mos_slot.at(v)), kLatMos + kLatSmem) : Val::E("m" + std::to_string(v) + "@", kLatMos);
         return Val::E(S(val_slot.at(v)));
     };
 
@@ -355,7 +381,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         if (a.c && d.c) return Val::K(a.v / d.v);
         o << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo@, ghi@);\n";
         H.n_lu_divs++;
-        return Val::E(tmp);
+        return Val::E(tmp, std::max(a.t, RDv[k].t) + kLatDiv);
     };
     for (int i = 0; i < N; ++i) {
         o << "            {  // position " << i << " = row " << perm[i] << "\n";
@@ -370,7 +396,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
             if (v.e == name) return;
             o << "                " << (declared.count(j) ? "" : "double ") << name << " = " << v.e << ";\n";
             declared.insert(j);
-            row[j] = Val::E(name);
+            row[j] = Val::E(name, v.t);
         };
         for (int j = 0; j <= N; ++j) {
             if (j < N && !A.pat[i][j]) continue;
@@ -411,8 +437,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
               << ") <= 0x1.fffffffffffffp+1023);\n"
               << "                " << S(sd) << " = " << dn << ";\n"
               << "                " << S(srd) << " = rcp_seq(" << dn << ");\n";
-            Dv[i] = Val::E(S(sd));
-            RDv[i] = Val::E(S(srd));
+            Dv[i] = Val::E(S(sd), d.t + kLatSmem);
+            RDv[i] = Val::E(S(srd), d.t + kLatRcp + kLatSmem);
             H.n_rcp++;
         }
         for (int j : A.ucols[i]) {
@@ -422,14 +448,14 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
             } else {
                 const int su = alloc();
                 o << "                " << S(su) << " = " << u.e << ";\n";
-                Uv[i][j] = Val::E(S(su));
+                Uv[i][j] = Val::E(S(su), u.t + kLatSmem);
             }
         }
         if (row[N].c) {
             Yv[i] = row[N];
         } else {
             o << "                " << S(Y0 + i) << " = rb@;\n";
-            Yv[i] = Val::E(S(Y0 + i));
+            Yv[i] = Val::E(S(Y0 + i), row[N].t + kLatSmem);
         }
         o << "            }\n";
     }
@@ -445,7 +471,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
             H.n_back_terms++;
             if (!s.c && (++t % 3) == 0) {  // keep expressions shallow
                 o << "                const double s" << t << "@ = " << s.e << ";\n";
-                s = Val::E("s" + std::to_string(t) + "@");
+                s = Val::E("s" + std::to_string(t) + "@", s.t);
             }
         }
         const Val q = divide(s, i, "qq@", "                ");
@@ -453,8 +479,11 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         if (!Dv[i].c) o << "                if (fabs(" << Dv[i].e << ") < 1e-15) q" << i << "@ = 0.0;\n";
         if (opt.q_in_smem) o << "                " << S(Y0 + i) << " = q" << i << "@;\n";
         o << "            }\n";
-        Q[i] = opt.q_in_smem ? Val::E(S(Y0 + i)) : Val::E("q" + std::to_string(i) + "@");
+        Q[i] = opt.q_in_smem ? Val::E(S(Y0 + i), q.t + kLatSmem) : Val::E("q" + std::to_string(i) + "@", q.t);
+        H.crit_cycles = std::max(H.crit_cycles, Q[i].t);
     }
+    H.crit_lu_cycles = H.crit_cycles;
+    H.crit_cycles += 5 * kLatOp + 5 * kLatOp + kLatSqrt;  // damped update + square, 32-leaf tree, sqrt
     // ---- prediction check / per-lane generic redo ------------------------------------------------------------
     o << "            const bool redo@ = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu)) && !done@;\n"
          "            if (__any_sync(0xFFFFFFFFu, ANY(redo@))) {\n"
@@ -544,12 +573,18 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
 
     H.n_slots = n_slots;
     H.replicas = R;
-    H.smem_bytes = (size_t)n_slots * 8 * kTpb * R;
-    if (H.smem_bytes > kMaxSmem) throw std::runtime_error("specialize: per-instance state exceeds shared memory");
+    const size_t warp_bytes = (size_t)n_slots * 8 * 32 * R;
+    if (warp_bytes > kMaxSmem) throw std::runtime_error("specialize: per-instance state exceeds shared memory");
+    const int kTpb = 32 * (opt.warps_per_cta > 0 ? opt.warps_per_cta : pick_warps_per_cta(warp_bytes));
+    H.threads = kTpb;
+    H.smem_bytes = warp_bytes * (kTpb / 32);
+    if (H.smem_bytes > kMaxSmem) throw std::runtime_error("specialize: CTA state exceeds shared memory");
     std::ostringstream pro;
     pro << "// generated by specialize_tpi.cpp — thread-per-instance transient kernel for one topology and one\n"
            "// predicted pivot permutation; " << n_slots << " shared-memory doubles per instance, " << R
         << " instance(s) per thread, " << kTpb << " threads per CTA.\n"
+           "// longest dependency chain of one Newton iteration: " << H.crit_cycles << " cycles (LU + substitutions: "
+        << H.crit_lu_cycles << ")\n"
            "#include \"tpi_runtime.cuh\"\n"
            "using namespace csim;\n"
            "#define TPB " << kTpb << "\n"
@@ -559,7 +594,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
            "#define SPEC_NV " << mp.n_values << "\n"
            "#define SM(k, r) sm[((k) + (r) * NSLOTS) * TPB + tid]\n"
            "#define PRM(k, bb) ld_nohoist(params + (long long)(k) * B + (bb))\n"
-           "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kMaxSmem / (H.smem_bytes + 1024)))
+           "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kSmemPerSm / (H.smem_bytes + kCtaReserve)))
         << ")\n"
            "csim_tran_tpi(DevPlan P, DevTran T, long long B, const double* __restrict__ params,\n"
            "              double* __restrict__ xio, double* __restrict__ wave, int* __restrict__ iters_total,\n"
@@ -568,6 +603,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
            "              unsigned long long* __restrict__ stats) {\n"
            "    extern __shared__ double sm[];\n"
            "    const int tid = threadIdx.x;\n"
+
            "    const double dt = T.dt;\n"
            "    const unsigned long long F = 0x" << std::hex << (((unsigned long long)H.hash_hi << 32) | H.hash_lo) << std::dec
         << "ull;\n";
