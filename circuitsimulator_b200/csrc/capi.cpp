@@ -72,8 +72,15 @@ struct SpecState {
 // Thread-per-instance specialised transient kernel (specialize_tpi.cpp).
 struct TpiState {
     bool ready = false;
-    TpiHost host;
+    TpiHost host;  // one-warp CTAs: the fastest per warp (measured), default
     JitKernel k;
+    int warps_per_sm = 0, n_sms = 0;
+    // Same code in wider CTAs where that packs more warps into an SM's shared memory (dbmixer: 4 instead of 3).
+    // Built on the first launch whose batch needs fewer waves of CTAs that way.
+    bool wide_tried = false, wide_ready = false;
+    TpiHost host_wide;
+    JitKernel k_wide;
+    int warps_per_sm_wide = 0;
     unsigned long long* d_stats = nullptr;  // [2]: fallback solves, Newton solves
     std::string log;
 };
@@ -178,7 +185,7 @@ int spec_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     return CSIM_OK;
 }
 
-// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bits 8-9: replicas - 1, bits 12-14: warps per CTA); unset = defaults.
+// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bits 8-9: replicas - 1, bits 12-14: warps per CTA, bits 16-19: rows in flight); unset = defaults.
 TpiOptions tpi_options_from_env() {
     TpiOptions opt;
     if (const char* env = std::getenv("CSIM_TPI_OPTS")) {
@@ -190,58 +197,95 @@ TpiOptions tpi_options_from_env() {
         opt.mos_branchless = m & 16;
         opt.replicas = 1 + ((m >> 8) & 3);
         opt.warps_per_cta = (m >> 12) & 7;
+        if ((m >> 16) & 15) opt.rows_in_flight = (m >> 16) & 15;
     }
     return opt;
 }
 
-// Generates, compiles and loads the thread-per-instance kernel specialised to `perm`.
-// The generator sizes the CTA so that an SM's shared memory holds as many warps as possible; the driver's
-// occupancy answer for the loaded kernel is checked against the plain one-warp CTA and the kernel is rebuilt
-// that way if the wider CTA does not deliver (the answer is in the log either way).
+// Generates, compiles and loads one variant of the thread-per-instance kernel specialised to `perm`.
+// warps_per_cta: 1, or 0 = the CTA width that packs most warps into an SM's shared memory.
+int tpi_build_variant(const csim_plan* plan, const std::vector<int32_t>& perm, int warps_per_cta, TpiHost& host,
+                      JitKernel& k, int& warps_per_sm, std::string& log) {
+    jit_unload(k);
+    TpiOptions opt = tpi_options_from_env();
+    if (opt.warps_per_cta == 0) opt.warps_per_cta = warps_per_cta;
+    try {
+        host = generate_tran_tpi(plan->host, perm, opt);
+    } catch (const std::exception& e) {
+        log = e.what();
+        return fail(CSIM_E_UNSUPPORTED, log);
+    }
+    std::vector<char> cubin;
+    if (!jit_compile(host.source, "csim_tran_tpi.cu", jit_library_dir() + "/csrc", cubin, log)) {
+        log = "NVRTC: " + log;
+        return fail(CSIM_E_CUDA, log);
+    }
+    CU(jit_load(cubin, "csim_tran_tpi", k));
+    CU(cudaKernelSetAttributeForDevice(k.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)host.smem_bytes,
+                                       plan->device));
+    int ctas = 0;
+    CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas, reinterpret_cast<const void*>(k.kernel), host.threads,
+                                                     host.smem_bytes));
+    warps_per_sm = ctas * (host.threads / 32);
+    return CSIM_OK;
+}
+
 int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     TpiState& tp = plan->tpi;
     tp.ready = false;
+    tp.wide_tried = tp.wide_ready = false;
+    jit_unload(tp.k_wide);
     if (tp.d_stats) cudaFree(tp.d_stats);
     tp.d_stats = nullptr;
-    TpiOptions opt = tpi_options_from_env();
     std::string log;
-    int warps_per_sm = 0;
-    for (int attempt = 0; attempt < 2; ++attempt) {
-        jit_unload(tp.k);
-        try {
-            tp.host = generate_tran_tpi(plan->host, perm, opt);
-        } catch (const std::exception& e) {
-            tp.log = e.what();
-            return fail(CSIM_E_UNSUPPORTED, tp.log);
-        }
-        std::vector<char> cubin;
-        if (!jit_compile(tp.host.source, "csim_tran_tpi.cu", jit_library_dir() + "/csrc", cubin, log)) {
-            tp.log = "NVRTC: " + log;
-            return fail(CSIM_E_CUDA, tp.log);
-        }
-        CU(jit_load(cubin, "csim_tran_tpi", tp.k));
-        CU(cudaKernelSetAttributeForDevice(tp.k.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)tp.host.smem_bytes, plan->device));
-        int ctas = 0;
-        CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas, reinterpret_cast<const void*>(tp.k.kernel),
-                                                         tp.host.threads, tp.host.smem_bytes));
-        warps_per_sm = ctas * (tp.host.threads / 32);
-        const size_t warp_bytes = tp.host.smem_bytes / (size_t)(tp.host.threads / 32);
-        const int one_warp_ctas = (int)std::min<size_t>(32, 233472 / (warp_bytes + 1024));
-        if (tp.host.threads == 32 || opt.warps_per_cta > 0 || warps_per_sm > one_warp_ctas) break;
-        opt.warps_per_cta = 1;
+    const int rc = tpi_build_variant(plan, perm, 1, tp.host, tp.k, tp.warps_per_sm, log);
+    if (rc) {
+        tp.log = log;
+        return rc;
     }
+    CU(cudaDeviceGetAttribute(&tp.n_sms, cudaDevAttrMultiProcessorCount, plan->device));
     CU(cudaMalloc((void**)&tp.d_stats, 2 * sizeof(unsigned long long)));
     CU(cudaMemset(tp.d_stats, 0, 2 * sizeof(unsigned long long)));
     tp.log = "thread-per-instance: " + std::to_string(tp.host.n_slots) + " shared doubles per instance, " +
              std::to_string(tp.host.replicas) + " instance(s) per thread, " + std::to_string(tp.host.threads) +
-             " threads per CTA, " + std::to_string(warps_per_sm) + " warps resident per SM; per Newton iteration: " +
+             " threads per CTA, " + std::to_string(tp.warps_per_sm) + " warps resident per SM; per Newton iteration: " +
              std::to_string(tp.host.n_lu_divs) + " multipliers, " + std::to_string(tp.host.n_elim_updates) +
              " row updates, " + std::to_string(tp.host.n_back_terms) + " back-substitution terms, " +
              std::to_string(tp.host.n_g_adds) + "+" + std::to_string(tp.host.n_rhs_adds) + " assembly adds; longest dependency chain " +
              std::to_string(tp.host.crit_cycles) + " cycles" + (log.size() > 1 ? "\n" + log : "");
     tp.ready = true;
     return CSIM_OK;
+}
+
+// A warp of a 2-warp CTA runs ~14 % slower than a warp of a 1-warp CTA (B200, dbmixer: 4,415 ms against 3,874 ms
+// for the same 256 warps), so the wide variant is used only when it saves whole waves of CTAs.
+constexpr double kTpiWidePenalty = 1.15;
+
+// true -> launch the wide variant for a batch of B instances (builds it on first need)
+bool tpi_use_wide(const csim_plan* plan, int64_t B) {
+    TpiState& tp = plan->tpi;
+    std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
+    if (tp.warps_per_sm <= 0 || tp.n_sms <= 0) return false;
+    const int64_t warps = (B + 32 * tp.host.replicas - 1) / (32 * tp.host.replicas);
+    const int64_t cap = (int64_t)tp.n_sms * tp.warps_per_sm;
+    const int64_t waves = (warps + cap - 1) / cap;
+    if (waves <= 1) return false;
+    if (!tp.wide_tried) {
+        tp.wide_tried = true;
+        std::string log;
+        if (tpi_build_variant(plan, tp.host.perm, 0, tp.host_wide, tp.k_wide, tp.warps_per_sm_wide, log) == CSIM_OK &&
+            tp.host_wide.threads > 32 && tp.warps_per_sm_wide > tp.warps_per_sm) {
+            tp.wide_ready = true;
+            tp.log += "\nwide variant: " + std::to_string(tp.host_wide.threads) + " threads per CTA, " +
+                      std::to_string(tp.warps_per_sm_wide) + " warps resident per SM";
+        } else {
+            jit_unload(tp.k_wide);
+        }
+    }
+    if (!tp.wide_ready) return false;
+    const int64_t cap_w = (int64_t)tp.n_sms * tp.warps_per_sm_wide;
+    const int64_t waves_w = (warps + cap_w - 1) / cap_w;
+    return (double)waves_w * kTpiWidePenalty < (double)waves;
 }
 
 // Pivot order the reference's LU picks for instance 0 of the batch at its current state: one TRAN
@@ -400,11 +444,13 @@ cudaError_t tpi_launch(const csim_plan* plan, const DevTran& T, int64_t B, const
     if (e != cudaSuccess) return e;
     unsigned long long* stats = tp.d_stats;
     void* args[] = {&P, &Tc, &Bll, &params, &x, &wave, &iters_total, &iters_step, &pivot_hash, &status, &scratch, &stats};
-    const int T_ = tp.host.threads;
-    const int64_t per_cta = (int64_t)T_ * tp.host.replicas;
+    const bool wide = tpi_use_wide(plan, B);
+    const TpiHost& H = wide ? tp.host_wide : tp.host;
+    const int T_ = H.threads;
+    const int64_t per_cta = (int64_t)T_ * H.replicas;
     const unsigned blocks = (unsigned)((B + per_cta - 1) / per_cta);
-    e = cudaLaunchKernel(reinterpret_cast<const void*>(tp.k.kernel), dim3(blocks), dim3(T_), args, tp.host.smem_bytes,
-                         stream);
+    e = cudaLaunchKernel(reinterpret_cast<const void*>((wide ? tp.k_wide : tp.k).kernel), dim3(blocks), dim3(T_), args,
+                         H.smem_bytes, stream);
     cudaFreeAsync(scratch, stream);
     return e;
 }
@@ -534,6 +580,7 @@ void csim_plan_destroy(csim_plan* plan) {
         for (void* d : plan->spec.owned) cudaFree(d);
         jit_unload(plan->spec.k);
         jit_unload(plan->tpi.k);
+        jit_unload(plan->tpi.k_wide);
         if (plan->tpi.d_stats) cudaFree(plan->tpi.d_stats);
         jit_unload(plan->stamp_spec[0].k);
         jit_unload(plan->stamp_spec[1].k);

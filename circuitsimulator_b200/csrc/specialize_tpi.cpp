@@ -368,9 +368,17 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
             for (int t = 0; t < 4; ++t) o << "            " << S(mos_slot[op.out + t]) << " = " << mn(t) << ";\n";
     }
     // ---- rows: assemble, eliminate, park ----------------------------------------------------------------
+    // A row is emitted in SEGMENTS — assembly, one elimination step per earlier pivot row k with a structural
+    // non-zero at (i,k), parking — and up to opt.rows_in_flight rows are open at a time, their segments
+    // interleaved round-robin.  Step (i,k) only needs row k parked, so any such order is a topological order
+    // of the up-looking LU and every entry still receives its updates in ascending k (bit-identical).  The
+    // elimination steps of ONE row form a serial chain (multiplier -> update -> next multiplier, ~44 cycles
+    // per step); rows that do not feed each other fill those gaps, and the compiler's scheduling window is
+    // too short to find them when whole rows follow each other in the source.
     // generator-side description of the factorisation so far
     std::vector<Val> Dv(N), RDv(N), Yv(N);
     std::vector<std::map<int, Val>> Uv(N);
+    std::vector<bool> parked(N, false);
     char num[64];
     auto fabs_lit = [&](double v) { return lit(std::fabs(v)); };
     // a / pivot(k): exact rewrites for +-1 pivots, constant folding, otherwise the guarded split division
@@ -383,21 +391,30 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         H.n_lu_divs++;
         return Val::E(tmp, std::max(a.t, RDv[k].t) + kLatDiv);
     };
-    for (int i = 0; i < N; ++i) {
-        o << "            {  // position " << i << " = row " << perm[i] << "\n";
+    struct RowGen {
+        int i = 0;
         std::map<int, Val> row;
         std::set<int> declared;
-        auto assign = [&](int j, const Val& v) {  // j == N: right-hand side
-            const std::string name = (j == N ? std::string("rb") : "r" + std::to_string(j)) + "@";
-            if (v.c) {
-                row[j] = v;
-                return;
-            }
-            if (v.e == name) return;
-            o << "                " << (declared.count(j) ? "" : "double ") << name << " = " << v.e << ";\n";
-            declared.insert(j);
-            row[j] = Val::E(name, v.t);
-        };
+        std::vector<int> ks;  // elimination steps still to do, ascending
+        size_t next = 0;
+        bool assembled = false;
+    };
+    const char* ind = "            ";
+    auto assign = [&](RowGen& R, int j, const Val& v) {  // j == N: right-hand side
+        const std::string name =
+            (j == N ? "rb" + std::to_string(R.i) : "r" + std::to_string(R.i) + "_" + std::to_string(j)) + "@";
+        if (v.c) {
+            R.row[j] = v;
+            return;
+        }
+        if (v.e == name) return;
+        o << ind << (R.declared.count(j) ? "" : "double ") << name << " = " << v.e << ";\n";
+        R.declared.insert(j);
+        R.row[j] = Val::E(name, v.t);
+    };
+    auto emit_assembly = [&](RowGen& R) {
+        const int i = R.i;
+        o << ind << "// position " << i << " = row " << perm[i] << "\n";
         for (int j = 0; j <= N; ++j) {
             if (j < N && !A.pat[i][j]) continue;
             Val acc = j < N ? base[i][j] : Val::K(0.0);
@@ -405,59 +422,98 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
                 acc = t.sub ? sub(acc, val(t.value)) : add(acc, val(t.value));
                 (j < N ? H.n_g_adds : H.n_rhs_adds)++;
             }
-            assign(j, acc);
+            assign(R, j, acc);
         }
-        for (int k = 0; k < i; ++k) {
-            if (!A.pat[i][k]) continue;
-            const Val a = row[k];
-            // the reference would have picked this row instead of the predicted pivot (solver.hpp:46-56)
-            if (a.c && Dv[k].c) {
-                if (std::fabs(a.v) > std::fabs(Dv[k].v)) o << "                bad@ = true;\n";
-            } else {
-                o << "                bad@ = bad@ || (fabs(" << a.e << ") > "
-                  << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")") << ");\n";
-            }
-            std::snprintf(num, sizeof num, "f%d_%d@", i, k);
-            const Val f = divide(a, k, num, "                ");
-            for (int j : A.cols_k[k]) {
-                assign(j, sub(row[j], mul(f, Uv[k].at(j))));
-                H.n_elim_updates++;
-            }
-            assign(N, sub(row[N], mul(f, Yv[k])));
+        R.assembled = true;
+    };
+    auto emit_step = [&](RowGen& R, int k) {
+        const int i = R.i;
+        const Val a = R.row[k];
+        // the reference would have picked this row instead of the predicted pivot (solver.hpp:46-56)
+        if (a.c && Dv[k].c) {
+            if (std::fabs(a.v) > std::fabs(Dv[k].v)) o << ind << "bad@ = true;\n";
+        } else {
+            o << ind << "bad@ = bad@ || (fabs(" << a.e << ") > " << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")")
+              << ");\n";
         }
+        std::snprintf(num, sizeof num, "f%d_%d@", i, k);
+        const Val f = divide(a, k, num, ind);
+        for (int j : A.cols_k[k]) {
+            assign(R, j, sub(R.row[j], mul(f, Uv[k].at(j))));
+            H.n_elim_updates++;
+        }
+        assign(R, N, sub(R.row[N], mul(f, Yv[k])));
+    };
+    auto emit_park = [&](RowGen& R) {
+        const int i = R.i;
         // pivot of this position: singular / non-finite pivots go to the generic path
-        const Val d = row[i];
+        const Val d = R.row[i];
         if (d.c && (d.v == 1.0 || d.v == -1.0)) {
             Dv[i] = d;
         } else {
             const int sd = alloc(), srd = alloc();
-            const std::string dn = "r" + std::to_string(i) + "@";
-            if (d.c) o << "                const double " << dn << " = " << d.e << ";\n";
-            o << "                bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(C.lu_eps) << " && fabs(" << dn
+            const std::string dn = "r" + std::to_string(i) + "_" + std::to_string(i) + "@";
+            if (d.c) o << ind << "const double " << dn << " = " << d.e << ";\n";
+            o << ind << "bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(C.lu_eps) << " && fabs(" << dn
               << ") <= 0x1.fffffffffffffp+1023);\n"
-              << "                " << S(sd) << " = " << dn << ";\n"
-              << "                " << S(srd) << " = rcp_seq(" << dn << ");\n";
+              << ind << S(sd) << " = " << dn << ";\n"
+              << ind << S(srd) << " = rcp_seq(" << dn << ");\n";
             Dv[i] = Val::E(S(sd), d.t + kLatSmem);
             RDv[i] = Val::E(S(srd), d.t + kLatRcp + kLatSmem);
             H.n_rcp++;
         }
         for (int j : A.ucols[i]) {
-            const Val u = row[j];
+            const Val u = R.row[j];
             if (u.c) {
                 Uv[i][j] = u;
             } else {
                 const int su = alloc();
-                o << "                " << S(su) << " = " << u.e << ";\n";
+                o << ind << S(su) << " = " << u.e << ";\n";
                 Uv[i][j] = Val::E(S(su), u.t + kLatSmem);
             }
         }
-        if (row[N].c) {
-            Yv[i] = row[N];
+        if (R.row[N].c) {
+            Yv[i] = R.row[N];
         } else {
-            o << "                " << S(Y0 + i) << " = rb@;\n";
-            Yv[i] = Val::E(S(Y0 + i), row[N].t + kLatSmem);
+            o << ind << S(Y0 + i) << " = rb" << i << "@;\n";
+            Yv[i] = Val::E(S(Y0 + i), R.row[N].t + kLatSmem);
         }
-        o << "            }\n";
+        parked[i] = true;
+    };
+    {
+        const size_t W = (size_t)std::max(1, opt.rows_in_flight);
+        std::vector<RowGen> open;
+        int next_row = 0;
+        while (next_row < N || !open.empty()) {
+            while (open.size() < W && next_row < N) {
+                RowGen R;
+                R.i = next_row++;
+                for (int k = 0; k < R.i; ++k)
+                    if (A.pat[R.i][k]) R.ks.push_back(k);
+                open.push_back(std::move(R));
+            }
+            bool progressed = false;
+            for (size_t r = 0; r < open.size();) {
+                RowGen& R = open[r];
+                if (!R.assembled) {
+                    emit_assembly(R);
+                } else if (R.next < R.ks.size()) {
+                    if (!parked[R.ks[R.next]]) {  // waits for a row that is still open (a lower one: no deadlock)
+                        ++r;
+                        continue;
+                    }
+                    emit_step(R, R.ks[R.next++]);
+                } else {
+                    emit_park(R);
+                    open.erase(open.begin() + (long)r);
+                    progressed = true;
+                    continue;
+                }
+                progressed = true;
+                ++r;
+            }
+            if (!progressed) throw std::runtime_error("specialize: row schedule made no progress");
+        }
     }
     // ---- back substitution (include/solver.hpp:116-128) ---------------------------------------------------
     std::vector<Val> Q(N);
