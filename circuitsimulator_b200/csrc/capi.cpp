@@ -109,12 +109,15 @@ struct csim_batch {
     const csim_plan* plan = nullptr;
     int64_t B = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t copy_stream = nullptr;  // waveform chunks go home while the next chunk of timepoints is computed
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_chunk = nullptr;
     double* d_params = nullptr;
     double* d_x = nullptr;
     uint64_t* d_hash = nullptr;
     uint32_t* d_status = nullptr;
     int32_t* d_iters = nullptr;  // [max(ramp,1)][B], also reused for iters_total
+    double* d_wave = nullptr;    // device waveform of csim_batch_tran, kept between calls (grow-only): allocating and
+    size_t wave_bytes = 0;       // freeing gigabytes per call costs more than the copy it feeds
     float last_ms = 0.f;
 };
 
@@ -852,8 +855,11 @@ void csim_batch_destroy(csim_batch* b) {
     cudaFree(b->d_hash);
     cudaFree(b->d_status);
     cudaFree(b->d_iters);
+    cudaFree(b->d_wave);
     if (b->ev0) cudaEventDestroy(b->ev0);
     if (b->ev1) cudaEventDestroy(b->ev1);
+    if (b->ev_chunk) cudaEventDestroy(b->ev_chunk);
+    if (b->copy_stream) cudaStreamDestroy(b->copy_stream);
     if (b->stream) cudaStreamDestroy(b->stream);
     delete b;
 }
@@ -895,6 +901,12 @@ int csim_batch_dc(csim_batch* b, double* x, int32_t* iters, uint64_t* pivot_hash
 }
 
 // x_start == nullptr: DC operating point first (csim_batch_tran); else the transient starts from x_start [N][B]
+// csim_batch_tran with host buffers: waveforms of at least kChunkMinWaveBytes over at least kChunkMinSteps
+// timepoints are produced and copied home in kWaveChunks pieces (see batch_tran_impl)
+constexpr size_t kChunkMinWaveBytes = (size_t)256 << 20;
+constexpr int64_t kChunkMinSteps = 4096;
+constexpr int kWaveChunks = 8;
+
 static int batch_tran_impl(csim_batch* b, const csim_tran_args* a, const double* x_start, double* x_dc, double* x_final,
                            double* wave, int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash,
                            uint32_t* status) {
@@ -916,7 +928,6 @@ static int batch_tran_impl(csim_batch* b, const csim_tran_args* a, const double*
     auto cleanup = [&]() {
         cudaFree(d_table);
         cudaFree(d_group_b);
-        cudaFree(d_wave);
         cudaFree(d_its);
         cudaFree(d_total);
     };
@@ -939,7 +950,14 @@ static int batch_tran_impl(csim_batch* b, const csim_tran_args* a, const double*
         CUC(cudaMemcpyAsync(d_group_b, a->src_group_b, bytes, cudaMemcpyHostToDevice, b->stream));
     }
     if (wave_elems) {
-        CUC(cudaMalloc((void**)&d_wave, sizeof(double) * wave_elems));
+        if (b->wave_bytes < sizeof(double) * wave_elems) {
+            cudaFree(b->d_wave);
+            b->d_wave = nullptr;
+            b->wave_bytes = 0;
+            CUC(cudaMalloc((void**)&b->d_wave, sizeof(double) * wave_elems));
+            b->wave_bytes = sizeof(double) * wave_elems;
+        }
+        d_wave = b->d_wave;
         CUC(cudaMemsetAsync(d_wave, 0xFF, sizeof(double) * wave_elems, b->stream));  // NaN = "never written"
     }
     if (iters_step) {
@@ -965,20 +983,57 @@ static int batch_tran_impl(csim_batch* b, const csim_tran_args* a, const double*
         return rc;
     }
     if (x_dc) CUC(cudaMemcpyAsync(x_dc, b->d_x, sizeof(double) * (size_t)N * B, cudaMemcpyDeviceToHost, b->stream));
-    // ... then the step loop (255-420)
-    rc = csim_dev_tran(plan, B, b->d_params, &da, b->d_x, d_wave, d_total, d_its, b->d_hash, b->d_status, b->stream);
-    if (rc) {
-        cleanup();
-        return rc;
+    // ... then the step loop (255-420).  A long run with a large waveform is cut into chunks of timepoints (the
+    // kernels carry every piece of state across a step range: x, iteration totals, pivot hash, status): the rows
+    // of `wave` one chunk recorded go to the host on a second stream while the next chunk is computed, so the
+    // caller pays for the last chunk's copy only instead of the whole waveform's.
+    const int64_t span = (int64_t)a->step_end - a->step_begin;
+    int forced = 0;  // CSIM_WAVE_CHUNKS=n: chunk regardless of size (tests exercise the path on small batches)
+    if (const char* env = std::getenv("CSIM_WAVE_CHUNKS")) forced = std::atoi(env);
+    const bool chunked = wave && wave_elems && a->out_stride > 0 && a->wave_ld > 0 &&
+                         (forced > 1 ? span >= forced
+                                     : forced == 0 && wave_elems * sizeof(double) >= kChunkMinWaveBytes &&
+                                           span >= kChunkMinSteps);
+    const int n_chunks = chunked ? (forced > 1 ? forced : kWaveChunks) : 1;
+    if (chunked && !b->copy_stream) {
+        CUC(cudaStreamCreateWithFlags(&b->copy_stream, cudaStreamNonBlocking));
+        CUC(cudaEventCreateWithFlags(&b->ev_chunk, cudaEventDisableTiming));
+    }
+    for (int c = 0; c < n_chunks; ++c) {
+        csim_tran_args ca = da;
+        ca.step_begin = a->step_begin + (int32_t)(span * c / n_chunks);
+        ca.step_end = a->step_begin + (int32_t)(span * (c + 1) / n_chunks);
+        rc = csim_dev_tran(plan, B, b->d_params, &ca, b->d_x, d_wave, d_total, d_its, b->d_hash, b->d_status, b->stream);
+        if (rc) {
+            if (b->copy_stream) cudaStreamSynchronize(b->copy_stream);
+            cleanup();
+            return rc;
+        }
+        if (!chunked) break;
+        // rows of `wave` written by steps [step_begin, step_end): step s records row (s+1)/stride - 1 - r0 when
+        // (s+1) % stride == 0 and s >= out_begin_step
+        const int64_t stride = a->out_stride, r0 = a->out_begin_step / stride;
+        int64_t rlo = (ca.step_begin + stride) / stride - 1 - r0, rhi = ca.step_end / stride - r0;
+        if (rlo < 0) rlo = 0;
+        if (rhi > a->wave_ld) rhi = a->wave_ld;
+        if (rhi > rlo) {
+            CUC(cudaEventRecord(b->ev_chunk, b->stream));
+            CUC(cudaStreamWaitEvent(b->copy_stream, b->ev_chunk, 0));
+            CUC(cudaMemcpy2DAsync(wave + rlo, sizeof(double) * (size_t)a->wave_ld, d_wave + rlo,
+                                  sizeof(double) * (size_t)a->wave_ld, sizeof(double) * (size_t)(rhi - rlo),
+                                  (size_t)B * a->n_probes, cudaMemcpyDeviceToHost, b->copy_stream));
+        }
     }
     CUC(cudaEventRecord(b->ev1, b->stream));
     if (x_final) CUC(cudaMemcpyAsync(x_final, b->d_x, sizeof(double) * (size_t)N * B, cudaMemcpyDeviceToHost, b->stream));
-    if (wave && wave_elems) CUC(cudaMemcpyAsync(wave, d_wave, sizeof(double) * wave_elems, cudaMemcpyDeviceToHost, b->stream));
+    if (wave && wave_elems && !chunked)
+        CUC(cudaMemcpyAsync(wave, d_wave, sizeof(double) * wave_elems, cudaMemcpyDeviceToHost, b->stream));
     if (iters_total) CUC(cudaMemcpyAsync(iters_total, d_total, sizeof(int32_t) * B, cudaMemcpyDeviceToHost, b->stream));
     if (iters_step) CUC(cudaMemcpyAsync(iters_step, d_its, (size_t)nsteps * B, cudaMemcpyDeviceToHost, b->stream));
     if (pivot_hash) CUC(cudaMemcpyAsync(pivot_hash, b->d_hash, sizeof(uint64_t) * B, cudaMemcpyDeviceToHost, b->stream));
     if (status) CUC(cudaMemcpyAsync(status, b->d_status, sizeof(uint32_t) * B, cudaMemcpyDeviceToHost, b->stream));
     CUC(cudaStreamSynchronize(b->stream));
+    if (chunked) CUC(cudaStreamSynchronize(b->copy_stream));
     CUC(cudaEventElapsedTime(&b->last_ms, b->ev0, b->ev1));
     cleanup();
 #undef CUC

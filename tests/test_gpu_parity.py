@@ -246,6 +246,37 @@ def test_host_buffer_api_equals_device_api(torch):
         assert out["hash"][b] == np.uint64(ot["hash"]) and out["iters_total"][b] == ot["total"]
 
 
+@pytest.mark.parametrize("stride,begin", [(1, 0), (7, 30)])
+def test_host_buffer_api_chunked_waveform_copy(torch, monkeypatch, stride, begin):
+    """csim_batch_tran cuts a long run into chunks of timepoints and copies each chunk's waveform rows home while
+    the next chunk is computed; forced here on a small batch (CSIM_WAVE_CHUNKS): every output equals the
+    single-launch run bit for bit, with decimation and a late tstart."""
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    plan = make_plan(topo)
+    B, dt, ns = 5, float(g["dt"]), 131
+    P = perturb(topo.params, topo, B, 7)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    setup = capi.TranSetup(dt, ns, m, grp, tab, probes=np.array([8, 1], np.int32), out_stride=stride, out_begin_step=begin)
+    outs = []
+    for chunks in ("1", "5"):
+        monkeypatch.setenv("CSIM_WAVE_CHUNKS", chunks)
+        batch = capi.Batch(plan, B)
+        batch.set_params(P.T)
+        outs.append(batch.tran(setup, want_iters_step=True))
+    one, many = outs
+    assert not np.isnan(many["wave"]).any()
+    for k in ("x_dc", "x_final", "wave"):
+        assert_same_bits(many[k], one[k], k)
+    for k in ("iters_total", "iters_step", "hash", "status"):
+        assert np.array_equal(many[k], one[k]), k
+    od = O.dc(topo, P[2])
+    ot = O.tran(topo, P[2], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+    steps = [s for s in range(ns) if (s + 1) % stride == 0 and s >= begin]
+    assert_same_bits(many["wave"][2].T, ot["wave"][steps][:, [8, 1]], "chunked waveform vs oracle")
+    assert many["hash"][2] == np.uint64(ot["hash"]) and many["iters_total"][2] == ot["total"]
+
+
 def test_degenerate_parameters_follow_reference_rules(torch):
     """R == 0 skips the stamp, C <= 0 skips the companion, L <= 0 leaves an empty branch row -> singular LU ->
     zero vector (src/element.cpp:20-23, src/tanalisis.cpp:65,296, include/solver.hpp:58-61,94-97)."""
