@@ -34,6 +34,7 @@ EXPORTS = [
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
+    "csim_plan_specialize_variants", "csim_plan_generate_source_variants",
     "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
 ]
 
@@ -107,6 +108,8 @@ def lib():
             [C.c_void_p] * 7
         L.csim_plan_jit_mode.argtypes = [C.c_void_p, C.c_int]
         L.csim_plan_specialize.argtypes = [C.c_void_p, C.POINTER(C.c_int32)]
+        L.csim_plan_specialize_variants.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32)]
+        L.csim_plan_generate_source_variants.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_char_p, C.c_int32]
         L.csim_plan_spec_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_uint64),
                                           C.POINTER(C.c_uint64), C.c_char_p, C.c_int32]
         L.csim_plan_spec_source.argtypes = [C.c_void_p, C.c_char_p, C.c_int32]
@@ -193,6 +196,21 @@ class Plan:
         perm = _i32(perm)
         assert perm.size == self.n_unknowns
         _check(lib().csim_plan_specialize(self.handle, _ip(perm)), "csim_plan_specialize")
+
+    def specialize_variants(self, perms):
+        """Thread-per-instance kernel with several predicted permutations, perms[n_variants][N]."""
+        perms = np.ascontiguousarray(perms, np.int32)
+        assert perms.ndim == 2 and perms.shape[1] == self.n_unknowns
+        _check(lib().csim_plan_specialize_variants(self.handle, perms.shape[0], _ip(perms)), "csim_plan_specialize_variants")
+
+    def generate_source_variants(self, perms) -> str:
+        perms = np.ascontiguousarray(perms, np.int32)
+        n = lib().csim_plan_generate_source_variants(self.handle, perms.shape[0], _ip(perms), None, 0)
+        if n < 0:
+            _check(n, "csim_plan_generate_source_variants")
+        buf = C.create_string_buffer(n + 1)
+        lib().csim_plan_generate_source_variants(self.handle, perms.shape[0], _ip(perms), buf, n + 1)
+        return buf.value.decode()
 
     def spec_info(self):
         act, fb, sv = C.c_int32(), C.c_uint64(), C.c_uint64()

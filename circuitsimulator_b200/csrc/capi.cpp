@@ -2,6 +2,7 @@
 #include <cuda_runtime.h>
 
 #include <cmath>
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <memory>
@@ -82,6 +83,8 @@ struct TpiState {
     JitKernel k_wide;
     int warps_per_sm_wide = 0;
     unsigned long long* d_stats = nullptr;  // [2]: fallback solves, Newton solves
+    unsigned long long* d_miss = nullptr;   // permutations met by the generic redo path (specialize.hpp kTpiMiss*)
+    std::string history;                    // one line per variant added by the automatic mode
     std::string log;
 };
 
@@ -207,13 +210,13 @@ TpiOptions tpi_options_from_env() {
 
 // Generates, compiles and loads one variant of the thread-per-instance kernel specialised to `perm`.
 // warps_per_cta: 1, or 0 = the CTA width that packs most warps into an SM's shared memory.
-int tpi_build_variant(const csim_plan* plan, const std::vector<int32_t>& perm, int warps_per_cta, TpiHost& host,
-                      JitKernel& k, int& warps_per_sm, std::string& log) {
+int tpi_build_variant(const csim_plan* plan, const std::vector<std::vector<int32_t>>& perms, int warps_per_cta,
+                      TpiHost& host, JitKernel& k, int& warps_per_sm, std::string& log) {
     jit_unload(k);
     TpiOptions opt = tpi_options_from_env();
     if (opt.warps_per_cta == 0) opt.warps_per_cta = warps_per_cta;
     try {
-        host = generate_tran_tpi(plan->host, perm, opt);
+        host = generate_tran_tpi(plan->host, perms, opt);
     } catch (const std::exception& e) {
         log = e.what();
         return fail(CSIM_E_UNSUPPORTED, log);
@@ -233,15 +236,20 @@ int tpi_build_variant(const csim_plan* plan, const std::vector<int32_t>& perm, i
     return CSIM_OK;
 }
 
+int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& perms);
 int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
+    return tpi_build(plan, std::vector<std::vector<int32_t>>{perm});
+}
+int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& perms) {
     TpiState& tp = plan->tpi;
     tp.ready = false;
     tp.wide_tried = tp.wide_ready = false;
     jit_unload(tp.k_wide);
     if (tp.d_stats) cudaFree(tp.d_stats);
-    tp.d_stats = nullptr;
+    if (tp.d_miss) cudaFree(tp.d_miss);
+    tp.d_stats = tp.d_miss = nullptr;
     std::string log;
-    const int rc = tpi_build_variant(plan, perm, 1, tp.host, tp.k, tp.warps_per_sm, log);
+    const int rc = tpi_build_variant(plan, perms, 1, tp.host, tp.k, tp.warps_per_sm, log);
     if (rc) {
         tp.log = log;
         return rc;
@@ -249,13 +257,16 @@ int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     CU(cudaDeviceGetAttribute(&tp.n_sms, cudaDevAttrMultiProcessorCount, plan->device));
     CU(cudaMalloc((void**)&tp.d_stats, 2 * sizeof(unsigned long long)));
     CU(cudaMemset(tp.d_stats, 0, 2 * sizeof(unsigned long long)));
-    tp.log = "thread-per-instance: " + std::to_string(tp.host.n_slots) + " shared doubles per instance, " +
+    CU(cudaMalloc((void**)&tp.d_miss, sizeof(unsigned long long) * kTpiMissEntries * kTpiMissStride));
+    CU(cudaMemset(tp.d_miss, 0, sizeof(unsigned long long) * kTpiMissEntries * kTpiMissStride));
+    tp.log = "thread-per-instance: " + std::to_string(tp.host.perms.size()) + " predicted permutation(s), " +
+             std::to_string(tp.host.n_slots) + " shared doubles per instance, " +
              std::to_string(tp.host.replicas) + " instance(s) per thread, " + std::to_string(tp.host.threads) +
              " threads per CTA, " + std::to_string(tp.warps_per_sm) + " warps resident per SM; per Newton iteration: " +
              std::to_string(tp.host.n_lu_divs) + " multipliers, " + std::to_string(tp.host.n_elim_updates) +
              " row updates, " + std::to_string(tp.host.n_back_terms) + " back-substitution terms, " +
              std::to_string(tp.host.n_g_adds) + "+" + std::to_string(tp.host.n_rhs_adds) + " assembly adds; longest dependency chain " +
-             std::to_string(tp.host.crit_cycles) + " cycles" + (log.size() > 1 ? "\n" + log : "");
+             std::to_string(tp.host.crit_cycles) + " cycles" + tp.history + (log.size() > 1 ? "\n" + log : "");
     tp.ready = true;
     return CSIM_OK;
 }
@@ -276,7 +287,7 @@ bool tpi_use_wide(const csim_plan* plan, int64_t B) {
     if (!tp.wide_tried) {
         tp.wide_tried = true;
         std::string log;
-        if (tpi_build_variant(plan, tp.host.perm, 0, tp.host_wide, tp.k_wide, tp.warps_per_sm_wide, log) == CSIM_OK &&
+        if (tpi_build_variant(plan, tp.host.perms, 0, tp.host_wide, tp.k_wide, tp.warps_per_sm_wide, log) == CSIM_OK &&
             tp.host_wide.threads > 32 && tp.warps_per_sm_wide > tp.warps_per_sm) {
             tp.wide_ready = true;
             tp.log += "\nwide variant: " + std::to_string(tp.host_wide.threads) + " threads per CTA, " +
@@ -322,6 +333,10 @@ int spec_pilot(const csim_plan* plan, int64_t B, const double* d_params, const d
 // (almost) every solve: a lane that misses redoes the solve alone while its 31 neighbours wait.
 constexpr double kTpiMaxMissRate = 0.02;
 constexpr unsigned long long kTpiMinSolves = 20000;
+// Before giving the kernel up, further predicted permutations are added (one per re-evaluation, the one the
+// redo path met most often) while more than kTpiAdaptMissRate of the solves miss.
+constexpr double kTpiAdaptMissRate = 0.002;
+constexpr int kTpiMaxVariants = 8;
 
 // Kernel to use for this launch: 0 generic, 2 warp-per-instance, 3 thread-per-instance (compiled on first use).
 int spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const double* d_x, double dt,
@@ -330,11 +345,44 @@ int spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const
     TpiState& tp = plan->tpi;
     std::lock_guard<std::recursive_mutex> lock(sp.mu);
     if (sp.mode == 0) return 0;
-    if (sp.mode == 1 && sp.kind == 3 && tp.ready && tp.d_stats) {  // re-evaluate the automatic choice
+    if ((sp.mode == 1 || sp.mode == 3) && sp.kind == 3 && tp.ready && tp.d_stats) {  // re-evaluate the choice
         unsigned long long st[2] = {0, 0};
         cudaStreamSynchronize(stream);
-        if (cudaMemcpy(st, tp.d_stats, sizeof(st), cudaMemcpyDeviceToHost) == cudaSuccess && st[1] >= kTpiMinSolves &&
-            (double)st[0] > kTpiMaxMissRate * (double)st[1]) {
+        const bool have = cudaMemcpy(st, tp.d_stats, sizeof(st), cudaMemcpyDeviceToHost) == cudaSuccess &&
+                          st[1] >= kTpiMinSolves;
+        // first remedy: one more predicted permutation — the one the redo path met most often
+        if (have && (double)st[0] > kTpiAdaptMissRate * (double)st[1] && tp.d_miss &&
+            (int)tp.host.perms.size() < kTpiMaxVariants) {
+            std::vector<unsigned long long> tab((size_t)kTpiMissEntries * kTpiMissStride, 0);
+            int best = -1;
+            if (cudaMemcpy(tab.data(), tp.d_miss, tab.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) ==
+                cudaSuccess)
+                for (int e = 0; e < kTpiMissEntries; ++e) {
+                    const unsigned long long hsh = tab[(size_t)e * kTpiMissStride], cnt = tab[(size_t)e * kTpiMissStride + 1];
+                    if (!hsh || std::find(tp.host.hashes.begin(), tp.host.hashes.end(), hsh) != tp.host.hashes.end()) continue;
+                    if (best < 0 || cnt > tab[(size_t)best * kTpiMissStride + 1]) best = e;
+                }
+            if (best >= 0 && tab[(size_t)best * kTpiMissStride + 1] * 4 >= st[0] / 10) {  // worth a variant: >= 2.5 % of the misses
+                std::vector<std::vector<int32_t>> perms = tp.host.perms;
+                std::vector<int32_t> np(plan->host.N);
+                for (int i = 0; i < plan->host.N; ++i) np[i] = (int32_t)tab[(size_t)best * kTpiMissStride + 2 + i];
+                perms.push_back(np);
+                const std::string note = "\n" + std::to_string(st[0]) + " of " + std::to_string(st[1]) +
+                                         " solves missed the predicted pivot order -> variant " +
+                                         std::to_string(perms.size() - 1) + " added (met " +
+                                         std::to_string(tab[(size_t)best * kTpiMissStride + 1]) + " times)";
+                const std::vector<std::vector<int32_t>> old = tp.host.perms;
+                const std::string hist = tp.history;
+                tp.history += note;
+                if (tpi_build(plan, perms) != CSIM_OK) {
+                    tp.history = hist;
+                    if (tpi_build(plan, old) != CSIM_OK) sp.kind = 0;
+                }
+                st[0] = st[1] = 0;  // statistics restart with the new kernel
+            }
+        }
+        if (sp.mode == 1 && sp.kind == 3 && have && st[1] >= kTpiMinSolves && (double)st[0] > kTpiMaxMissRate * (double)st[1] &&
+            (int)tp.host.perms.size() >= kTpiMaxVariants) {
             tp.log += "\nautomatic mode: " + std::to_string(st[0]) + " of " + std::to_string(st[1]) +
                       " solves missed the predicted pivot order -> warp-per-instance kernel";
             sp.kind = 2;
@@ -446,6 +494,7 @@ cudaError_t tpi_launch(const csim_plan* plan, const DevTran& T, int64_t B, const
     cudaError_t e = cudaMallocAsync((void**)&scratch, sizeof(double) * (size_t)tp.host.n_scratch_rows * B, stream);
     if (e != cudaSuccess) return e;
     unsigned long long* stats = tp.d_stats;
+    Tc.miss = tp.d_miss;
     void* args[] = {&P, &Tc, &Bll, &params, &x, &wave, &iters_total, &iters_step, &pivot_hash, &status, &scratch, &stats};
     const bool wide = tpi_use_wide(plan, B);
     const TpiHost& H = wide ? tp.host_wide : tp.host;
@@ -1214,6 +1263,38 @@ int csim_plan_specialize(csim_plan* plan, const int32_t* perm) {
     rc = spec_build(plan, pv);
     if (rc == CSIM_OK) sp.kind = 2;
     return rc;
+}
+
+int csim_plan_specialize_variants(csim_plan* plan, int32_t n_variants, const int32_t* perms) {
+    int rc = need_device(plan, "csim_plan_specialize_variants");
+    if (rc) return rc;
+    if (!perms || n_variants < 1 || n_variants > kTpiMaxVariants)
+        return fail(CSIM_E_INVALID, "csim_plan_specialize_variants: 1..8 permutations expected");
+    std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
+    SpecState& sp = plan->spec;
+    sp.tried = true;
+    if (sp.mode == 0 || sp.mode == 2) sp.mode = 1;
+    const int N = plan->host.N;
+    std::vector<std::vector<int32_t>> pv;
+    for (int v = 0; v < n_variants; ++v) pv.emplace_back(perms + (size_t)v * N, perms + (size_t)(v + 1) * N);
+    rc = tpi_build(plan, pv);
+    if (rc == CSIM_OK) sp.kind = 3;
+    return rc;
+}
+
+int csim_plan_generate_source_variants(const csim_plan* plan, int32_t n_variants, const int32_t* perms, char* out,
+                                       int32_t cap) {
+    if (!plan || !perms || n_variants < 1) return fail(CSIM_E_INVALID, "csim_plan_generate_source_variants: bad argument");
+    try {
+        const int N = plan->host.N;
+        std::vector<std::vector<int32_t>> pv;
+        for (int v = 0; v < n_variants; ++v) pv.emplace_back(perms + (size_t)v * N, perms + (size_t)(v + 1) * N);
+        TpiHost th = generate_tran_tpi(plan->host, pv, tpi_options_from_env());
+        if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", th.source.c_str());
+        return (int)th.source.size();
+    } catch (const std::exception& e) {
+        return fail(CSIM_E_UNSUPPORTED, e.what());
+    }
 }
 
 int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, uint64_t* fallback_solves,

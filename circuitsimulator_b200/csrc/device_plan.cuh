@@ -44,6 +44,7 @@ struct DevTran {
     const int32_t* src_group_b;  // [n_sources][B] or nullptr
     const int32_t* probes;       // [n_probes]
     const uint8_t* skip;         // [B] or nullptr: instances with skip[b] != 0 are left untouched (steady-state driver)
+    unsigned long long* miss;    // thread-per-instance kernel: log of the permutations its redo path met, or nullptr
 };
 
 // Device-side tables of a specialised kernel (built by specialize.cpp).

@@ -83,8 +83,10 @@ bool jit_compile(const std::string& source, const std::string& name, const std::
         return false;
     }
     const std::string inc = "-I" + include_dir;
-    const char* opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=false", "-lineinfo", inc.c_str()};
-    rc = n.CompileProgram(prog, 5, opts);
+    // (177: generated code declares every static value, used or not)
+    const char* opts[] = {"--gpu-architecture=sm_100a", "--std=c++17", "--fmad=false", "-lineinfo", "--diag-suppress=177",
+                          inc.c_str()};
+    rc = n.CompileProgram(prog, 6, opts);
     size_t ls = 0;
     n.GetProgramLogSize(prog, &ls);
     if (ls > 1) {

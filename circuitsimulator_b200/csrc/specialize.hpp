@@ -43,7 +43,9 @@ size_t spec_smem_bytes(const HostPlan& hp, const SpecHost& sh);
 
 // ---- thread-per-instance transient kernel (specialize_tpi.cpp, tpi_runtime.cuh) -----------------
 struct TpiHost {
-    std::vector<int32_t> perm;
+    std::vector<int32_t> perm;                 // variant 0
+    std::vector<std::vector<int32_t>> perms;   // all variants
+    std::vector<uint64_t> hashes;              // pivot-hash contribution of each variant's permutation
     std::string source;  // entry: csim_tran_tpi
     int32_t threads = 32, replicas = 1, n_slots = 0, n_scratch_rows = 0;
     size_t smem_bytes = 0;
@@ -65,6 +67,12 @@ struct TpiOptions {
     int replicas = 1;            // instances advanced together by one thread (interleaved instruction streams)
 };
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt = TpiOptions());
+TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms,
+                          const TpiOptions& opt = TpiOptions());
+
+// Device-side log of the permutations the generic redo path met (tpi_generic_solve): kTpiMissEntries entries of
+// kTpiMissStride uint64 = { pivot-hash contribution (0 = free), count, perm[0..31] }.
+constexpr int kTpiMissEntries = 16, kTpiMissStride = 34;
 
 // ---- standalone assembly kernel (specialize_stamp.cpp) ---------------------------------------
 struct StampSpecHost {

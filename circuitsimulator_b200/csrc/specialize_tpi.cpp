@@ -174,23 +174,44 @@ Val mul(const Val& a, const Val& b) {
 }  // namespace
 
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt) {
+    return generate_tran_tpi(hp, std::vector<std::vector<int32_t>>{perm}, opt);
+}
+
+// Several predicted permutations ("variants"): the Newton body is emitted once per variant and every lane runs
+// the variant that held for its last solve (int var).  A lane whose variant misses redoes the solve generically
+// — which yields the permutation the reference actually took — and moves to the variant with that
+// permutation if there is one.  Circuits whose pivot order depends on the operating region (buffer.sp while
+// its stages switch) stay on straight-line code that way; lanes of one warp on different variants execute
+// the bodies one after the other.
+TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms, const TpiOptions& opt) {
     const std::string why = spec_unsupported_reason(hp);
     if (!why.empty()) throw std::runtime_error("specialize: " + why);
+    if (perms.empty()) throw std::runtime_error("specialize: no permutation");
     const ModeProgram& mp = hp.mode[CSIM_MODE_TRAN];
     const csim_constants& C = hp.consts;
-    const Analysis A = analyse(hp, perm);
-    const int N = A.N;
+    const int K = (int)perms.size();
+    std::vector<Analysis> As;
+    for (const auto& pm : perms) As.push_back(analyse(hp, pm));
+    const int N = As[0].N;
+    if (K > 1 && opt.replicas > 1) throw std::runtime_error("specialize: variants and replicas cannot be combined");
     TpiHost H;
-    H.perm = perm;
-    for (int i = 0; i < N; ++i) {  // pivot-hash contribution of the predicted permutation
-        uint32_t key = (uint32_t)i * 1024u + (uint32_t)perm[i] + 1u;
-        uint32_t lo = key * 0x9E3779B1u;
-        lo ^= lo >> 15;
-        uint32_t hi = key * 0x85EBCA77u;
-        hi ^= hi >> 13;
-        H.hash_lo += lo;
-        H.hash_hi += hi;
+    H.perm = perms[0];
+    H.perms = perms;
+    for (const auto& pm : perms) {  // pivot-hash contribution of each predicted permutation
+        uint32_t hlo = 0, hhi = 0;
+        for (int i = 0; i < N; ++i) {
+            uint32_t key = (uint32_t)i * 1024u + (uint32_t)pm[i] + 1u;
+            uint32_t lo = key * 0x9E3779B1u;
+            lo ^= lo >> 15;
+            uint32_t hi = key * 0x85EBCA77u;
+            hi ^= hi >> 13;
+            hlo += lo;
+            hhi += hi;
+        }
+        H.hashes.push_back(((uint64_t)hhi << 32) | hlo);
     }
+    H.hash_lo = (uint32_t)H.hashes[0];
+    H.hash_hi = (uint32_t)(H.hashes[0] >> 32);
 
     // ---- classify values ------------------------------------------------------------------------
     enum Kind { STATIC, STEP, SRC, MOS };
@@ -232,9 +253,12 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     };
     // static prefix sums: constant-folded, or one slot per distinct ordered term list
     std::map<std::vector<std::pair<int, bool>>, int> base_of;
-    std::vector<std::vector<Val>> base(N, std::vector<Val>(N, Val::K(0.0)));
+    std::vector<std::vector<std::vector<Val>>> bases(K, std::vector<std::vector<Val>>(N, std::vector<Val>(N, Val::K(0.0))));
+    for (int v = 0; v < K; ++v)
     for (int i = 0; i < N; ++i)
         for (int j = 0; j < N; ++j) {
+            const Analysis& A = As[v];
+            std::vector<std::vector<Val>>& base = bases[v];
             if (A.prefix[i][j].empty()) continue;
             bool all_c = true;
             for (const Term& t : A.prefix[i][j]) all_c = all_c && is_const[t.value];
@@ -253,9 +277,10 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         }
     // non-MOS, non-constant values referenced by the per-iteration terms
     std::map<int, int> val_slot;
+    for (int v = 0; v < K; ++v)
     for (int i = 0; i < N; ++i)
         for (int j = 0; j <= N; ++j)
-            for (const Term& t : A.rest[i][j])
+            for (const Term& t : As[v].rest[i][j])
                 if (kind[t.value] != MOS && !is_const[t.value] && !val_slot.count(t.value)) val_slot[t.value] = alloc();
     // static values needed again at every step (companion-model conductances) -> global scratch rows
     std::map<int, int> gs_row;
@@ -293,6 +318,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
          "    unsigned int st@ = 0, n_fallback@ = 0;\n"
          "    int total@ = 0;\n"
          "    bool dead@ = !live@, degen@ = false;\n";
+    if (K > 1) o << "    int var@ = 0;  // variant (predicted permutation) that held for this lane's last solve\n";
+    o << "";
     for (int i = 0; i < N; ++i) {
         if (opt.x_in_smem) o << "    " << S(X0 + i) << " = xio[(long long)" << i << " * B + bb@];\n";
         else o << "    double x" << i << "@ = xio[(long long)" << i << " * B + bb@];\n";
@@ -375,6 +402,19 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     // elimination steps of ONE row form a serial chain (multiplier -> update -> next multiplier, ~44 cycles
     // per step); rows that do not feed each other fill those gaps, and the compiler's scheduling window is
     // too short to find them when whole rows follow each other in the source.
+    if (K > 1)  // (a lane that is done may skip every variant's body)
+        for (int i = 0; i < N; ++i) o << "            double q" << i << "@ = 0.0;\n";
+    const int n_common = n_slots;  // slots below are shared by all variants; each variant parks its LU above
+    int n_slots_max = n_slots;
+    TpiHost H0;  // statistics of variant 0
+    for (int v = 0; v < K; ++v) {
+    const Analysis& A = As[v];
+    const std::vector<std::vector<Val>>& base = bases[v];
+    const std::vector<int32_t>& perm = perms[v];
+    n_slots = n_common;
+    if (K > 1)
+        o << "            if (__any_sync(0xFFFFFFFFu, var@ == " << v << " && !done@)) {\n"
+             "            if (var@ == " << v << ") {  // variant " << v << "\n";
     // generator-side description of the factorisation so far
     std::vector<Val> Dv(N), RDv(N), Yv(N);
     std::vector<std::map<int, Val>> Uv(N);
@@ -447,7 +487,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     auto emit_park = [&](RowGen& R) {
         const int i = R.i;
         // pivot of this position: singular / non-finite pivots go to the generic path
-        const Val d = R.row[i];
+        // (a permutation nobody's matrix can take may put a structural zero on the diagonal: constant 0 -> "bad")
+        const Val d = R.row.count(i) ? R.row[i] : Val::K(0.0);
         if (d.c && (d.v == 1.0 || d.v == -1.0)) {
             Dv[i] = d;
         } else {
@@ -517,7 +558,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     }
     // ---- back substitution (include/solver.hpp:116-128) ---------------------------------------------------
     std::vector<Val> Q(N);
-    for (int i = 0; i < N; ++i) o << "            double q" << i << "@;\n";
+    if (K == 1)
+        for (int i = 0; i < N; ++i) o << "            double q" << i << "@;\n";
     for (int i = N - 1; i >= 0; --i) {
         o << "            {\n";
         Val s = Yv[i];
@@ -532,11 +574,23 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
         }
         const Val q = divide(s, i, "qq@", "                ");
         o << "                q" << i << "@ = " << q.e << ";\n";
-        if (!Dv[i].c) o << "                if (fabs(" << Dv[i].e << ") < 1e-15) q" << i << "@ = 0.0;\n";
+        // solver.hpp:124-127 zeroes the unknown of a pivot below 1e-15; the pivot check above sends every
+        // |pivot| < lu_eps to the generic path, so the test is dead code unless lu_eps was lowered
+        if (!Dv[i].c && !(C.lu_eps >= 1e-15))
+            o << "                if (fabs(" << Dv[i].e << ") < 1e-15) q" << i << "@ = 0.0;\n";
         if (opt.q_in_smem) o << "                " << S(Y0 + i) << " = q" << i << "@;\n";
         o << "            }\n";
         Q[i] = opt.q_in_smem ? Val::E(S(Y0 + i), q.t + kLatSmem) : Val::E("q" + std::to_string(i) + "@", q.t);
         H.crit_cycles = std::max(H.crit_cycles, Q[i].t);
+    }
+    if (K > 1) o << "            }\n            }\n";
+    n_slots_max = std::max(n_slots_max, n_slots);
+    if (v == 0) H0 = H;
+    }  // variants
+    n_slots = n_slots_max;
+    {  // the reported statistics are those of variant 0
+        H.n_elim_updates = H0.n_elim_updates, H.n_lu_divs = H0.n_lu_divs, H.n_back_terms = H0.n_back_terms;
+        H.n_g_adds = H0.n_g_adds, H.n_rhs_adds = H0.n_rhs_adds, H.n_rcp = H0.n_rcp, H.crit_cycles = H0.crit_cycles;
     }
     H.crit_lu_cycles = H.crit_cycles;
     H.crit_cycles += 5 * kLatOp + 5 * kLatOp + kLatSqrt;  // damped update + square, 32-leaf tree, sqrt
@@ -547,18 +601,59 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
          "                if (redo@) {\n"
          "                    ++n_fallback@;\n"
          "                    double xl[SPEC_N], xo[SPEC_N];\n";
+    if (K > 1) o << "                    unsigned long long pc@ = 0;\n";
+    o << "";
     for (int i = 0; i < N; ++i) o << "                    xl[" << i << "] = " << xrd(i) << ";\n";
     o << "                    tpi_generic_solve<SPEC_N, SPEC_NV>(P, T, params, B, bb@, step, xl, scratch + (long long)" << XP0
-      << " * B, xo, h@, st@);\n";
+      << " * B, xo, h@, st@" << (K > 1 ? ", pc@" : "") << ");\n";
     for (int i = 0; i < N; ++i) o << "                    q" << i << "@ = xo[" << i << "];\n";
+    for (int v = 0; v < K && K > 1; ++v)  // the permutation the reference took: run that variant from now on
+        o << "                    if (pc@ == 0x" << std::hex << H.hashes[v] << std::dec << "ull) var@ = " << v << ";\n";
+    o << "                }\n"
+         "                //@END\n"
+         "            }\n";
+    {
+        std::ostringstream f;
+        for (int v = K - 1; v >= 1; --v) f << "var@ == " << v << " ? 0x" << std::hex << H.hashes[v] << std::dec << "ull : ";
+        f << "F";
+        o << "            if (!redo@ && !done@) h@ = (h@ ^ (" << f.str() << ")) * 0x100000001B3ull;\n";
+    }
+    // ---- damping, norm, convergence (src/tanalisis.cpp:359-376) -----------------------------------------------
+    // The reference throws when a solution entry is not finite.  A non-finite q(i) makes n(i) and the sum of
+    // squares non-finite (inf/NaN propagate through every operation below), so "sum of squares finite" proves
+    // all 31 entries finite with one comparison; only when it is not (overflow of a square counts too) are the
+    // entries themselves inspected, in a branch no lane normally takes.
+    for (int i = 0; i < N; ++i) {
+        const std::string xi = xrd(i), I = std::to_string(i);
+        if (opt.x_in_smem) o << "            const double xo" << I << "@ = " << xi << ";\n";
+        const std::string xv = opt.x_in_smem ? "xo" + I + "@" : xi;
+        o << "            const double n" << I << "@ = d_add(" << xv << ", d_mul(" << lit(C.tran_alpha) << ", d_sub(q" << I
+          << "@, " << xv << ")));\n"
+          << "            double e" << I << "@ = d_sub(n" << I << "@, " << xv << ");\n"
+          << "            e" << I << "@ = d_mul(e" << I << "@, e" << I << "@);\n";
+    }
+    // 32-leaf pairwise tree (oracle/csim_norm2.h); leaves >= N are +0 and adding +0 to a square is exact
+    {
+        std::vector<std::string> leaf(32);
+        for (int i = 0; i < 32; ++i) leaf[i] = i < N ? "e" + std::to_string(i) + "@" : "";
+        for (int s = 16; s >= 1; s >>= 1)
+            for (int i = 0; i < s; ++i) {
+                if (leaf[i + s].empty()) continue;
+                if (leaf[i].empty()) leaf[i] = leaf[i + s];
+                else leaf[i] = "d_add(" + leaf[i] + ", " + leaf[i + s] + ")";
+            }
+        o << "            const double ssq@ = " << leaf[0] << ";\n";
+    }
+    o << "            bool fin@ = finite_d(ssq@);\n"
+         "            if (__any_sync(0xFFFFFFFFu, ANY(!fin@ && !done@))) {\n"
+         "                //@BEGIN\n"
+         "                if (!fin@) {\n"
+         "                    fin@ = true;\n";
+    for (int i = 0; i < N; ++i) o << "                    fin@ = fin@ && finite_d(q" << i << "@);\n";
     o << "                }\n"
          "                //@END\n"
          "            }\n"
-         "            if (!redo@ && !done@) h@ = (h@ ^ F) * 0x100000001B3ull;\n";
-    // ---- damping, norm, convergence (src/tanalisis.cpp:359-376) -----------------------------------------------
-    o << "            bool fin@ = true;\n";
-    for (int i = 0; i < N; ++i) o << "            fin@ = fin@ && finite_d(q" << i << "@);\n";
-    o << "            //@BEGIN\n"
+         "            //@BEGIN\n"
          "            if (!done@) {\n"
          "                ++count@;\n"
          "                if (!fin@) {  // the reference throws here\n"
@@ -571,27 +666,10 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
          "            const bool upd@ = !done@;\n";
     for (int i = 0; i < N; ++i) {
         const std::string xi = xrd(i), I = std::to_string(i);
-        if (opt.x_in_smem) o << "            const double xo" << I << "@ = " << xi << ";\n";
-        const std::string xv = opt.x_in_smem ? "xo" + I + "@" : xi;
-        o << "            const double n" << I << "@ = d_add(" << xv << ", d_mul(" << lit(C.tran_alpha) << ", d_sub(q" << I
-          << "@, " << xv << ")));\n"
-          << "            double e" << I << "@ = d_sub(n" << I << "@, " << xv << ");\n"
-          << "            e" << I << "@ = d_mul(e" << I << "@, e" << I << "@);\n";
         if (opt.x_in_smem) o << "            if (upd@) " << xi << " = n" << I << "@;\n";
         else o << "            x" << I << "@ = upd@ ? n" << I << "@ : x" << I << "@;\n";
     }
-    // 32-leaf pairwise tree (oracle/csim_norm2.h); leaves >= N are +0 and adding +0 to a square is exact
-    {
-        std::vector<std::string> leaf(32);
-        for (int i = 0; i < 32; ++i) leaf[i] = i < N ? "e" + std::to_string(i) + "@" : "";
-        for (int s = 16; s >= 1; s >>= 1)
-            for (int i = 0; i < s; ++i) {
-                if (leaf[i + s].empty()) continue;
-                if (leaf[i].empty()) leaf[i] = leaf[i + s];
-                else leaf[i] = "d_add(" + leaf[i] + ", " + leaf[i + s] + ")";
-            }
-        o << "            const double err@ = sqrt(" << leaf[0] << ");\n";
-    }
+    o << "            const double err@ = sqrt(ssq@);\n";
     o << "            //@BEGIN\n"
          "            if (upd@) {\n"
          "                if (err@ < " << lit(C.tran_tol) << ") done@ = true;\n"
@@ -637,7 +715,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
     if (H.smem_bytes > kMaxSmem) throw std::runtime_error("specialize: CTA state exceeds shared memory");
     std::ostringstream pro;
     pro << "// generated by specialize_tpi.cpp — thread-per-instance transient kernel for one topology and one\n"
-           "// predicted pivot permutation; " << n_slots << " shared-memory doubles per instance, " << R
+           "// predicted pivot permutation (" << K << " variant(s)); " << n_slots << " shared-memory doubles per instance, " << R
         << " instance(s) per thread, " << kTpb << " threads per CTA.\n"
            "// longest dependency chain of one Newton iteration: " << H.crit_cycles << " cycles (LU + substitutions: "
         << H.crit_lu_cycles << ")\n"

@@ -171,6 +171,11 @@ int csim_plan_dims(const csim_plan* plan, int32_t* n_unknowns, int32_t* n_params
 int csim_plan_jit_mode(csim_plan* plan, int mode);
 /* Specialise now for perm[N] (perm[i] = original row expected at pivot position i). */
 int csim_plan_specialize(csim_plan* plan, const int32_t* perm);
+/* Thread-per-instance kernel with several predicted permutations, perms[n_variants][N] (1 <= n_variants <= 8):
+ * every lane runs the variant whose permutation its last solve took; a solve no variant predicts is redone
+ * generically, as always.  In automatic mode the library adds variants itself (one per re-evaluation, the
+ * permutation the redo path met most often) while more than 0.2 % of the solves miss.                 */
+int csim_plan_specialize_variants(csim_plan* plan, int32_t n_variants, const int32_t* perms);
 /* active: 0 none / 2 / 3 = kind of the specialised kernel in use; perm [N] (NULL ok); counters since load:
  * Newton solves done by the generic fallback / all Newton solves; log: generator + NVRTC messages. */
 int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, uint64_t* fallback_solves,
@@ -182,6 +187,9 @@ int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* 
 /* Same for either specialised transient kernel: kind 2 = warp per instance (csim_tran_spec),
  * kind 3 = thread per instance (csim_tran_tpi). */
 int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_t* perm, char* out, int32_t cap);
+/* Host-only: thread-per-instance source for perms[n_variants][N]. */
+int csim_plan_generate_source_variants(const csim_plan* plan, int32_t n_variants, const int32_t* perms, char* out,
+                                       int32_t cap);
 #endif
 
 /* Systems with more than 32 unknowns (the 200-stage ladder has 404) run on the large-matrix path, the

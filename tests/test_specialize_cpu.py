@@ -44,6 +44,21 @@ def test_generated_source_compiles_for_sm100a(name, kind):
     assert cs > 10000
 
 
+def test_multi_variant_source_compiles_for_sm100a():
+    """Two predicted permutations: both Newton bodies in one kernel, selected per lane."""
+    from circuitsimulator_b200 import capi
+    nvrtc = pytest.importorskip("cuda.bindings.nvrtc")
+    g, topo = load_golden("buffer")
+    plan = capi.Plan(topo.n_unknowns, topo.n_node_eq, topo.elem_type, topo.elem_flags, topo.elem_nodes,
+                     topo.elem_branch, topo.elem_param, topo.n_params, device=-1)
+    p0 = np.asarray(_perm(topo, g), np.int32)
+    p1 = p0.copy()
+    p1[[2, 5]] = p1[[5, 2]]
+    src = plan.generate_source_variants(np.stack([p0, p1]))
+    assert "(2 variant(s))" in src and "var_0 == 1" in src
+    assert _nvrtc_compile(nvrtc, src, b"tpi2.cu") > 10000
+
+
 def _nvrtc_compile(nvrtc, src, name):
     shim = (b"#pragma once\ntypedef signed char int8_t; typedef unsigned char uint8_t; typedef short int16_t; "
             b"typedef unsigned short uint16_t;\ntypedef int int32_t; typedef unsigned int uint32_t; "
