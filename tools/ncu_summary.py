@@ -24,6 +24,8 @@ WANT = ["Kernel Name", "gpu__time_duration.sum", "launch__grid_size", "launch__b
         "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio", "sm__icc_request_hit_rate.pct",
+        "smsp__issue_active.avg.per_cycle_active", "lts__t_sectors_srcunit_tex_op_read.sum",
         "sm__cycles_elapsed.max", "smsp__cycles_active.avg"]
 with open(out + "_ncu_lines.txt", "w") as f:
     for r in rows[2:]:
