@@ -34,7 +34,7 @@ EXPORTS = [
     "csim_plan_jit_mode", "csim_plan_specialize", "csim_plan_spec_info", "csim_plan_spec_source",
     "csim_plan_generate_source", "csim_dev_selftest_div",
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
-    "csim_plan_specialize_variants", "csim_plan_generate_source_variants",
+    "csim_plan_specialize_variants", "csim_plan_generate_source_variants", "csim_dev_selftest_tdiv",
     "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
 ]
 
@@ -115,6 +115,7 @@ def lib():
         L.csim_plan_spec_source.argtypes = [C.c_void_p, C.c_char_p, C.c_int32]
         L.csim_plan_generate_source.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_char_p, C.c_int32]
         L.csim_dev_selftest_div.argtypes = [C.c_int64] + [C.c_void_p] * 5
+        L.csim_dev_selftest_tdiv.argtypes = [C.c_int64] + [C.c_void_p] * 6
         L.csim_plan_stamp_info.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int64),
                                            C.POINTER(C.c_int64), C.c_char_p, C.c_int32]
         L.csim_plan_generate_stamp_source.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int32]
@@ -537,6 +538,18 @@ class Batch:
     @property
     def last_kernel_ms(self) -> float:
         return float(lib().csim_batch_last_kernel_ms(self.handle))
+
+
+def selftest_tdiv(a, b):
+    """(q, q_ref, in_range) on the device for float64 CUDA tensors a, b (see csim_dev_selftest_tdiv)."""
+    torch = _torch()
+    _dev_f64(a)
+    _dev_f64(b, a.shape)
+    q, qr = torch.empty_like(a), torch.empty_like(a)
+    ok = torch.empty(a.shape, dtype=torch.int32, device=a.device)
+    _check(lib().csim_dev_selftest_tdiv(a.numel(), _ptr(a), _ptr(b), _ptr(q), _ptr(qr), _ptr(ok), _stream()),
+           "csim_dev_selftest_tdiv")
+    return q, qr, ok
 
 
 def selftest_div(a, b):

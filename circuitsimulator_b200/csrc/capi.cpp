@@ -1386,6 +1386,13 @@ int csim_dev_selftest_div(int64_t n, const double* a, const double* b, double* q
     return CSIM_OK;
 }
 
+int csim_dev_selftest_tdiv(int64_t n, const double* a, const double* b, double* q, double* q_ref, int32_t* in_range,
+                           void* stream) {
+    if (n <= 0 || !a || !b || !q || !q_ref || !in_range) return fail(CSIM_E_INVALID, "csim_dev_selftest_tdiv: bad argument");
+    CU(launch_tdiv_selftest(n, a, b, q, q_ref, in_range, (cudaStream_t)stream));
+    return CSIM_OK;
+}
+
 float csim_batch_last_kernel_ms(const csim_batch* b) { return b ? b->last_ms : 0.f; }
 
 }  // extern "C"

@@ -575,6 +575,24 @@ __global__ void div_selftest_kernel(int64_t n, const double* __restrict__ a, con
     }
 }
 
+// tdiv (thread-per-instance kernel): quotient, IEEE quotient, and whether tdiv's own range guards accept the
+// division (in_range == 1 promises q == q_ref bit for bit)
+__global__ void tdiv_selftest_kernel(int64_t n, const double* __restrict__ a, const double* __restrict__ b,
+                                     double* __restrict__ q, double* __restrict__ q_ref, int32_t* __restrict__ in_range) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        unsigned int glo = 0xFFFFFFFFu, ghi = 0u;
+        q[i] = tdiv(a[i], b[i], rcp_seq(b[i]), glo, ghi);
+        q_ref[i] = a[i] / b[i];
+        in_range[i] = !(glo < 0x03600000u || ghi > 0x7FEFFFFFu);
+    }
+}
+
+cudaError_t launch_tdiv_selftest(int64_t n, const double* a, const double* b, double* q, double* q_ref,
+                                 int32_t* in_range, cudaStream_t stream) {
+    tdiv_selftest_kernel<<<1184, 256, 0, stream>>>(n, a, b, q, q_ref, in_range);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_div_selftest(int64_t n, const double* a, const double* b, double* q_split, double* q_ref,
                                 cudaStream_t stream) {
     div_selftest_kernel<<<1184, 256, 0, stream>>>(n, a, b, q_split, q_ref);

@@ -495,8 +495,9 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
             const int sd = alloc(), srd = alloc();
             const std::string dn = "r" + std::to_string(i) + "_" + std::to_string(i) + "@";
             if (d.c) o << ind << "const double " << dn << " = " << d.e << ";\n";
-            o << ind << "bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(C.lu_eps) << " && fabs(" << dn
-              << ") <= 0x1.fffffffffffffp+1023);\n"
+            // (rcp_seq needs a normal reciprocal: 2^-1021 <= |pivot| <= 2^1021; anything else is redone generically)
+            o << ind << "bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(std::max(C.lu_eps, 0x1p-1021)) << " && fabs(" << dn
+              << ") <= 0x1p+1021);\n"
               << ind << S(sd) << " = " << dn << ";\n"
               << ind << S(srd) << " = rcp_seq(" << dn << ");\n";
             Dv[i] = Val::E(S(sd), d.t + kLatSmem);

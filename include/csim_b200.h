@@ -252,6 +252,11 @@ int csim_plan_generate_stamp_source(const csim_plan* plan, int mode, char* out, 
  * division of a[i]/b[i], q_ref[i] = the compiler's IEEE a[i]/b[i]; they must be bit-identical. */
 int csim_dev_selftest_div(int64_t n, const double* a, const double* b, double* q_split, double* q_ref,
                           void* stream);
+/* Same for the thread-per-instance kernel's division (2^-1021 <= |b| <= 2^1021, the kernel's pivot test): q[i], the IEEE quotient and
+ * in_range[i] = 1 where the division's own range guards accept it — there q must equal q_ref bit for bit
+ * (elsewhere the kernel redoes the solve with true divisions). */
+int csim_dev_selftest_tdiv(int64_t n, const double* a, const double* b, double* q, double* q_ref, int32_t* in_range,
+                           void* stream);
 #endif
 
 /* ===================== device-pointer entry points ======================== */

@@ -66,6 +66,44 @@ def test_config3_buffer_monte_carlo_65536(torch):
     assert np.array_equal(t2["hash"].cpu().numpy(), t["hash"][lo:lo + n].cpu().numpy())
 
 
+def test_dbmixer_batch_beyond_one_wave_uses_wide_ctas(torch):
+    """dbmixer.sp, 16,384 Monte-Carlo instances (config 4's batch size): more warps than one wave of one-warp CTAs
+    holds (3 per SM), so the launch uses the 2-warp-CTA variant of the thread-per-instance kernel (4 per SM).
+    A shard of the batch run alone (one-warp CTAs) gives the same bits; a subset equals the oracle."""
+    from circuitsimulator_b200 import capi
+    from circuitsimulator_b200.netlist import Netlist
+    g, _ = load_golden("dbmixer")
+    nl = Netlist(str(g["netlist"]))
+    topo = _topo_of(nl)
+    B, ns = 16384, 24
+    P = nl.monte_carlo(B, SEED + 5)
+    plan = nl.plan()
+    setup = nl.tran_setup(probes=np.arange(nl.n_unknowns, dtype=np.int32), n_steps=ns)
+    params = torch.from_numpy(P).cuda()
+    d = capi.dc(plan, params)
+    t = capi.tran(plan, params, d["x"].clone(), setup, pivot_hash=d["hash"].clone(), status=d["status"].clone())
+    torch.cuda.synchronize()
+    info = plan.spec_info()
+    assert info["kind"] == 3, info["log"]
+    if torch.cuda.get_device_properties(0).multi_processor_count * 3 * 32 < B:
+        assert "wide variant" in info["log"], info["log"]
+    wave = t["wave"].cpu().numpy()
+    assert int(t["status"].max()) == 0 and np.isfinite(wave).all()
+    m, grp, tab = O.make_source_tables(topo, nl.params, setup.dt, ns)
+    hashes = t["hash"].cpu().numpy().view(np.uint64)
+    for b in (0, 31, 32, 63, 8191, 8192, 14207, 14208, 16383):
+        od = O.dc(topo, P[:, b])
+        ot = O.tran(topo, P[:, b], setup.dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(wave[b].T, ot["wave"], f"instance {b}")
+        assert hashes[b] == np.uint64(ot["hash"])
+    lo, n = 9000, 700
+    ps = params[:, lo:lo + n].contiguous()
+    d2 = capi.dc(plan, ps)
+    t2 = capi.tran(plan, ps, d2["x"].clone(), setup, pivot_hash=d2["hash"].clone(), status=d2["status"].clone())
+    assert_same_bits(t2["wave"].cpu().numpy(), wave[lo:lo + n], "shard (one-warp CTAs) vs whole batch (wide CTAs)")
+    assert np.array_equal(t2["hash"].cpu().numpy(), t["hash"][lo:lo + n].cpu().numpy())
+
+
 def test_config4_amplitude_frequency_sweep_per_instance_sources(torch):
     """dbmixer.sp LO sweep (config 4's batch layout at 6 x 5 points): every instance has its own LO amplitude
     (a parameter) and frequency (its own host-tabulated sin row, selected through src_group_b).  Transient

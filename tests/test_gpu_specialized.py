@@ -71,6 +71,41 @@ def test_split_division_is_bit_identical_to_ieee_division(torch):
     assert np.array_equal(qr[~nan].view(np.uint64), host[~nan].view(np.uint64))
 
 
+def test_guarded_division_of_the_thread_per_instance_kernel(torch):
+    """tdiv (spec_runtime.cuh): wherever its own range guards accept a division the quotient is IEEE a / b bit for
+    bit — signed zeros included (the sign comes from a*rcp(b)) — and ordinary magnitudes are always accepted, so the
+    redo path is not taken for them.  Divisors span 2^-1021 .. 2^1021 (the kernel's pivot test; outside it the
+    solve is redone generically)."""
+    from circuitsimulator_b200 import capi
+    rng = np.random.default_rng(1)
+    n = 1 << 22
+    a = rng.normal(size=n) * 10.0 ** rng.uniform(-30, 30, n)
+    b = rng.normal(size=n) * 10.0 ** rng.uniform(-30, 30, n)
+    k = 1 << 18
+    a[:k] = np.ldexp(rng.uniform(1, 2, k), rng.integers(-1074, 1023, k)) * rng.choice([-1.0, 1.0], k)
+    b[:k] = np.ldexp(rng.uniform(1, 2, k), rng.integers(-1021, 1021, k)) * rng.choice([-1.0, 1.0], k)
+    b[k:2 * k] = np.nextafter(np.ldexp(1.0, rng.integers(-500, 500, k)), 0)        # mantissa all ones
+    a[2 * k:3 * k] = rng.integers(1, 1 << 20, k).astype(float)                        # exact small quotients
+    b[2 * k:3 * k] = rng.integers(1, 1 << 20, k).astype(float)
+    a[3 * k:4 * k] = rng.choice([0.0, -0.0], k)                                       # exact zeros of either sign
+    a[4 * k:5 * k] = rng.integers(1, 1 << 30, k) * 5e-324 * rng.choice([-1.0, 1.0], k)  # denormal numerators
+    b[4 * k:5 * k] = rng.integers(1, 64, k).astype(float)                             # ... with halfway quotients
+    b[b == 0.0] = 1.0
+    q, qr, ok = capi.selftest_tdiv(dev(torch, a), dev(torch, b))
+    torch.cuda.synchronize()
+    q, qr, ok = q.cpu().numpy(), qr.cpu().numpy(), ok.cpu().numpy().astype(bool)
+    with np.errstate(all="ignore"):
+        host = a / b
+    assert np.array_equal(qr.view(np.uint64), host.view(np.uint64))
+    diff = ok & (q.view(np.uint64) != qr.view(np.uint64))
+    assert not diff.any(), (int(diff.sum()), [(float.hex(x), float.hex(y), float.hex(u), float.hex(v))
+                                              for x, y, u, v in zip(a[diff][:6], b[diff][:6], q[diff][:6], qr[diff][:6])])
+    assert ok[3 * k:4 * k].all() and np.array_equal(np.signbit(q[3 * k:4 * k]), np.signbit(host[3 * k:4 * k]))
+    assert not ok[4 * k:5 * k].any()                       # denormal numerators are never trusted
+    plain = (np.abs(a) > 1e-200) & (np.abs(a) < 1e200) & (np.abs(host) > 1e-200) & (np.abs(host) < 1e200)
+    assert ok[plain].all() and plain.sum() > n // 2
+
+
 KINDS = pytest.mark.parametrize("kind", [2, 3])  # 2: warp per instance (csim_tran_spec), 3: thread per instance (csim_tran_tpi)
 ENTRY = {2: "csim_tran_spec", 3: "csim_tran_tpi"}
 
