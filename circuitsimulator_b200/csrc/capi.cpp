@@ -257,8 +257,8 @@ int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& pe
     CU(cudaDeviceGetAttribute(&tp.n_sms, cudaDevAttrMultiProcessorCount, plan->device));
     CU(cudaMalloc((void**)&tp.d_stats, 2 * sizeof(unsigned long long)));
     CU(cudaMemset(tp.d_stats, 0, 2 * sizeof(unsigned long long)));
-    CU(cudaMalloc((void**)&tp.d_miss, sizeof(unsigned long long) * kTpiMissEntries * kTpiMissStride));
-    CU(cudaMemset(tp.d_miss, 0, sizeof(unsigned long long) * kTpiMissEntries * kTpiMissStride));
+    CU(cudaMalloc((void**)&tp.d_miss, sizeof(unsigned long long) * kTpiMissWords));
+    CU(cudaMemset(tp.d_miss, 0, sizeof(unsigned long long) * kTpiMissWords));
     tp.log = "thread-per-instance: " + std::to_string(tp.host.perms.size()) + " predicted permutation(s), " +
              std::to_string(tp.host.n_slots) + " shared doubles per instance, " +
              std::to_string(tp.host.replicas) + " instance(s) per thread, " + std::to_string(tp.host.threads) +

@@ -402,8 +402,23 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     // elimination steps of ONE row form a serial chain (multiplier -> update -> next multiplier, ~44 cycles
     // per step); rows that do not feed each other fill those gaps, and the compiler's scheduling window is
     // too short to find them when whole rows follow each other in the source.
-    if (K > 1)  // (a lane that is done may skip every variant's body)
-        for (int i = 0; i < N; ++i) o << "            double q" << i << "@ = 0.0;\n";
+    // Several variants: a lane whose variant misses first tries the variant that FOLLOWED it the last time any lane
+    // left it (succ[], a hint table behind the miss log, racy on purpose) in a second pass over the same bodies, and
+    // only then takes the generic redo.  Instances of one batch walk through the same sequence of operating
+    // regions, so after the first of them every change of permutation costs one more straight-line solve instead
+    // of a dense generic one.
+    if (K > 1) {
+        for (int i = 0; i < N; ++i) o << "            double q" << i << "@ = 0.0;\n";  // (done lanes skip all bodies)
+        o << "            bool need@ = !done@, missed@ = false;\n"
+             "            int var_before@ = var@;\n"
+             "#pragma unroll 1\n"
+             "            for (int pass = 0; pass < 2; ++pass) {\n"
+             "            if (need@) {\n"
+             "                bad@ = degen@;\n"
+             "                glo@ = 0xFFFFFFFFu;\n"
+             "                ghi@ = 0u;\n"
+             "            }\n";
+    }
     const int n_common = n_slots;  // slots below are shared by all variants; each variant parks its LU above
     int n_slots_max = n_slots;
     TpiHost H0;  // statistics of variant 0
@@ -413,8 +428,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     const std::vector<int32_t>& perm = perms[v];
     n_slots = n_common;
     if (K > 1)
-        o << "            if (__any_sync(0xFFFFFFFFu, var@ == " << v << " && !done@)) {\n"
-             "            if (var@ == " << v << ") {  // variant " << v << "\n";
+        o << "            if (__any_sync(0xFFFFFFFFu, var@ == " << v << " && need@)) {\n"
+             "            if (var@ == " << v << " && need@) {  // variant " << v << "\n";
     // generator-side description of the factorisation so far
     std::vector<Val> Dv(N), RDv(N), Yv(N);
     std::vector<std::map<int, Val>> Uv(N);
@@ -596,7 +611,22 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     H.crit_lu_cycles = H.crit_cycles;
     H.crit_cycles += 5 * kLatOp + 5 * kLatOp + kLatSqrt;  // damped update + square, 32-leaf tree, sqrt
     // ---- prediction check / per-lane generic redo ------------------------------------------------------------
-    o << "            const bool redo@ = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu)) && !done@;\n"
+    if (K > 1)
+        o << "            if (need@) missed@ = bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu);\n"
+             "            need@ = false;\n"
+             "            if (pass == 0 && missed@ && !degen@ && T.miss) {\n"
+             "                const int w = (int)T.miss[TPI_SUCC0 + var@] - 1;\n"
+             "                if (w >= 0 && w < " << K << " && w != var@) {\n"
+             "                    var@ = w;\n"
+             "                    need@ = true;\n"
+             "                }\n"
+             "            }\n"
+             "            if (!__any_sync(0xFFFFFFFFu, need@)) break;\n"
+             "            }  // pass\n"
+             "            const bool redo@ = missed@;\n";
+    else
+    o << "            const bool redo@ = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu)) && !done@;\n";
+    o << ""
          "            if (__any_sync(0xFFFFFFFFu, ANY(redo@))) {\n"
          "                //@BEGIN\n"
          "                if (redo@) {\n"
@@ -608,8 +638,14 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     o << "                    tpi_generic_solve<SPEC_N, SPEC_NV>(P, T, params, B, bb@, step, xl, scratch + (long long)" << XP0
       << " * B, xo, h@, st@" << (K > 1 ? ", pc@" : "") << ");\n";
     for (int i = 0; i < N; ++i) o << "                    q" << i << "@ = xo[" << i << "];\n";
-    for (int v = 0; v < K && K > 1; ++v)  // the permutation the reference took: run that variant from now on
-        o << "                    if (pc@ == 0x" << std::hex << H.hashes[v] << std::dec << "ull) var@ = " << v << ";\n";
+    if (K > 1) {  // the permutation the reference took: run that variant from now on, and leave the hint
+        o << "                    int learned@ = -1;\n";
+        for (int v = 0; v < K; ++v)
+            o << "                    if (pc@ == 0x" << std::hex << H.hashes[v] << std::dec << "ull) learned@ = " << v << ";\n";
+        o << "                    var@ = learned@ >= 0 ? learned@ : var_before@;\n"
+             "                    if (learned@ >= 0 && learned@ != var_before@ && T.miss)\n"
+             "                        T.miss[TPI_SUCC0 + var_before@] = (unsigned long long)(learned@ + 1);\n";
+    }
     o << "                }\n"
          "                //@END\n"
          "            }\n";
@@ -729,6 +765,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
            "#define SPEC_NV " << mp.n_values << "\n"
            "#define SM(k, r) sm[((k) + (r) * NSLOTS) * TPB + tid]\n"
            "#define PRM(k, bb) ld_nohoist(params + (long long)(k) * B + (bb))\n"
+           "#define TPI_SUCC0 " << kTpiMissEntries * kTpiMissStride << "\n"
            "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kSmemPerSm / (H.smem_bytes + kCtaReserve)))
         << ")\n"
            "csim_tran_tpi(DevPlan P, DevTran T, long long B, const double* __restrict__ params,\n"
