@@ -139,7 +139,7 @@ def run_reference(args):
     val = pts / (ms / 1e3)
     sample = f"{per_step} instances x {pts // per_step} timepoints per step, one instance per host thread"
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": METRIC.replace("dbmixer", args.netlist), "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(args), "sample": sample},
@@ -399,7 +399,7 @@ def run_ours(args):
             cpu = {"value": None, "unit": UNIT, "cores": None, "kind": "reference", "sample": f"failed: {ex}"}
 
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "metric": METRIC.replace("dbmixer", args.netlist), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {"workload": workload_name(args), "netlist": args.netlist, "instances_per_gpu": B,
