@@ -60,17 +60,17 @@ for mask in sys.argv[2:]:
     sass = subprocess.run(["cuobjdump", "-sass", "-fun", "csim_tran_tpi", out + "bin"], capture_output=True, text=True).stdout
     open(out[:-3] + ".sass", "w").write(sass)
     ins = parse(sass)
-    best = (0, 0, 0)
+    spans = []
     for a, t, h in ins:
-        if "BRA" in t:
-            mm = re.search(r"BRA\S*\s+(?:\S+,\s*)?0x([0-9a-f]+)", t)
-            if mm and int(mm.group(1), 16) < a and a - int(mm.group(1), 16) > best[0]:
-                # the outermost loop is the time loop; the Newton loop is the second largest span
-                best = (a - int(mm.group(1), 16), int(mm.group(1), 16), a)
-    spans = sorted(((a - int(re.search(r"0x([0-9a-f]+)", t).group(1), 16), int(re.search(r"0x([0-9a-f]+)", t).group(1), 16), a)
-                    for a, t, h in ins if "BRA" in t and re.search(r"0x([0-9a-f]+)", t) and int(re.search(r"0x([0-9a-f]+)", t).group(1), 16) < a), reverse=True)
-    # Newton loop: the largest span strictly inside the time loop (or the largest if only one)
-    newton = spans[1] if len(spans) > 1 and spans[1][1] >= spans[0][1] and spans[1][2] <= spans[0][2] else spans[0]
+        mm = re.search(r"BRA\S*\s+(?:\S+,\s*)?0x([0-9a-f]+)", t) if "BRA" in t else None
+        if mm and int(mm.group(1), 16) < a:
+            spans.append((a - int(mm.group(1), 16), int(mm.group(1), 16), a))
+    # Newton loop: the smallest backward-branch span that holds most of the kernel's FP64 arithmetic of ONE variant
+    # (the time loop and the kernel as a whole are larger spans around it)
+    is64 = lambda t: re.match(r"(@!?U?P\d+ )?D(ADD|MUL|FMA)", t) is not None
+    tot64 = sum(1 for a, t, h in ins if is64(t))
+    newton = min((sp for sp in spans if sum(1 for a, t, h in ins if sp[1] <= a <= sp[2] and is64(t)) >= 0.5 * tot64),
+                 default=max(spans))
     sel = [x for x in ins if newton[1] <= x[0] <= newton[2]]
     st = sum((h >> 41) & 0xF for a, t, h in sel)
     f64 = sum(1 for a, t, h in sel if re.match(r"(@!?U?P\d+ )?D(ADD|MUL|FMA|SETP)", t))
