@@ -1317,7 +1317,33 @@ int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, u
     if (fallback_solves) *fallback_solves = st[0] + st2[0];
     if (solves) *solves = st[1] + st2[1];
     std::string all = sp.log;
-    if (!tp.log.empty()) all = tp.log + (all.empty() ? "" : "\n" + all);
+    std::string redo_log;  // what the generic redo path met since the kernel was built: per known variant / unknown orders
+    if (kind == 3 && plan->device >= 0 && tp.d_miss) {
+        std::vector<unsigned long long> tab((size_t)kTpiMissWords, 0);
+        if (cudaMemcpy(tab.data(), tp.d_miss, tab.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess) {
+            unsigned long long unknown = 0;
+            int distinct = 0;
+            for (int e = 0; e < kTpiMissEntries; ++e) {
+                const unsigned long long hsh = tab[(size_t)e * kTpiMissStride], cnt = tab[(size_t)e * kTpiMissStride + 1];
+                if (!hsh) continue;
+                const auto it = std::find(tp.host.hashes.begin(), tp.host.hashes.end(), hsh);
+                if (it == tp.host.hashes.end()) {
+                    unknown += cnt;
+                    ++distinct;
+                } else {
+                    redo_log += " variant " + std::to_string(it - tp.host.hashes.begin()) + ": " + std::to_string(cnt) + ";";
+                }
+            }
+            if (!redo_log.empty() || distinct)
+                redo_log = "\nredone solves by the order the reference took:" + redo_log + " other orders (" +
+                           std::to_string(distinct) + " distinct logged): " + std::to_string(unknown);
+        }
+    }
+    if (!tp.log.empty()) {
+        const size_t nl = tp.log.find('\n');  // summary line, then the redo log, then history and compiler messages
+        all = tp.log.substr(0, nl) + redo_log + (nl == std::string::npos ? "" : tp.log.substr(nl)) +
+              (all.empty() ? "" : "\n" + all);
+    }
     if (log && log_cap > 0) std::snprintf(log, (size_t)log_cap, "%s", all.c_str());
     return CSIM_OK;
 }
