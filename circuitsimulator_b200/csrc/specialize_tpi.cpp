@@ -402,23 +402,21 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     // elimination steps of ONE row form a serial chain (multiplier -> update -> next multiplier, ~44 cycles
     // per step); rows that do not feed each other fill those gaps, and the compiler's scheduling window is
     // too short to find them when whole rows follow each other in the source.
-    // Several variants: a lane whose variant misses tries the others in further passes over the same bodies — first
-    // the variant that FOLLOWED it the last time any lane left it (succ[], a hint table behind the miss log, racy on
-    // purpose), then the rest in order of discovery (= decreasing frequency) — and only when none holds takes the
-    // generic redo.  Nearly every miss of buffer.sp ends in a permutation some variant already has (csim_plan_spec_info's
-    // redo log), so a change of permutation costs a few more straight-line solves instead of a dense generic one.
+    // Several variants: a lane whose variant misses first tries the variant that FOLLOWED it the last time any lane
+    // left it (succ[], a hint table behind the miss log, racy on purpose) in a second pass over the same bodies, and
+    // only then takes the generic redo.  Instances of one batch walk through the same sequence of operating
+    // regions, so after the first of them every change of permutation costs one more straight-line solve instead
+    // of a dense generic one.
     if (K > 1) {
         for (int i = 0; i < N; ++i) o << "            double q" << i << "@ = 0.0;\n";  // (done lanes skip all bodies)
         o << "            bool need@ = !done@, missed@ = false;\n"
-             "            const int var_before@ = var@;\n"
-             "            unsigned int tried@ = 0u;\n"
+             "            int var_before@ = var@;\n"
              "#pragma unroll 1\n"
-             "            for (int pass = 0; pass < " << K << "; ++pass) {\n"
+             "            for (int pass = 0; pass < 2; ++pass) {\n"
              "            if (need@) {\n"
              "                bad@ = degen@;\n"
              "                glo@ = 0xFFFFFFFFu;\n"
              "                ghi@ = 0u;\n"
-             "                tried@ |= 1u << var@;\n"
              "            }\n";
     }
     const int n_common = n_slots;  // slots below are shared by all variants; each variant parks its LU above
@@ -616,24 +614,16 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     if (K > 1)
         o << "            if (need@) missed@ = bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu);\n"
              "            need@ = false;\n"
-             "            if (pass + 1 < " << K << " && missed@ && !degen@) {\n"
-             "                int w = -1;\n"
-             "                if (pass == 0 && T.miss) {\n"
-             "                    w = (int)T.miss[TPI_SUCC0 + var_before@] - 1;\n"
-             "                    if (w < 0 || w >= " << K << " || ((tried@ >> w) & 1u)) w = -1;\n"
-             "                }\n"
-             "                const unsigned int rest = ~tried@ & " << ((1u << K) - 1u) << "u;\n"
-             "                if (w < 0 && rest) w = __ffs((int)rest) - 1;\n"
-             "                if (w >= 0) {\n"
+             "            if (pass == 0 && missed@ && !degen@ && T.miss) {\n"
+             "                const int w = (int)T.miss[TPI_SUCC0 + var@] - 1;\n"
+             "                if (w >= 0 && w < " << K << " && w != var@) {\n"
              "                    var@ = w;\n"
              "                    need@ = true;\n"
              "                }\n"
              "            }\n"
              "            if (!__any_sync(0xFFFFFFFFu, need@)) break;\n"
              "            }  // pass\n"
-             "            const bool redo@ = missed@;\n"
-             "            if (!missed@ && var@ != var_before@ && T.miss)  // a later pass held: the hint for the next lane\n"
-             "                T.miss[TPI_SUCC0 + var_before@] = (unsigned long long)(var@ + 1);\n";
+             "            const bool redo@ = missed@;\n";
     else
     o << "            const bool redo@ = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu)) && !done@;\n";
     o << ""

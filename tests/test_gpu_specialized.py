@@ -202,9 +202,9 @@ def test_degenerate_and_chunked_through_specialised_kernel(torch, kind):
 
 def test_variants_switch_per_lane_after_a_miss(torch):
     """Two predicted permutations, the FIRST one wrong (identity) and the second the one partial pivoting takes:
-    every lane's first solve misses on variant 0, a second pass over the bodies finds that variant 1 holds and the
-    lane stays there.  Results equal the generic kernel's bit for bit; only the real pivot-order changes of
-    buffer.sp (neither variant predicts them) go through the generic redo path, as with one variant."""
+    every lane misses its first solve, learns from the redo which variant holds and runs that one from then on.
+    Results equal the generic kernel's bit for bit; only the first solve of each lane (plus the real pivot-order
+    changes of buffer.sp) goes through the redo path."""
     from circuitsimulator_b200 import capi
     g, topo = load_golden("buffer")
     B, dt, ns = 40, float(g["dt"]), 120
@@ -225,7 +225,8 @@ def test_variants_switch_per_lane_after_a_miss(torch):
     i1, i2 = one.spec_info(), two.spec_info()
     assert i2["kind"] == 3 and "2 predicted permutation(s)" in i2["log"], i2["log"]
     assert i1["solves"] == i2["solves"]
-    assert abs(i2["fallback_solves"] - i1["fallback_solves"]) <= 2 * B, (i1, i2)
+    # B lanes miss once more each (their first solve), nothing else changes
+    assert i1["fallback_solves"] < i2["fallback_solves"] <= i1["fallback_solves"] + 2 * B, (i1, i2)
 
 
 def test_automatic_mode_adds_variants_then_picks_the_kernel_by_miss_rate(torch):
