@@ -51,6 +51,9 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=0, help="instances in the CPU baseline sample (0 = 2 per thread)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--strong-total", type=int, default=65536,
+                    help="strong-scaling record: this many instances split over the N GPUs, one timed run (0 = skip)")
+    ap.add_argument("--strong-out-stride", type=int, default=100)
     return ap.parse_args()
 
 
@@ -104,17 +107,18 @@ def measured_peaks():
 
 # ------------------------------------------------------------------------------------------
 def cpu_reference_leg(nl_name, n_inst, n_threads, tran_steps):
-    """The UNMODIFIED reference (oracle/_ref), one instance per host thread at a time."""
+    """The UNMODIFIED reference (oracle/_ref), one instance per host thread at a time.
+    Nothing of the product is on this path: the netlist is parsed by the reference's own parser (O.Ref), the
+    Monte-Carlo draw is the oracle's restatement of the recipe, the timed wall is inside ref_run_batch."""
     from oracle import oraclelib as O
-    from circuitsimulator_b200.netlist import Netlist
-    nl = Netlist(load_netlist_text(nl_name))
-    topo = O.Topology(nl.n_unknowns, nl.n_node_eq, nl.elem_type, nl.elem_flags, nl.elem_nodes, nl.elem_branch,
-                      nl.elem_param, nl.n_params, nl.params, nl.node_names, nl.elem_names)
-    P = nl.monte_carlo(n_inst, SEED)
-    tran = dict(nl.tran)
+    ref = O.Ref(load_netlist_text(nl_name))
+    topo = ref.topology()
+    tran = ref.tran_cfg()
+    ref.close()
+    P = O.monte_carlo(topo, n_inst, SEED)  # [n_inst, P]
     if tran_steps:
         tran["tstop"] = tran["tstep"] * tran_steps
-    texts = [O.netlist_from_params(topo, P[:, b], tran=tran) for b in range(n_inst)]
+    texts = [O.netlist_from_params(topo, P[b], tran=tran) for b in range(n_inst)]
     wall, pts = O.ref_run_batch(texts, n_threads)
     return wall, pts
 
@@ -138,6 +142,8 @@ def run_reference(args):
     ms = 1e3 * float(np.mean(times))
     val = pts / (ms / 1e3)
     sample = f"{per_step} instances x {pts // per_step} timepoints per step, one instance per host thread"
+    maps = open("/proc/self/maps").read() if os.path.exists("/proc/self/maps") else ""
+    assert "libcsim_b200" not in maps, "the reference arm must not map the product library"
     print(json.dumps({
         "impl": "reference", "metric": METRIC.replace("dbmixer", args.netlist), "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -154,6 +160,44 @@ def workload_name(args):
     return (f"{args.netlist}.sp DC operating point + transient ({n}), {args.instances_per_gpu} Monte-Carlo instances "
             f"per GPU ({args.instances_per_gpu * args.gpus} total; 65,536 at 8 GPUs), 5% uniform parameter spread, "
             f"seed {SEED}")
+
+
+# ------------------------------------------------------------------------------------------
+def parity_check(args, out, wave, probes, n_steps, nl):
+    """Instance 0 of rank 0 (the nominal circuit) of the LAST TIMED step against the reference-pinned golden
+    fixture — the fixture was generated from the unmodified reference by tests/golden/make_golden.py; nothing
+    under oracle/ is executed here.  Bitwise on doubles and the pivot hash, exact on the Newton total."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", f"{args.netlist}_nominal.npz"))
+    full = n_steps == nl.n_steps
+    res = {"instance": 0, "golden": f"tests/golden/{args.netlist}_nominal.npz", "full_length": bool(full)}
+    bits = lambda a: np.ascontiguousarray(a, np.float64).view(np.uint64)  # noqa: E731
+    w0 = wave[0].cpu().numpy()  # [n_probes, n_out]
+    stride = args.out_stride
+    checks = {}
+    if args.netlist == "dbmixer":
+        if full and 100 % stride == 0:
+            mine = w0[:, 100 // stride - 1:: 100 // stride]
+            checks["wave_every_100th_of_50000"] = bool(np.array_equal(bits(mine.T), bits(g["wave_dec100"][:, probes])))
+        elif stride == 1:
+            k = min(n_steps, g["wave_first"].shape[0])
+            checks[f"wave_first_{k}"] = bool(np.array_equal(bits(w0[:, :k].T), bits(g["wave_first"][:k][:, probes])))
+    else:
+        if stride == 1:
+            k = min(n_steps, g["wave"].shape[0])
+            checks[f"wave_first_{k}"] = bool(np.array_equal(bits(w0[:, :k].T), bits(g["wave"][:k][:, probes])))
+    if full:
+        want_total = int(g["iters_step"].astype(np.int64).sum())
+        res["newton_total"] = int(out["iters_total"][0].item())
+        res["newton_total_golden"] = want_total
+        checks["newton_total"] = res["newton_total"] == want_total
+        checks["pivot_hash"] = bool(out["hash"][:1].cpu().numpy().view(np.uint64)[0] == np.uint64(g["hash"]))
+        xf = g["x_final"] if "x_final" in g.files else g["wave"][-1]
+        checks["x_final_bits"] = bool(np.array_equal(bits(out["x"][:, 0].cpu().numpy()), bits(xf)))
+    res["checks"] = checks
+    res["ok"] = bool(checks) and all(checks.values())
+    if not res["ok"]:
+        raise SystemExit(f"bench.py: PARITY FAILURE against the golden fixture: {json.dumps(res)}")
+    return res
 
 
 # ------------------------------------------------------------------------------------------
@@ -232,11 +276,21 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def one_step():
+    kev = []  # (before DC, between DC and transient, after transient) events of every timed step
+
+    def one_step(timed=False):
         h, st = capi.new_diag(B, dev)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)] if timed else None
+        if timed:
+            ev[0].record()
         d = capi.dc(plan, params, h, st)
+        if timed:
+            ev[1].record()
         iters_total.zero_()
         t = capi.tran(plan, params, d["x"], setup, wave=wave, iters_total=iters_total, pivot_hash=h, status=st)
+        if timed:
+            ev[2].record()
+            kev.append(ev)
         return t
 
     for _ in range(args.warmup):
@@ -249,10 +303,12 @@ def run_ours(args):
     barrier()
     e0.record()
     for _ in range(args.steps):
-        out = one_step()
+        out = one_step(timed=True)
     e1.record()
     barrier()
     ms_step = e0.elapsed_time(e1) / args.steps
+    dc_ms = float(np.mean([ev[0].elapsed_time(ev[1]) for ev in kev]))      # launch duration of the DC kernel
+    tran_ms = float(np.mean([ev[1].elapsed_time(ev[2]) for ev in kev]))    # ... of the fused transient kernel
     clocks = sampler.stop() if rank == 0 else None
     tms = torch.tensor([ms_step], dtype=torch.float64, device=dev)
     if world > 1:
@@ -261,6 +317,49 @@ def run_ours(args):
     value = world * B * n_steps / (ms_step / 1e3)
     newton_total = int(out["iters_total"].sum().item())
     status_or = int(out["status"].max().item())
+
+    # ---- parity of the run that was just timed: instance 0 of rank 0's shard is the nominal circuit, whose
+    # reference-pinned run is the golden fixture (tests/golden/<netlist>_nominal.npz, made by make_golden.py from
+    # the unmodified reference): final state and pivot hash bit for bit, Newton total, every 100th waveform row
+    parity = None
+    if rank == 0:
+        parity = parity_check(args, out, wave, probes, n_steps, nl)
+
+    # ---- strong scaling: a FIXED total (65,536 instances) split over the N GPUs, one timed run, decimated output
+    strong = None
+    if args.strong_total and args.strong_total % world == 0:
+        Bs_ = args.strong_total // world
+        if Bs_ == B:
+            strong = {"total_instances": args.strong_total, "instances_per_gpu": Bs_, "value": value, "unit": UNIT,
+                      "ms": ms_step, "out_stride": args.out_stride, "note": "same shard size as the main run"}
+        else:
+            ssetup = nl.tran_setup(probes=probes, out_stride=args.strong_out_stride, n_steps=n_steps)
+            sparams = torch.from_numpy(shard.shard_params(nl, args.strong_total, rank, world, SEED)).to(dev)
+            swave = torch.empty((Bs_, len(probes), max(ssetup.n_out, 1)), dtype=torch.float64, device=dev)
+            stot = torch.zeros((Bs_,), dtype=torch.int32, device=dev)
+
+            def strong_step():
+                h, st = capi.new_diag(Bs_, dev)
+                d = capi.dc(plan, sparams, h, st)
+                stot.zero_()
+                return capi.tran(plan, sparams, d["x"], ssetup, wave=swave, iters_total=stot, pivot_hash=h, status=st)
+
+            strong_step()  # warm-up (kernel variants, clocks)
+            barrier()
+            q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            q0.record()
+            sout = strong_step()
+            q1.record()
+            barrier()
+            sms = torch.tensor([q0.elapsed_time(q1)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(sms, op=dist.ReduceOp.MAX)
+            strong = {"total_instances": args.strong_total, "instances_per_gpu": Bs_,
+                      "value": args.strong_total * n_steps / (float(sms.item()) / 1e3), "unit": UNIT,
+                      "ms": float(sms.item()), "out_stride": args.strong_out_stride,
+                      "status_or": int(sout["status"].max().item()),
+                      "note": "one timed run after one warm-up, device-resident, max over ranks"}
+            del sparams, swave, stot, sout
 
     # ---- e2e: the host-buffer C-ABI call (csim_batch_tran): H2D params + tables, D2H waveforms + diagnostics
     e2e = None
@@ -360,28 +459,43 @@ def run_ours(args):
             traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
     except Exception:
         pass
-    roofline = {"kernel": "csim_stamp_spec<TRAN>" if sinfo["active"] else "stamp_csr_kernel<TRAN>", "bound": "hbm",
-                "achieved": achieved, "peak": peaks["hbm_gbs"],
-                "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_src,
-                "algorithmic_bytes_per_launch": bytes_per_inst * Bs, "peak_kind": peak_kind,
-                "bytes_per_instance": bytes_per_inst, "bytes_per_instance_survey_formula": 8 * (P + N + N + nnz + N),
-                "instances": Bs, "ms": stamp_ms,
-                "l2": "inputs+outputs %.2f GB > 126 MB L2" % (bytes_per_inst * Bs / 1e9)}
+    roofline_stamp = {"kernel": "csim_stamp_spec<TRAN>" if sinfo["active"] else "stamp_csr_kernel<TRAN>", "bound": "hbm",
+                      "achieved": achieved, "peak": peaks["hbm_gbs"],
+                      "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "traffic_source": traffic_src,
+                      "algorithmic_bytes_per_launch": bytes_per_inst * Bs, "peak_kind": peak_kind,
+                      "bytes_per_instance": bytes_per_inst, "bytes_per_instance_survey_formula": 8 * (P + N + N + nnz + N),
+                      "instances": Bs, "ms": stamp_ms, "in_timed_region": False,
+                      "l2": "inputs+outputs %.2f GB > 126 MB L2" % (bytes_per_inst * Bs / 1e9)}
     del sp, sx, sxp, ssv, svals, srhs
 
+    # ---- roofline of the DOMINANT kernel of the timed region: the fused transient (FP64 pipe, not HBM: state stays
+    # on chip).  achieved = useful FP64 operations of one launch (structural non-zeros of one Newton iteration x the
+    # Newton iterations the launch ran) / mean launch duration (CUDA events around the launch on the
+    # launching stream, inside the timed loop); peak = separate DMUL+DADD throughput measured in THIS run
+    # (csim_dev_fp64_peak; FMA is not allowed on the reference's expressions).
     fl = symbolic_flops(nl, plan, capi, torch)
-    newton_per_s = world * newton_total / (ms_step / 1e3)
-    fp64_peak = 18.46  # Tflop/s, separate DMUL+DADD (FMA is not allowed on this path), measured: profiles/r1_microbench_fp64.txt
+    fp64_peak = capi.fp64_peak(local)
     fused_kind = plan.spec_info().get("kind", 0)
-    roofline_fused = {"kernel": {3: "csim_tran_tpi (NVRTC, thread per instance)", 2: "csim_tran_spec (NVRTC, warp per instance)"}
-                      .get(fused_kind, "tran_kernel (generic)") + " + dc_kernel", "bound": "fp64-latency",
-                      "useful_tflops": newton_per_s / world * fl["useful"] / 1e12,
-                      "dense_equiv_tflops": newton_per_s / world * fl["dense"] / 1e12,
-                      "peak": fp64_peak, "unit": "TFLOP/s (separate mul/add, per GPU)",
-                      "frac_useful": newton_per_s / world * fl["useful"] / 1e12 / fp64_peak,
-                      "frac_dense_equiv": newton_per_s / world * fl["dense"] / 1e12 / fp64_peak,
-                      "flops_per_newton_iter": fl, "newton_iters_per_timepoint": newton_total / (B * n_steps),
-                      "hbm_bytes_per_timepoint": 8 * len(probes) / args.out_stride}
+    kname = {3: "csim_tran_tpi (NVRTC, thread per instance)", 2: "csim_tran_spec (NVRTC, warp per instance)"}.get(
+        fused_kind, "tran_kernel (generic)")
+    tran_tflops = newton_total * fl["useful"] / (tran_ms / 1e3) / 1e12
+    tj = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "tran_traffic.json")))
+        if tj.get("netlist") != args.netlist:
+            tj = None
+    except Exception:
+        tj = None
+    roofline = {"kernel": kname, "bound": "fp64", "achieved": tran_tflops, "peak": fp64_peak,
+                "unit": "TFLOP/s", "frac": tran_tflops / fp64_peak if fp64_peak else None,
+                "traffic": tj["dram_bytes_per_launch"] if tj else None, "traffic_source": tj["source"] if tj else None,
+                "peak_kind": "separate DMUL+DADD (no FMA), measured in this run by csim_dev_fp64_peak",
+                "ms_per_launch": tran_ms, "share_of_step": tran_ms / ms_step, "dc_kernel_ms": dc_ms,
+                "useful_flops_per_newton_iter": fl["useful"], "newton_iters_per_launch": newton_total,
+                "flops_per_newton_iter": fl, "newton_iters_per_timepoint": newton_total / (B * n_steps),
+                "hbm_bytes_per_timepoint": 8 * len(probes) / args.out_stride,
+                "dense_equiv_tflops": newton_total * fl["dense"] / (tran_ms / 1e3) / 1e12,
+                "note": "dense_equiv counts what the reference executes (zeros included); it is a work measure, not a utilisation"}
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -408,7 +522,8 @@ def run_ours(args):
                          % (wave.numel() * 8 / 1e9),
                    "parallelism": f"instances sharded over {world} GPU(s), no data-path collective"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": 2 * args.steps,
-        "roofline": roofline, "roofline_fused": roofline_fused, "cpu_baseline": cpu,
+        "roofline": roofline, "roofline_stamp": roofline_stamp, "cpu_baseline": cpu, "parity_check": parity,
+        "strong": strong,
         "newton_iterations": newton_total, "status_or": status_or, "gather_ms": gather_ms,
     }
     print(json.dumps(line))
@@ -419,10 +534,11 @@ def run_ours(args):
 def main():
     args = parse_args()
     import __graft_entry__ as g
-    g.build()
     if args.impl == "reference":
+        g.build(load_library=False)  # the reference arm never maps libcsim_b200.so
         run_reference(args)
     else:
+        g.build()
         run_ours(args)
 
 

@@ -36,6 +36,7 @@ EXPORTS = [
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
     "csim_plan_specialize_variants", "csim_plan_generate_source_variants", "csim_dev_selftest_tdiv",
     "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
+    "csim_dev_fp64_peak",
 ]
 
 
@@ -538,6 +539,14 @@ class Batch:
     @property
     def last_kernel_ms(self) -> float:
         return float(lib().csim_batch_last_kernel_ms(self.handle))
+
+
+def fp64_peak(device: int = 0) -> float:
+    """csim_dev_fp64_peak: sustained separate DMUL+DADD Tflop/s of the chip (the fused kernels' roofline peak)."""
+    v = C.c_double()
+    lib().csim_dev_fp64_peak.argtypes = [C.c_int, C.POINTER(C.c_double)]
+    _check(lib().csim_dev_fp64_peak(int(device), C.byref(v)), "csim_dev_fp64_peak")
+    return float(v.value)
 
 
 def selftest_tdiv(a, b):

@@ -1421,4 +1421,16 @@ int csim_dev_selftest_tdiv(int64_t n, const double* a, const double* b, double* 
 
 float csim_batch_last_kernel_ms(const csim_batch* b) { return b ? b->last_ms : 0.f; }
 
+int csim_dev_fp64_peak(int device, double* tflops_mul_add) {
+    if (!tflops_mul_add) return fail(CSIM_E_INVALID, "csim_dev_fp64_peak: null argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+        return fail(CSIM_E_CUDA, "csim_dev_fp64_peak: no such CUDA device");
+    CU(cudaSetDevice(device));
+    int sms = 0;
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    CU(measure_fp64_peak(sms, tflops_mul_add, nullptr));
+    return CSIM_OK;
+}
+
 }  // extern "C"

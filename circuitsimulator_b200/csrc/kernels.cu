@@ -600,6 +600,52 @@ cudaError_t launch_div_selftest(int64_t n, const double* a, const double* b, dou
 }
 
 // =============================================================================
+// FP64 pipe probe: the roofline denominator of the fused kernels, measured in the run.  Register-resident, eight
+// independent chains per thread of SEPARATE multiply and add (FMA is not allowed on the reference's expressions,
+// so the FMA peak does not apply).  Returns Tflop/s over the whole chip.
+// =============================================================================
+__global__ void __launch_bounds__(256) fp64_peak_kernel(double* __restrict__ out, double a, double b, int iters) {
+    double v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = a + k + threadIdx.x * 1e-6;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = __dadd_rn(__dmul_rn(v[k], b), a);
+    }
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += v[k];
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+cudaError_t measure_fp64_peak(int sm_count, double* tflops, cudaStream_t stream) {
+    const int blocks = sm_count * 8, iters = 20000;
+    double* out = nullptr;
+    cudaError_t e = cudaMalloc((void**)&out, sizeof(double) * (size_t)blocks * 256);
+    if (e != cudaSuccess) return e;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    double best = 0.0;
+    for (int rep = 0; rep < 4; ++rep) {  // first pass warms the clocks up
+        cudaEventRecord(e0, stream);
+        fp64_peak_kernel<<<blocks, 256, 0, stream>>>(out, 1.0, 0.9999999, iters);
+        cudaEventRecord(e1, stream);
+        e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double flop = 2.0 * (double)blocks * 256 * 8 * iters;
+        if (rep > 0 && ms > 0.f) best = flop / ms / 1e9 > best ? flop / ms / 1e9 : best;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    *tflops = best;
+    return e == cudaSuccess ? cudaGetLastError() : e;
+}
+
+// =============================================================================
 // launch wrappers
 // =============================================================================
 static size_t newton_smem_bytes(const DevMode& m) {

@@ -61,4 +61,7 @@ cudaError_t launch_tdiv_selftest(int64_t n, const double* a, const double* b, do
 cudaError_t launch_div_selftest(int64_t n, const double* a, const double* b, double* q_split, double* q_ref,
                                 cudaStream_t stream);
 
+// FP64 pipe probe (separate DMUL + DADD, register-resident): Tflop/s of the whole chip, best of three timed launches
+cudaError_t measure_fp64_peak(int sm_count, double* tflops, cudaStream_t stream);
+
 }  // namespace csim

@@ -403,6 +403,13 @@ int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, d
 float csim_batch_last_kernel_ms(const csim_batch* batch);
 #endif
 
+/* FP64 pipe probe: sustained Tflop/s of SEPARATE multiplies and adds over the whole chip (register-resident, eight
+ * independent chains per thread; FMA is not allowed on the reference's expressions, so its peak does not apply).
+ * The denominator of the fused kernels' roofline fraction, measured in the run that reports it.   */
+#ifndef __CUDACC_RTC__
+int csim_dev_fp64_peak(int device, double* tflops_mul_add);
+#endif
+
 /* ---- pivot-sequence hash (shared definition, host-callable) ------------- *
  * Every factorisation contributes f = sum_i mix(i, perm[i]) (mod 2^64) and the
  * running hash becomes h' = (h XOR f) * 0x100000001B3.  h starts at

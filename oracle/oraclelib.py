@@ -483,6 +483,22 @@ def ref_hardware_threads() -> int:
     return int(ref_lib().ref_hardware_threads())
 
 
+def monte_carlo(topo: Topology, n: int, seed: int, rel: float = 0.05):
+    """SURVEY.md §8(d) recipe, [n, P]: instance 0 nominal; instance i > 0 nominal*(1+rel*u_i), u~U(-1,1) drawn
+    row-wise from PCG64(seed); R, C, L and MOS Vth/K/lambda/Cj0 only (sources nominal)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    P = topo.params.size
+    mask = np.zeros(P, bool)
+    for e in range(topo.n_elems):
+        ty = int(topo.elem_type[e])
+        if ty in (ELEM_R, ELEM_C, ELEM_L, ELEM_MOS):
+            mask[topo.elem_param[e]: topo.elem_param[e] + PARAM_COUNT[ty]] = True
+    u = rng.uniform(-1.0, 1.0, size=(n, P))
+    out = np.repeat(topo.params[None, :], n, 0)
+    out[1:, mask] = topo.params[mask] * (1.0 + rel * u[1:, mask])
+    return out
+
+
 # ------------------------------------------------------------ netlist writer
 
 def netlist_from_params(topo: Topology, params, tran=None, title="generated instance") -> str:

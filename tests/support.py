@@ -36,17 +36,8 @@ def load_golden(name):
 def perturb(nominal, topo, n, seed, rel=0.05):
     """instance 0 nominal; others nominal*(1+rel*u), u~U(-1,1), PCG64(seed); R, C, L and MOS
     Vth/K/lambda/Cj0 only (sources nominal).  Returns [n, P]."""
-    rng = np.random.Generator(np.random.PCG64(seed))
-    P = nominal.size
-    mask = np.zeros(P, bool)
-    for e in range(topo.n_elems):
-        ty = int(topo.elem_type[e])
-        if ty in (O.ELEM_R, O.ELEM_C, O.ELEM_L, O.ELEM_MOS):
-            mask[topo.elem_param[e]: topo.elem_param[e] + O.PARAM_COUNT[ty]] = True
-    u = rng.uniform(-1.0, 1.0, size=(n, P))
-    out = np.repeat(nominal[None, :], n, 0)
-    out[1:, mask] = nominal[mask] * (1.0 + rel * u[1:, mask])
-    return out
+    assert nominal is topo.params or np.array_equal(nominal, topo.params)
+    return O.monte_carlo(topo, n, seed, rel)
 
 
 def make_plan(topo, device=0):
