@@ -2,6 +2,7 @@
 // with the product's own parser, lower it, tabulate sources.  Declared in include/csim_host.h.
 #include <cmath>
 #include <cstring>
+#include <memory>
 #include <sstream>
 #include <string>
 
@@ -36,7 +37,7 @@ const char* csimh_last_error(void) { return g_herr.c_str(); }
 csimh_netlist* csimh_parse(const char* text) {
     if (!text) return nullptr;
     try {
-        auto* h = new csimh_netlist();
+        std::unique_ptr<csimh_netlist> h(new csimh_netlist());
         std::istringstream in(text);
         NetlistParser parser(h->ckt, h->sim);
         parser.parseStream(in, "<memory>");
@@ -44,7 +45,7 @@ csimh_netlist* csimh_parse(const char* text) {
         h->ckt.assignEquationIndices();
         h->low = csim::lower(h->ckt);
         h->header = h->low.csv_header();
-        return h;
+        return h.release();
     } catch (const std::exception& e) {
         g_herr = e.what();
         return nullptr;
@@ -52,6 +53,35 @@ csimh_netlist* csimh_parse(const char* text) {
 }
 
 void csimh_free(csimh_netlist* h) { delete h; }
+
+// PULSE (type 1: spec = v1 v2 td tr tf ton per) or PWL (type 3: spec = n times then n values) waveform on the
+// idx-th independent source (V and I in netlist order) — TranWaveform's other two kinds, which the reference
+// implements (include/sim.hpp:80-138) but its parser never produces (src/parser.cpp:346-351).  Re-lowers.
+int csimh_set_source_waveform(csimh_netlist* h, int32_t idx, int32_t type, const double* spec, int32_t n) {
+    if (!h || !spec || (type != 1 && type != 3) || (type == 3 && n <= 0)) return -1;
+    int s = 0;
+    for (const auto& e : h->ckt.elements) {
+        auto* v = dynamic_cast<VoltageSource*>(e.get());
+        auto* c = dynamic_cast<CurrentSource*>(e.get());
+        if (!v && !c) continue;
+        if (s++ != idx) continue;
+        SourceSpec sp = v ? v->getSpec() : c->getSpec();
+        if (type == 1) {
+            sp.tran.type = WaveformType::PULSE;
+            sp.tran.pulse = PulseSpec{spec[0], spec[1], spec[2], spec[3], spec[4], spec[5], spec[6]};
+        } else {
+            sp.tran.type = WaveformType::PWL;
+            sp.tran.pwl.t.assign(spec, spec + n);
+            sp.tran.pwl.v.assign(spec + n, spec + 2 * n);
+        }
+        if (v) v->replaceSpec(sp);
+        else c->replaceSpec(sp);
+        h->low = csim::lower(h->ckt);
+        return 0;
+    }
+    g_herr = "csimh_set_source_waveform: no such source";
+    return -1;
+}
 
 int csimh_dims(const csimh_netlist* h, int32_t* n_unknowns, int32_t* n_node_eq, int32_t* n_elems, int32_t* n_params,
                int32_t* n_sources) {

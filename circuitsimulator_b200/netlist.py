@@ -25,6 +25,8 @@ def _hlib():
         L.csimh_sin_table.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, C.c_void_p]
         L.csimh_write_instance_csv.argtypes = [C.c_void_p, C.c_char_p, C.c_int64, C.c_int64, C.c_int32, C.c_void_p,
                                                C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.csimh_set_source_waveform.restype = C.c_int
+        L.csimh_set_source_waveform.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_int32]
         L.csimh_n_dc_sweeps.argtypes = [C.c_void_p]
         L.csimh_run_dc_sweep.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                          C.c_void_p, C.c_void_p]
@@ -104,6 +106,21 @@ class Netlist:
     def plan(self, device: int = 0, consts=None) -> capi.Plan:
         return capi.Plan(self.n_unknowns, self.n_node_eq, self.elem_type, self.elem_flags, self.elem_nodes,
                          self.elem_branch, self.elem_param, self.n_params, device=device, consts=consts)
+
+    def set_source_waveform(self, source, kind: str, spec):
+        """PULSE (spec = v1 v2 td tr tf ton per) or PWL (spec = (times, values)) waveform on an independent source
+        (name or index among the V/I sources in netlist order) — include/sim.hpp:80-138."""
+        src = self.source_elems()
+        idx = source if isinstance(source, int) else [self.elem_names[e].lower() for e in src].index(source.lower())
+        if kind.lower() == "pwl":
+            t, v = np.asarray(spec[0], np.float64), np.asarray(spec[1], np.float64)
+            flat, n, ty = np.ascontiguousarray(np.concatenate([t, v])), t.size, 3
+        else:
+            flat, n, ty = np.ascontiguousarray(spec, np.float64), 0, 1
+            assert flat.size == 7
+        rc = _hlib().csimh_set_source_waveform(C.c_void_p(self._h), int(idx), ty, flat.ctypes.data_as(C.c_void_p), int(n))
+        if rc:
+            raise capi.CsimError("csimh_set_source_waveform failed")
 
     def source_tables(self, dt: float | None = None, n_steps: int | None = None):
         """(src_mode, src_group, table[n_groups, n_steps]) tabulated with the host libm."""

@@ -59,6 +59,7 @@ public:
     CurrentSource(const std::string& n, int np, int nm, const SourceSpec& s) : Element(n, {np, nm}), spec(s) {}
     const SourceSpec& setSpec() const { return spec; }  // (sic) the reference's name for this getter
     const SourceSpec& getSpec() const { return spec; }
+    void replaceSpec(const SourceSpec& s) { spec = s; }  // superset: PULSE / PWL sources (the parser only makes SIN)
     int abiType() const override;
     int abiFlags() const override;
     void abiParams(std::vector<double>& out) const override;
@@ -74,6 +75,7 @@ public:
     void setBranchEqIndex(int idx) { branchEqIndex = idx; }
     int getBranchEqIndex() const { return branchEqIndex; }
     const SourceSpec& getSpec() const { return spec; }
+    void replaceSpec(const SourceSpec& s) { spec = s; }  // superset: PULSE / PWL sources (the parser only makes SIN)
     int abiType() const override;
     int abiFlags() const override;
     int abiBranch() const override { return branchEqIndex; }

@@ -14,6 +14,10 @@ const char* csimh_last_error(void);
 /* parseStream + ensureDefaultOp + assignEquationIndices + lower (src/main.cpp:29-34). NULL on error. */
 csimh_netlist* csimh_parse(const char* netlist_text);
 void csimh_free(csimh_netlist* h);
+/* PULSE (type 1: spec = v1 v2 td tr tf ton per) or PWL (type 3: spec = n times then n values) waveform on the idx-th
+ * independent source (V and I in netlist order): the two TranWaveform kinds of include/sim.hpp:80-138 that the
+ * reference's parser never produces.  csimh_tabulate_sources then emits a CSIM_SRC_VAL_TABLE row for it. */
+int csimh_set_source_waveform(csimh_netlist* h, int32_t idx, int32_t type, const double* spec, int32_t n);
 int csimh_dims(const csimh_netlist* h, int32_t* n_unknowns, int32_t* n_node_eq, int32_t* n_elems,
                int32_t* n_params, int32_t* n_sources);
 /* arrays sized per csimh_dims; nodes is [n_elems][4]; nominal is [n_params] */

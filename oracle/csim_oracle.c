@@ -66,6 +66,66 @@ void oracle_sin_table(double freq, double td, double phi, double dt, int32_t n_s
     }
 }
 
+/* clamp01, include/sim.hpp (helper of the PULSE branch) */
+static double clamp01(double k) { return k < 0.0 ? 0.0 : (k > 1.0 ? 1.0 : k); }
+
+/* TranWaveform::eval PULSE branch, include/sim.hpp:80-115.  spec = v1 v2 td tr tf ton per */
+static double pulse_eval(const double* p, double t) {
+    const double v1 = p[0], v2 = p[1], td = p[2], tr = p[3], tf = p[4], ton = p[5], per = p[6];
+    if (per <= 0.0) { /* single shot, sim.hpp:81-96 */
+        double tau = t - td;
+        if (tau <= 0.0) return v1;
+        if (tau < tr) {
+            double k = clamp01(tau / tr);
+            return v1 + k * (v2 - v1);
+        } else if (tau < tr + ton) {
+            return v2;
+        } else {
+            double tfall = tau - (tr + ton);
+            double k = clamp01(tfall / tf);
+            return v2 + k * (v1 - v2);
+        }
+    }
+    /* periodic, sim.hpp:97-114 */
+    if (t < td) return v1;
+    double tau = fmod(t - td, per);
+    if (tau < 0.0) tau += per;
+    if (tau < tr) {
+        double k = clamp01(tau / tr);
+        return v1 + (v2 - v1) * k;
+    } else if (tau < tr + ton) {
+        return v2;
+    } else if (tau < tr + ton + tf) {
+        double tfall = tau - (tr + ton);
+        double k = clamp01(tfall / tf);
+        return v2 + (v1 - v2) * k;
+    }
+    return v1;
+}
+
+/* TranWaveform::eval PWL branch, include/sim.hpp:124-138.  spec = t[0..n) then v[0..n) */
+static double pwl_eval(const double* tt, const double* vv, int32_t n, double t) {
+    if (n <= 0) return 0.0;
+    if (t <= tt[0]) return vv[0];
+    if (t >= tt[n - 1]) return vv[n - 1];
+    for (int32_t i = 0; i + 1 < n; ++i) {
+        if (t > tt[i] && t <= tt[i + 1]) {
+            double k = (t - tt[i]) / (tt[i + 1] - tt[i]);
+            return vv[i] + (vv[i + 1] - vv[i]) * k;
+        }
+    }
+    return vv[n - 1];
+}
+
+/* CSIM_SRC_VAL_TABLE row: out[s] = TranWaveform::eval((s+1)*dt).  type 1 = PULSE (spec: 7 doubles, n ignored),
+ * type 3 = PWL (spec: n times then n values) — the reference's WaveformType numbering (sim.hpp:25-30). */
+void oracle_waveform_table(int32_t type, const double* spec, int32_t n, double dt, int32_t n_steps, double* out) {
+    for (int32_t s = 0; s < n_steps; ++s) {
+        double t = (s + 1) * dt; /* src/tanalisis.cpp:256 */
+        out[s] = type == 1 ? pulse_eval(spec, t) : (type == 3 ? pwl_eval(spec, spec + n, n, t) : 0.0);
+    }
+}
+
 /* SourceSpec::evalTran, include/sim.hpp:160-162 (+ eval 75-143 through the table) */
 void oracle_src_tran(const csim_topology* t, const double* params, const int32_t* src_mode,
                      const int32_t* src_group, const double* table, int32_t table_steps, int32_t step,

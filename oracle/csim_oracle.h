@@ -50,6 +50,9 @@ void oracle_src_tran(const csim_topology* t, const double* params, const int32_t
                      double dt, double* src_val);
 /* S = sin(2*pi*freq*(t-td)+phi) at t=(s+1)*dt, s in [0,n_steps)  (include/sim.hpp:117-122). */
 void oracle_sin_table(double freq, double td, double phi, double dt, int32_t n_steps, double* out);
+/* CSIM_SRC_VAL_TABLE row: out[s] = TranWaveform::eval((s+1)*dt) for a PULSE (type 1, spec = v1 v2 td tr tf ton per)
+ * or PWL (type 3, spec = n times then n values) waveform  (include/sim.hpp:80-115,124-138). */
+void oracle_waveform_table(int32_t type, const double* spec, int32_t n, double dt, int32_t n_steps, double* out);
 
 /* Solver::solveLinearSystemLU (include/solver.hpp:30-131). A is row-major N*N
  * (not modified), returns 1 when the factorisation failed (x = 0 then). */

@@ -168,9 +168,28 @@ def pivot_hash_update(h: int, perm) -> int:
     return int(oracle_lib().oracle_pivot_hash_update(C.c_uint64(h), _p(perm, C.c_int32), perm.size))
 
 
-def make_source_tables(topo: Topology, params, dt: float, n_steps: int):
+WAVE_PULSE, WAVE_PWL = 1, 3  # the reference's WaveformType numbering (include/sim.hpp:25-30)
+
+
+def waveform_table(kind: int, spec, dt: float, n_steps: int):
+    """One CSIM_SRC_VAL_TABLE row: TranWaveform::eval((s+1)*dt) of a PULSE (spec: v1 v2 td tr tf ton per) or PWL
+    (spec: (times, values)) waveform, by the oracle's restatement of include/sim.hpp:80-138."""
+    L = oracle_lib()
+    if kind == WAVE_PWL:
+        t, v = np.asarray(spec[0], np.float64), np.asarray(spec[1], np.float64)
+        flat, n = np.ascontiguousarray(np.concatenate([t, v])), t.size
+    else:
+        flat, n = np.ascontiguousarray(spec, np.float64), 0
+    row = np.empty(n_steps, np.float64)
+    L.oracle_waveform_table(C.c_int32(kind), _p(flat, C.c_double), C.c_int32(n), C.c_double(dt), C.c_int32(n_steps),
+                            _p(row, C.c_double))
+    return row
+
+
+def make_source_tables(topo: Topology, params, dt: float, n_steps: int, waveforms=None):
     """Table convention of csim_src_mode for netlist-level sources: one SIN group per
-    SIN source, CONST otherwise.  Returns (src_mode, src_group, table[n_groups, n_steps])."""
+    SIN source, CONST otherwise; waveforms = {source index: (WAVE_PULSE | WAVE_PWL, spec)} adds a
+    CSIM_SRC_VAL_TABLE group for each.  Returns (src_mode, src_group, table[n_groups, n_steps])."""
     L = oracle_lib()
     params = np.asarray(params, dtype=np.float64)
     src = topo.source_elems()
@@ -178,6 +197,11 @@ def make_source_tables(topo: Topology, params, dt: float, n_steps: int):
     group = np.zeros(len(src), np.int32)
     rows = []
     for s, e in enumerate(src):
+        if waveforms and s in waveforms:
+            mode[s] = SRC_VAL_TABLE
+            group[s] = len(rows)
+            rows.append(waveform_table(waveforms[s][0], waveforms[s][1], dt, n_steps))
+            continue
         if topo.elem_flags[e] & FLAG_SRC_SIN:
             p = params[topo.elem_param[e]: topo.elem_param[e] + 6]
             row = np.empty(n_steps, np.float64)
@@ -432,6 +456,16 @@ class Ref:
 
     def source_tran(self, idx: int, t: float) -> float:
         return float(self.L.ref_source_tran(C.c_void_p(self.h), idx, t))
+
+    def set_source_waveform(self, idx: int, kind: int, spec):
+        """PULSE / PWL on the reference's own SourceSpec of source idx (its parser only produces SIN)."""
+        if kind == WAVE_PWL:
+            t, v = np.asarray(spec[0], np.float64), np.asarray(spec[1], np.float64)
+            flat, n = np.ascontiguousarray(np.concatenate([t, v])), t.size
+        else:
+            flat, n = np.ascontiguousarray(spec, np.float64), 0
+        rc = self.L.ref_set_source_waveform(C.c_void_p(self.h), C.c_int(idx), C.c_int(kind), _p(flat, C.c_double), C.c_int(n))
+        assert rc == 0, rc
 
 
 def ref_lu_solve(A, b):

@@ -378,6 +378,34 @@ double ref_source_tran(void* hv, int idx, double t) {
     return NAN;
 }
 
+// Gives the idx-th independent source (V and I in netlist order) a PULSE (type 1: spec = v1 v2 td tr tf ton per)
+// or PWL (type 3: spec = n times then n values) waveform.  The reference's parser only ever produces SIN
+// (src/parser.cpp:346-351), but TranWaveform::eval implements all three (include/sim.hpp:80-138): this sets the
+// reference's OWN SourceSpec object, so its drivers then run its own PULSE / PWL code.
+int ref_set_source_waveform(void* hv, int idx, int type, const double* spec, int n) {
+    auto* h = static_cast<Handle*>(hv);
+    int s = 0;
+    for (const auto& e : h->ckt.elements) {
+        SourceSpec* sp = nullptr;
+        if (auto v = std::dynamic_pointer_cast<VoltageSource>(e)) sp = const_cast<SourceSpec*>(&v->getSpec());
+        else if (auto c = std::dynamic_pointer_cast<CurrentSource>(e)) sp = const_cast<SourceSpec*>(&c->setSpec());
+        if (!sp) continue;
+        if (s++ != idx) continue;
+        if (type == 1) {
+            sp->tran.type = WaveformType::PULSE;
+            sp->tran.pulse = PulseSpec{spec[0], spec[1], spec[2], spec[3], spec[4], spec[5], spec[6]};
+        } else if (type == 3) {
+            sp->tran.type = WaveformType::PWL;
+            sp->tran.pwl.t.assign(spec, spec + n);
+            sp->tran.pwl.v.assign(spec + n, spec + 2 * n);
+        } else {
+            return -2;
+        }
+        return 0;
+    }
+    return -1;
+}
+
 // Timed CPU baseline.  netlists[i] = full netlist text of instance i.  n_threads
 // host threads (pinned round-robin onto the CPUs this process may use) pull
 // instance indices; each builds its own Circuit and runs the reference transient

@@ -142,9 +142,85 @@ def pin_netlist(name, text, expect_sha16=None, cap=600_000):
     return topo, cfg, o_dc, o_tr, dict(sha=sha, margin=margin, n_perm=len(uniq), n_steps=n_steps)
 
 
+SOURCES_NETLIST = """* current source + PULSE / PWL waveforms (fixture; reference grammar)
+Vdd vdd 0 DC 3
+I1 0 n1 DC 1e-3
+R1 n1 0 1k
+C1 n1 0 1e-12
+Vg g 0 DC 0.2
+M1 vdd g n2 n 10e-6 0.35e-6 1
+R2 n2 0 10k
+C2 n2 0 5e-13
+L1 n1 n3 1e-9
+R3 n3 0 2k
+.MODEL 1 VT 0.5 MU 3e-2 COX 6e-3 LAMBDA 0.05 CJ0 4e-14
+.TRAN 1e-11 2e-9
+.end
+"""
+# source index (V and I in netlist order: Vdd, I1, Vg) -> (kind, spec); PULSE: v1 v2 td tr tf ton per
+SOURCES_CASES = {
+    "const": {},                                                                   # I source, evalTran = dcValue
+    "pulse_periodic_pwl": {1: (O.WAVE_PULSE, [0.0, 2e-3, 1e-10, 5e-11, 1e-10, 3e-10, 8e-10]),
+                           2: (O.WAVE_PWL, ([0.0, 2e-10, 6e-10, 1.2e-9, 2e-9], [0.0, 1.0, 2.5, 0.3, 1.5]))},
+    "pulse_single": {1: (O.WAVE_PULSE, [1e-3, -1e-3, 3e-10, 2e-10, 4e-10, 5e-10, 0.0]),
+                     2: (O.WAVE_PULSE, [0.0, 2.0, 0.0, 1e-10, 1e-10, 2e-10, 5e-10])},
+}
+
+
+def pin_sources():
+    """a3 / a9: an I source in the transient and PULSE / PWL waveforms (include/sim.hpp:80-138,
+    src/element.cpp:34-66).  The reference's parser never produces them, its classes implement them: the
+    harness sets the reference's own SourceSpec objects and its unmodified drivers run."""
+    out = {"netlist": SOURCES_NETLIST}
+    for name, wf in SOURCES_CASES.items():
+        ref = O.Ref(SOURCES_NETLIST)
+        topo = ref.topology()
+        cfg = ref.tran_cfg()
+        dt = cfg["tstep"]
+        n_steps = int(np.floor(cfg["tstop"] / dt + 1e-12))
+        for idx, (kind, spec) in wf.items():
+            ref.set_source_waveform(idx, kind, spec)
+        mode, group, table = O.make_source_tables(topo, topo.params, dt, n_steps, waveforms=wf)
+        for s in range(len(mode)):  # the tabulated rows reproduce SourceSpec::evalTran at EVERY step, bit for bit
+            for st in range(n_steps):
+                v = O.src_tran(topo, topo.params, mode, group, table, st, dt)[s]
+                assert bits(np.array(v)) == bits(np.array(ref.source_tran(s, (st + 1) * dt))), (name, s, st)
+        with tempfile.TemporaryDirectory() as td:
+            csv = os.path.join(td, "ref.csv")
+            rc, tr = ref.tran(csv, trace_cap=50000)
+            assert rc == 0
+            ref_csv = open(csv).read()
+        o_dc = O.dc(topo, topo.params, trace_cap=2000)
+        o_tr = O.tran(topo, topo.params, dt, 0, n_steps, mode, group, table, o_dc["x"], trace_cap=50000,
+                      pivot_hash=o_dc["hash"])
+        nd = o_dc["trace"].n_iters
+        assert tr.n_iters == nd + o_tr["total"], (name, tr.n_iters, nd, o_tr["total"])
+        assert same_bits(tr.xraw[:nd], o_dc["trace"].xraw)
+        assert same_bits(tr.xraw[nd:], o_tr["trace"].xraw), f"{name}: raw LU solutions differ"
+        assert np.array_equal(tr.perm[nd:], o_tr["trace"].perm)
+        assert csv_from_wave(topo, o_dc["x"], o_tr["wave"], dt) == ref_csv, f"{name}: CSV differs"
+        print(f"   sources/{name}: PINNED ({tr.n_iters} Newton solves, CSV sha256 "
+              f"{hashlib.sha256(ref_csv.encode()).hexdigest()[:16]})")
+        out[name + "_x_dc"] = o_dc["x"]
+        out[name + "_wave"] = o_tr["wave"]
+        out[name + "_iters_step"] = o_tr["iters_step"]
+        out[name + "_hash"] = np.uint64(o_tr["hash"])
+        out[name + "_table"] = table
+        out[name + "_mode"] = mode
+        out[name + "_group"] = group
+    out.update(params=topo.params, elem_type=topo.elem_type, elem_flags=topo.elem_flags, elem_nodes=topo.elem_nodes,
+               elem_branch=topo.elem_branch, elem_param=topo.elem_param, n_node_eq=topo.n_node_eq, dt=dt,
+               tstop=cfg["tstop"])
+    np.savez_compressed(os.path.join(OUT, "sources.npz"), **out)
+
+
 def main():
     O.build(force=True)
     summary = {}
+    if "--sources-only" in sys.argv:
+        pin_sources()
+        return
+    pin_sources()
 
     # ---- buffer.sp (config 1): full raw waveform
     text = open(os.path.join(REF_TESTS, "buffer.sp")).read()

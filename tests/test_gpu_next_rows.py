@@ -153,3 +153,43 @@ def test_gauss_seidel_host_buffers(torch):
     ox, osw = O.gauss_seidel(A, b)
     assert sweeps[0] == osw
     assert_same_bits(x, ox, "host-buffer Gauss-Seidel")
+
+
+@pytest.mark.parametrize("jit", [3, 2, 0])
+@pytest.mark.parametrize("case", ["const", "pulse_periodic_pwl", "pulse_single"])
+def test_current_source_and_pulse_pwl_waveforms_in_transient(torch, case, jit):
+    """Rows a3 / a9: an I source in the transient (src/element.cpp:34-66) and PULSE / PWL sources through
+    CSIM_SRC_VAL_TABLE (include/sim.hpp:80-138) — against tests/golden/sources.npz, generated from the unmodified
+    reference's own SourceSpec code (make_golden.py: pin_sources), for every kernel family and a Monte-Carlo batch
+    against the oracle."""
+    from circuitsimulator_b200 import capi
+    from circuitsimulator_b200.netlist import Netlist
+    from test_sources_cpu import CASES, load_sources
+    g, topo, dt, ns = load_sources()
+    nl = Netlist(str(g["netlist"]))
+    for idx, (kind, spec) in CASES[case].items():
+        nl.set_source_waveform(idx, "pwl" if kind == O.WAVE_PWL else "pulse", spec)
+    plan = nl.plan()
+    plan.jit_mode(jit)
+    setup = nl.tran_setup(probes=np.arange(nl.n_unknowns, dtype=np.int32))
+    assert setup.n_steps == ns
+    B = 9
+    P = O.monte_carlo(topo, B, 4242)
+    params = torch.from_numpy(np.ascontiguousarray(P.T)).cuda()
+    d = capi.dc(plan, params)
+    x_dc = d["x"].clone()
+    t = capi.tran(plan, params, d["x"], setup, pivot_hash=d["hash"], status=d["status"], want_iters_step=True)
+    torch.cuda.synchronize()
+    assert plan.spec_info()["kind"] == jit
+    wave = t["wave"].cpu().numpy()
+    assert_same_bits(x_dc[:, 0].cpu().numpy(), g[case + "_x_dc"], "DC vs reference-pinned fixture")
+    assert_same_bits(wave[0].T, g[case + "_wave"], "waveform vs reference-pinned fixture")
+    assert np.array_equal(t["iters_step"][:, 0].cpu().numpy(), g[case + "_iters_step"])
+    assert np.uint64(t["hash"][0].item() & 0xFFFFFFFFFFFFFFFF) == g[case + "_hash"]
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns, waveforms=CASES[case])
+    for b in range(1, B):
+        od = O.dc(topo, P[b])
+        ot = O.tran(topo, P[b], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(wave[b].T, ot["wave"], f"instance {b}")
+        assert np.array_equal(t["iters_step"][:, b].cpu().numpy(), ot["iters_step"])
+        assert np.uint64(t["hash"][b].item() & 0xFFFFFFFFFFFFFFFF) == np.uint64(ot["hash"])
