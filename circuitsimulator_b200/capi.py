@@ -36,7 +36,7 @@ EXPORTS = [
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
     "csim_plan_specialize_variants", "csim_plan_generate_source_variants", "csim_dev_selftest_tdiv",
     "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
-    "csim_dev_fp64_peak",
+    "csim_dev_fp64_peak", "csim_dev_lu_factor", "csim_host_lu_factor",
 ]
 
 
@@ -317,6 +317,20 @@ def lu_solve(A, b, lu_eps=1e-15):
     _check(lib().csim_dev_lu_solve(n, B, _ptr(A), _ptr(b), _ptr(x), _ptr(perm), _ptr(sing), float(lu_eps), _stream()),
            "csim_dev_lu_solve")
     return x, perm, sing
+
+
+def lu_factor(A, n, lu_eps=1e-15):
+    """csim_dev_lu_factor: A [N*N,B] -> (LU [N*N,B] packed L\\U as Solver::luDecompose leaves it, perm [N,B], singular [B])."""
+    torch = _torch()
+    B = A.shape[1]
+    _dev_f64(A, (n * n, B))
+    LU = torch.empty_like(A)
+    perm = torch.empty((n, B), dtype=torch.int32, device=A.device)
+    sing = torch.empty((B,), dtype=torch.int32, device=A.device)
+    lib().csim_dev_lu_factor.argtypes = [C.c_int32, C.c_int64] + [C.c_void_p] * 4 + [C.c_double, C.c_void_p]
+    _check(lib().csim_dev_lu_factor(n, B, _ptr(A), _ptr(LU), _ptr(perm), _ptr(sing), float(lu_eps), _stream()),
+           "csim_dev_lu_factor")
+    return LU, perm, sing
 
 
 def new_diag(B, device):

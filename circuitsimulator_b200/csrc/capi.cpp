@@ -717,6 +717,20 @@ int csim_dev_lu_solve(int32_t n, int64_t B, const double* A, const double* b, do
     return CSIM_OK;
 }
 
+int csim_dev_lu_factor(int32_t n, int64_t B, const double* A, double* LU, int32_t* perm, int32_t* singular,
+                       double lu_eps, void* stream) {
+    if (n <= 0 || n > kDenseMaxN) return fail(CSIM_E_UNSUPPORTED, "csim_dev_lu_factor: n out of range");
+    if (B <= 0 || !A || !LU) return fail(CSIM_E_INVALID, "csim_dev_lu_factor: bad argument");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) return fail(CSIM_E_CUDA, "csim_dev_lu_factor: no CUDA device (no CPU fallback)");
+    if (n > 32 || env_big())
+        CU(launch_lu_dense(n, B, A, nullptr, nullptr, perm, singular, lu_eps, (cudaStream_t)stream, LU));
+    else
+        CU(launch_lu_solve(n, B, A, nullptr, nullptr, perm, singular, lu_eps, (cudaStream_t)stream, LU));
+    return CSIM_OK;
+}
+
 int csim_dev_dc(const csim_plan* plan, int64_t B, const double* params, double* x, int32_t* iters,
                 uint64_t* pivot_hash, uint32_t* status, void* stream) {
     int rc = need_device(plan, "csim_dev_dc");
@@ -1181,6 +1195,26 @@ int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, d
                                ds.as<int32_t>(), lu_eps, nullptr);
     if (rc) return rc;
     CU(cudaMemcpy(x, dx.p, sizeof(double) * (size_t)n * B, cudaMemcpyDeviceToHost));
+    if (perm) CU(cudaMemcpy(perm, dp.p, sizeof(int32_t) * (size_t)n * B, cudaMemcpyDeviceToHost));
+    if (singular) CU(cudaMemcpy(singular, ds.p, sizeof(int32_t) * (size_t)B, cudaMemcpyDeviceToHost));
+    return CSIM_OK;
+}
+
+int csim_host_lu_factor(int32_t n, int64_t B, const double* A, double* LU, int32_t* perm, int32_t* singular,
+                        double lu_eps) {
+    if (n <= 0 || n > kDenseMaxN) return fail(CSIM_E_UNSUPPORTED, "csim_host_lu_factor: n out of range");
+    if (B <= 0 || !A || !LU) return fail(CSIM_E_INVALID, "csim_host_lu_factor: bad argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(CSIM_E_CUDA, "csim_host_lu_factor: no CUDA device (no CPU fallback)");
+    DevBuf dA, dLU, dp, ds;
+    CU(dA.put(A, sizeof(double) * (size_t)n * n * B));
+    CU(dLU.put(nullptr, sizeof(double) * (size_t)n * n * B));
+    CU(dp.put(nullptr, sizeof(int32_t) * (size_t)n * B));
+    CU(ds.put(nullptr, sizeof(int32_t) * (size_t)B));
+    int rc = csim_dev_lu_factor(n, B, dA.as<double>(), dLU.as<double>(), dp.as<int32_t>(), ds.as<int32_t>(), lu_eps, nullptr);
+    if (rc) return rc;
+    CU(cudaMemcpy(LU, dLU.p, sizeof(double) * (size_t)n * n * B, cudaMemcpyDeviceToHost));
     if (perm) CU(cudaMemcpy(perm, dp.p, sizeof(int32_t) * (size_t)n * B, cudaMemcpyDeviceToHost));
     if (singular) CU(cudaMemcpy(singular, ds.p, sizeof(int32_t) * (size_t)B, cudaMemcpyDeviceToHost));
     return CSIM_OK;

@@ -100,7 +100,10 @@ __device__ __forceinline__ void dn_assemble(const DevMode& m, const double* vt, 
 
 // Factor [A | b] in place and solve.  Out: S.xr (zero vector when singular), S.rowat = pivot permutation,
 // h updated.  Returns true when singular (uniform over the CTA).
-__device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem& S, double eps, int tid, uint64_t& h) {
+// keepL: also write the multipliers back into the strict lower triangle of A (Solver::luDecompose's packed L\U,
+// solver.hpp:70-72); the Newton kernels never read L again and skip the traffic.
+__device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem& S, double eps, int tid, uint64_t& h,
+                            bool keepL = false) {
     const int lane = tid & 31, warp = tid >> 5;
 #ifdef CSIM_DN_PROF
     long long prof_acc[6] = {0, 0, 0, 0, 0, 0}, prof_t = clock64();
@@ -191,6 +194,11 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
             const int t = e / kDnNB, c = e - t * kDnNB;
             if (c >= t && c < nb) A[(size_t)S.rowat[k0 + t] * LD + k0 + c] = S.Pn[t * kDnLDP + c];
         }
+        if (keepL)  // multipliers of this panel: every row below the diagonal, through rowat (later exchanges move them along)
+            for (int e = tid; e < mrows * kDnNB; e += kDnThreads) {
+                const int r = e / kDnNB, c = e - r * kDnNB;
+                if (c < nb && c < r) A[(size_t)S.rowat[k0 + r] * LD + k0 + c] = S.Pn[r * kDnLDP + c];
+            }
         // ---- columns right of the panel (the right-hand side, column N, included), kDnCW at a time
         for (int j0 = k0 + nb; j0 <= N; j0 += kDnCW) {
             // strip of U: rows k0..k0+nb-1 of these columns, triangular solve against the panel's L (ascending k)
@@ -523,7 +531,7 @@ dc_dense_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double*
 __global__ void __launch_bounds__(kDnThreads, 2)
 lu_dense_kernel(int N, int64_t B, const double* __restrict__ Ain, const double* __restrict__ bin,
                 double* __restrict__ xout, int32_t* __restrict__ perm_out, int32_t* __restrict__ singular, double eps,
-                DnMem M) {
+                DnMem M, double* __restrict__ lu_out) {
     extern __shared__ unsigned char dn_smem[];
     const int tid = threadIdx.x, LD = dn_ld(N);
     const DnSmem S = dn_carve(dn_smem, N);
@@ -532,16 +540,21 @@ lu_dense_kernel(int N, int64_t B, const double* __restrict__ Ain, const double* 
         __syncthreads();
         for (int e = tid; e < N * (N + 1); e += kDnThreads) {
             const int i = e / (N + 1), j = e - i * (N + 1);
-            A[(size_t)i * LD + j] = j < N ? Ain[((int64_t)i * N + j) * B + b] : bin[(int64_t)i * B + b];
+            A[(size_t)i * LD + j] = j < N ? Ain[((int64_t)i * N + j) * B + b] : (bin ? bin[(int64_t)i * B + b] : 0.0);
         }
         __syncthreads();
         uint64_t h = 0;
-        const bool sing = dn_lu_solve(A, N, LD, S, eps, tid, h);
+        const bool sing = dn_lu_solve(A, N, LD, S, eps, tid, h, lu_out != nullptr);
         __syncthreads();
         for (int i = tid; i < N; i += kDnThreads) {
-            xout[(int64_t)i * B + b] = S.xr[i];
+            if (xout) xout[(int64_t)i * B + b] = S.xr[i];
             if (perm_out) perm_out[(int64_t)i * B + b] = S.rowat[i];
         }
+        if (lu_out)  // packed L\U in position order (the reference exchanges rows physically, solver.hpp:64-67)
+            for (int e = tid; e < N * N; e += kDnThreads) {
+                const int i = e / N, j = e - i * N;
+                lu_out[(int64_t)e * B + b] = A[(size_t)S.rowat[i] * LD + j];
+            }
         if (tid == 0 && singular) singular[b] = sing ? 1 : 0;
     }
 }
@@ -607,7 +620,7 @@ cudaError_t launch_dc_dense(const DevPlan& P, int64_t B, const double* params, d
 }
 
 cudaError_t launch_lu_dense(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
-                            int32_t* singular, double eps, cudaStream_t stream) {
+                            int32_t* singular, double eps, cudaStream_t stream, double* lu_out) {
     size_t smem;
     int grid;
     cudaError_t e = dn_grid(lu_dense_kernel, N, B, smem, grid);
@@ -615,7 +628,7 @@ cudaError_t launch_lu_dense(int N, int64_t B, const double* A, const double* b, 
     DnMem M;
     e = dn_alloc(N, 0, grid, stream, M);
     if (e == cudaSuccess) {
-        lu_dense_kernel<<<grid, kDnThreads, smem, stream>>>(N, B, A, b, x, perm, singular, eps, M);
+        lu_dense_kernel<<<grid, kDnThreads, smem, stream>>>(N, B, A, b, x, perm, singular, eps, M, lu_out);
         e = cudaGetLastError();
     }
     dn_free(M, stream);

@@ -114,7 +114,7 @@ stamp_csr_kernel(DevPlan P, int64_t B, const double* __restrict__ params, const 
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 lu_solve_kernel(int N, int64_t B, const double* __restrict__ A, const double* __restrict__ bvec,
                 double* __restrict__ xout, int32_t* __restrict__ perm_out, int32_t* __restrict__ singular,
-                double eps) {
+                double eps, double* __restrict__ lu_out) {
     extern __shared__ double smem[];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     double* S = smem + (size_t)wib * (32 * kLD + 32);
@@ -125,12 +125,19 @@ lu_solve_kernel(int N, int64_t B, const double* __restrict__ A, const double* __
         int i = idx / N, j = idx - i * N;
         S[i * kLD + j] = A[(int64_t)idx * B + b];
     }
-    bs[lane] = lane < N ? bvec[(int64_t)lane * B + b] : 0.0;
+    bs[lane] = (lane < N && bvec) ? bvec[(int64_t)lane * B + b] : 0.0;
     __syncwarp();
     int perm;
     bool sing = lu_solve_warp(S, bs, N, lane, eps, perm);
+    if (lu_out) {  // Solver::luDecompose: S holds the packed L\U, rows exchanged physically as the reference does
+        __syncwarp();
+        for (int idx = lane; idx < N * N; idx += 32) {
+            int i = idx / N, j = idx - i * N;
+            lu_out[(int64_t)idx * B + b] = S[i * kLD + j];
+        }
+    }
     if (lane < N) {
-        xout[(int64_t)lane * B + b] = bs[lane];
+        if (xout) xout[(int64_t)lane * B + b] = bs[lane];
         if (perm_out) perm_out[(int64_t)lane * B + b] = perm;
     }
     if (lane == 0 && singular) singular[b] = sing ? 1 : 0;
@@ -672,11 +679,11 @@ cudaError_t launch_stamp_csr(const DevPlan& P, int mode, int64_t B, const double
 }
 
 cudaError_t launch_lu_solve(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
-                            int32_t* singular, double eps, cudaStream_t stream) {
+                            int32_t* singular, double eps, cudaStream_t stream, double* lu_out) {
     size_t smem = (size_t)kWarpsPerBlock * (32 * kLD + 32) * sizeof(double);
     cudaFuncSetAttribute(lu_solve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int64_t blocks = (B + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    lu_solve_kernel<<<(unsigned)blocks, kWarpsPerBlock * 32, smem, stream>>>(N, B, A, b, x, perm, singular, eps);
+    lu_solve_kernel<<<(unsigned)blocks, kWarpsPerBlock * 32, smem, stream>>>(N, B, A, b, x, perm, singular, eps, lu_out);
     return cudaGetLastError();
 }
 

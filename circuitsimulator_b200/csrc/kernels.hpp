@@ -14,8 +14,9 @@ constexpr int kStampThreads = 128;  // standalone assembly: instances per CTA
 cudaError_t launch_stamp_csr(const DevPlan& P, int mode, int64_t B, const double* params, const double* x,
                              const double* x_prev, const double* src_val, double dt, double scale, double gmin,
                              double* vals, double* rhs, int sm_count, cudaStream_t stream);
+// lu_out (may be null): packed L\U of Solver::luDecompose, [N*N][B]
 cudaError_t launch_lu_solve(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
-                            int32_t* singular, double eps, cudaStream_t stream);
+                            int32_t* singular, double eps, cudaStream_t stream, double* lu_out = nullptr);
 cudaError_t launch_dc(const DevPlan& P, int64_t B, const double* params, double* x, int32_t* iters,
                       uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream);
 cudaError_t launch_tran(const DevPlan& P, const DevTran& T, int64_t B, const double* params, double* x, double* wave,
@@ -42,7 +43,7 @@ cudaError_t launch_tran_dense(const DevPlan& P, const DevTran& T, int64_t B, con
 cudaError_t launch_dc_dense(const DevPlan& P, int64_t B, const double* params, double* x, int32_t* iters,
                             uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream);
 cudaError_t launch_lu_dense(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
-                            int32_t* singular, double eps, cudaStream_t stream);
+                            int32_t* singular, double eps, cudaStream_t stream, double* lu_out = nullptr);
 
 cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double* x_prev, double tol, int period,
                                 uint8_t* skip, int32_t* periods, double* delta, unsigned long long* n_open,

@@ -10,6 +10,8 @@
 #include <algorithm>
 
 #include "csim/batchio.hpp"
+#include "csim/dcanalysis.hpp"
+#include "csim/solver.hpp"
 #include "csim/lower.hpp"
 #include "csim/sstateanalysis.hpp"
 #include "csim/parser.hpp"
@@ -179,6 +181,40 @@ int csimh_sin_table(double freq, double td, double phi, double dt, int32_t n_ste
         out[s] = std::sin(w * tau + phi);
     }
     return 0;
+}
+
+// dcSolveGaussSeidel of the host layer (src/dcanalysis.cpp:251-257) on the nominal circuit; x: [N].
+int csimh_dc_gauss_seidel(const csimh_netlist* h, double* x) {
+    if (!h || !x) return -1;
+    try {
+        const Eigen::VectorXd sol = dcSolveGaussSeidel(h->ckt);
+        for (int i = 0; i < h->low.n_unknowns; ++i) x[i] = sol(i);
+        return 0;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return -1;
+    }
+}
+
+// Solver::luDecompose of the host layer on one row-major n x n matrix: LU [n*n], perm [n]; returns 1 (true),
+// 0 (false: singular) or -1.
+int csimh_lu_decompose(int32_t n, const double* A, double* LU, int32_t* perm) {
+    if (n <= 0 || !A || !LU || !perm) return -1;
+    try {
+        Eigen::MatrixXd Am(n, n), F;
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < n; ++j) Am(i, j) = A[static_cast<std::size_t>(i) * n + j];
+        std::vector<int> p;
+        const bool ok = Solver::luDecompose(Am, F, p);
+        for (int i = 0; i < n && i < (int)p.size(); ++i) perm[i] = p[i];
+        if (F.rows() == n)
+            for (int i = 0; i < n; ++i)
+                for (int j = 0; j < n; ++j) LU[static_cast<std::size_t>(i) * n + j] = F(i, j);
+        return ok ? 1 : 0;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return -1;
+    }
 }
 
 // The reference's own driver signature, for drop-in checks from Python: DC + transient of the

@@ -284,11 +284,34 @@ class Netlist:
         out["transient_instances"] = int(n_inst.value)
         return out
 
+    def dc_gauss_seidel(self) -> np.ndarray:
+        """dcSolveGaussSeidel of the C++ host layer (the reference's Gauss-Seidel DC driver) on the nominal circuit."""
+        x = np.zeros(self.n_unknowns, np.float64)
+        L = _hlib()
+        L.csimh_dc_gauss_seidel.argtypes = [C.c_void_p, C.c_void_p]
+        if L.csimh_dc_gauss_seidel(C.c_void_p(self._h), x.ctypes.data_as(C.c_void_p)):
+            raise capi.CsimError("csimh_dc_gauss_seidel: " + L.csimh_last_error().decode(errors="replace"))
+        return x
+
     def run_reference_style_csv(self, path: str):
         """runTransientAnalysisBackwardEuler(ckt, sim, path) of the C++ host layer (B = 1 on the GPU)."""
         L = _hlib()
         if L.csimh_run_tran_csv(C.c_void_p(self._h), path.encode()) != 0:
             raise capi.CsimError(L.csimh_last_error().decode(errors="replace"))
+
+
+def lu_decompose(A):
+    """Solver::luDecompose of the C++ host layer: (LU packed as the reference leaves it, perm, ok)."""
+    A = np.ascontiguousarray(A, np.float64)
+    n = A.shape[0]
+    LU = np.zeros((n, n), np.float64)
+    perm = np.zeros(n, np.int32)
+    L = _hlib()
+    L.csimh_lu_decompose.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]
+    rc = L.csimh_lu_decompose(n, A.ctypes.data_as(C.c_void_p), LU.ctypes.data_as(C.c_void_p), perm.ctypes.data_as(C.c_void_p))
+    if rc < 0:
+        raise capi.CsimError("csimh_lu_decompose: " + L.csimh_last_error().decode(errors="replace"))
+    return LU, perm, bool(rc)
 
 
 def ladder_netlist(stages: int = 200, tstep: float = 1e-11, tstop: float = 2e-9) -> str:

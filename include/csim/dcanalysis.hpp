@@ -7,6 +7,8 @@ class Circuit;
 
 Eigen::VectorXd dcSolve(const Circuit& ckt);
 Eigen::VectorXd dcSolveLU(const Circuit& ckt);
-// Gauss-Seidel variant: not on the reference's default path; throws std::runtime_error
-// ("not implemented on the device") — SURVEY.md §8(f) rank 4.
+// Gauss-Seidel variant (src/dcanalysis.cpp:71-92,166-237,251-257; off the reference's default path): the direct
+// solve for linear circuits, the source ramp with 60 (120 on the last step) Newton iterations otherwise; assembly
+// and the Gauss-Seidel sweeps run on the device, the warnings and the (possibly unconverged) result are the
+// reference's.
 Eigen::VectorXd dcSolveGaussSeidel(const Circuit& ckt);

@@ -285,6 +285,18 @@ int csim_dev_lu_solve(int32_t n, int64_t B, const double* A, const double* b, do
                       int32_t* singular, double lu_eps, void* stream);
 #endif
 
+/* Batched Solver::luDecompose (include/solver.hpp:30-80): LU [N*N][B] = the packed factors exactly as the
+ * reference leaves them — U on and above the diagonal, the multipliers L(i,k) in the strict lower triangle
+ * (solver.hpp:70-72), rows exchanged physically, multipliers included (solver.hpp:64-67); perm [N][B];
+ * singular [B] = 1 where the reference returns false (LU then holds the reference's partial state for
+ * N <= 32 and is unspecified for larger N).  N <= 1280.                                              */
+#ifndef __CUDACC_RTC__
+int csim_dev_lu_factor(int32_t n, int64_t B, const double* A, double* LU, int32_t* perm, int32_t* singular,
+                       double lu_eps, void* stream);
+int csim_host_lu_factor(int32_t n, int64_t B, const double* A, double* LU, int32_t* perm, int32_t* singular,
+                        double lu_eps);
+#endif
+
 /* DC operating point for every instance (dcSolveLU, src/dcanalysis.cpp:242-248:
  * Newton ramp 95-163 when the netlist has MOSFETs, direct solve 46-68 otherwise).
  * x [N][B] out; iters [dc_ramp_steps][B] Newton iterations spent per ramp step

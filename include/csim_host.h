@@ -33,6 +33,10 @@ int csimh_tabulate_sources(const csimh_netlist* h, double dt, int32_t n_steps, i
                            double* table, int32_t* n_groups);
 int csimh_sin_table(double freq, double td, double phi, double dt, int32_t n_steps, double* out);
 int csimh_run_tran_csv(const csimh_netlist* h, const char* path);
+/* dcSolveGaussSeidel (src/dcanalysis.cpp:251-257) of the nominal circuit through the host layer; x [N]. */
+int csimh_dc_gauss_seidel(const csimh_netlist* h, double* x);
+/* Solver::luDecompose through the host layer: A, LU row-major [n*n], perm [n]; 1 = true, 0 = false, -1 = error. */
+int csimh_lu_decompose(int32_t n, const double* A, double* LU, int32_t* perm);
 /* runSteadyStateAnalysisBatch (include/csim/sstateanalysis.hpp); f0/tstep > 0 override .hb/.TRAN.
  * Returns steps per period, or -1. */
 int csimh_run_sstate(const csimh_netlist* h, int64_t B, const double* params, double f0, double tstep,

@@ -340,6 +340,41 @@ void oracle_stamp(const csim_topology* t, const csim_constants* c, int mode, con
 }
 
 /* Solver::luDecompose + solveLinearSystemLU, include/solver.hpp:30-131 */
+/* Solver::luDecompose, include/solver.hpp:30-80: LU = packed factors (multipliers in the strict lower triangle,
+ * rows exchanged physically), perm; returns 1 when the reference returns false (LU holds its partial state). */
+int oracle_lu_factor(int32_t n, const double* A, double* LU, int32_t* perm, double lu_eps) {
+    memcpy(LU, A, sizeof(double) * (size_t)n * (size_t)n);
+    for (int i = 0; i < n; ++i) perm[i] = i;
+    for (int k = 0; k < n; ++k) {
+        int pivot = k;
+        double maxAbs = fabs(LU[k * n + k]);
+        for (int i = k + 1; i < n; ++i) {
+            double val = fabs(LU[i * n + k]);
+            if (val > maxAbs) {
+                maxAbs = val;
+                pivot = i;
+            }
+        }
+        if (maxAbs < lu_eps) return 1;
+        if (pivot != k) {
+            for (int j = 0; j < n; ++j) {
+                double tmp = LU[k * n + j];
+                LU[k * n + j] = LU[pivot * n + j];
+                LU[pivot * n + j] = tmp;
+            }
+            int32_t tp = perm[k];
+            perm[k] = perm[pivot];
+            perm[pivot] = tp;
+        }
+        for (int i = k + 1; i < n; ++i) {
+            double factor = LU[i * n + k] / LU[k * n + k];
+            LU[i * n + k] = factor;
+            for (int j = k + 1; j < n; ++j) LU[i * n + j] -= factor * LU[k * n + j];
+        }
+    }
+    return 0;
+}
+
 int oracle_lu_solve(int32_t n, const double* A, const double* b, double* x, int32_t* perm_out, double lu_eps) {
     double* LU = (double*)malloc(sizeof(double) * (size_t)n * (size_t)n);
     double* y = (double*)malloc(sizeof(double) * (size_t)n);

@@ -54,6 +54,8 @@ void oracle_sin_table(double freq, double td, double phi, double dt, int32_t n_s
  * or PWL (type 3, spec = n times then n values) waveform  (include/sim.hpp:80-115,124-138). */
 void oracle_waveform_table(int32_t type, const double* spec, int32_t n, double dt, int32_t n_steps, double* out);
 
+/* Solver::luDecompose (include/solver.hpp:30-80): packed L\U + perm; returns 1 when the reference returns false. */
+int oracle_lu_factor(int32_t n, const double* A, double* LU, int32_t* perm, double lu_eps);
 /* Solver::solveLinearSystemLU (include/solver.hpp:30-131). A is row-major N*N
  * (not modified), returns 1 when the factorisation failed (x = 0 then). */
 int oracle_lu_solve(int32_t n, const double* A, const double* b, double* x, int32_t* perm, double lu_eps);

@@ -454,6 +454,13 @@ class Ref:
                          C.c_double(time), _p(G, C.c_double), _p(I, C.c_double))
         return G, I
 
+    def dc_gauss_seidel(self):
+        """The reference's dcSolveGaussSeidel (src/dcanalysis.cpp:251-257): (x, number of warning lines)."""
+        x = np.zeros(self.n_unknowns, np.float64)
+        nw = C.c_int64()
+        self.L.ref_dc_gauss_seidel(C.c_void_p(self.h), _p(x, C.c_double), C.byref(nw))
+        return x, int(nw.value)
+
     def source_tran(self, idx: int, t: float) -> float:
         return float(self.L.ref_source_tran(C.c_void_p(self.h), idx, t))
 
@@ -477,6 +484,29 @@ def ref_lu_solve(A, b):
     perm = np.zeros(n, np.int32)
     L.ref_lu_solve(C.c_int(n), _p(A, C.c_double), _p(b, C.c_double), _p(x, C.c_double), _p(perm, C.c_int32))
     return x, perm
+
+
+def lu_factor(A, lu_eps=1e-15):
+    """oracle_lu_factor (restatement of Solver::luDecompose): (LU packed, perm, failed)."""
+    L = oracle_lib()
+    A = np.ascontiguousarray(A, np.float64)
+    n = A.shape[0]
+    LU = np.zeros((n, n), np.float64)
+    perm = np.zeros(n, np.int32)
+    L.oracle_lu_factor.restype = C.c_int
+    failed = L.oracle_lu_factor(C.c_int32(n), _p(A, C.c_double), _p(LU, C.c_double), _p(perm, C.c_int32), C.c_double(lu_eps))
+    return LU, perm, bool(failed)
+
+
+def ref_lu_decompose(A):
+    """The unmodified reference's Solver::luDecompose: (LU, perm, ok)."""
+    L = ref_lib()
+    A = np.ascontiguousarray(A, np.float64)
+    n = A.shape[0]
+    LU = np.zeros((n, n), np.float64)
+    perm = np.zeros(n, np.int32)
+    ok = L.ref_lu_decompose(C.c_int(n), _p(A, C.c_double), _p(LU, C.c_double), _p(perm, C.c_int32))
+    return LU, perm, bool(ok)
 
 
 def gauss_seidel(A, b, x0=None, max_iters=1000, tol=1e-10):

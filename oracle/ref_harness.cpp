@@ -348,6 +348,45 @@ int ref_lu_solve(int n, const double* A, const double* b, double* x, int32_t* pe
     return 0;
 }
 
+// Solver::luDecompose (include/solver.hpp:30-80): packed L\U as the reference leaves it, its permutation and its
+// return value (1 = true).  LU is written only when the reference resized it (it does so before any early return
+// that matters here).
+int ref_lu_decompose(int n, const double* A, double* LU_out, int32_t* perm) {
+    Silence s;
+    Eigen::MatrixXd Am(n, n), LU;
+    for (int i = 0; i < n; ++i)
+        for (int j = 0; j < n; ++j) Am(i, j) = A[i * n + j];
+    std::vector<int> p;
+    const bool ok = Solver::luDecompose(Am, LU, p);
+    for (int i = 0; i < n && i < (int)p.size(); ++i) perm[i] = p[i];
+    if (LU.rows() == n && LU.cols() == n)
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < n; ++j) LU_out[i * n + j] = LU(i, j);
+    return ok ? 1 : 0;
+}
+
+// dcSolveGaussSeidel (src/dcanalysis.cpp:251-257 -> 71-92 / 166-237): the reference's own Gauss-Seidel DC driver,
+// warnings silenced; *n_warnings = lines it wrote to std::cerr.
+int ref_dc_gauss_seidel(void* hv, double* x, int64_t* n_warnings) {
+    auto* h = static_cast<Handle*>(hv);
+    std::ostringstream cap;
+    std::streambuf* old_err = std::cerr.rdbuf(cap.rdbuf());
+    Eigen::VectorXd sol;
+    {
+        Silence s2;  // (stdout)
+        std::cerr.rdbuf(cap.rdbuf());
+        sol = dcSolveGaussSeidel(h->ckt);
+    }
+    std::cerr.rdbuf(old_err);
+    const int n = h->ckt.numUnknowns();
+    for (int i = 0; i < n; ++i) x[i] = sol(i);
+    if (n_warnings) {
+        const std::string t = cap.str();
+        *n_warnings = (int64_t)std::count(t.begin(), t.end(), '\n');
+    }
+    return 0;
+}
+
 // Solver::solveLinearSystemGaussSeidel (include/solver.hpp:139-192), x in: x0, out: the last iterate
 int ref_gauss_seidel(int n, const double* A, const double* b, double* x, int max_iters, double tol) {
     Silence s;

@@ -214,13 +214,53 @@ def pin_sources():
     np.savez_compressed(os.path.join(OUT, "sources.npz"), **out)
 
 
+def pin_boundary():
+    """(b): Solver::luDecompose's packed factors and the Gauss-Seidel DC driver of the unmodified reference."""
+    rng = np.random.default_rng(11)
+    n_lu = 0
+    for n in list(range(1, 34)) + [40, 77]:
+        for k in range(4):
+            A = rng.uniform(-2, 2, (n, n))
+            if k == 1 and n > 2:
+                A[rng.integers(0, n)] = 0.0          # singular
+            if k == 2 and n > 1:
+                A[:, 0] = np.where(rng.uniform(size=n) < 0.5, 1.5, -1.5)  # ties in the first pivot search
+            if k == 3:
+                A[np.abs(A) < 1.2] = 0.0             # sparse, exact zeros
+            Lr, pr, okr = O.ref_lu_decompose(A)
+            Lo, po, failed = O.lu_factor(A)
+            assert okr == (not failed), (n, k)
+            assert np.array_equal(pr, po) and same_bits(Lr, Lo), f"luDecompose n={n} case {k}"
+            n_lu += 1
+    print(f"   Solver::luDecompose: {n_lu} matrices, packed factors and permutations bit-identical (incl. failures)")
+    out = {}
+    texts = {"buffer": open(os.path.join(REF_TESTS, "buffer.sp")).read(),
+             "dbmixer": open(os.path.join(REF_TESTS, "dbmixer.sp")).read(),
+             "sources": SOURCES_NETLIST,
+             "linear": "* linear divider with a current source\nI1 0 a DC 2e-3\nR1 a b 1k\nR2 b 0 3k\nR3 a 0 10k\n.end\n",
+             "mosdiode": "* current-driven MOS stack: no voltage source, so Gauss-Seidel has non-zero diagonals\n"
+                         "I1 0 d DC 1e-4\nR1 d 0 10k\nM1 d d s n 10e-6 0.35e-6 1\nR2 s 0 500\nI2 0 s DC 2e-5\n"
+                         ".MODEL 1 VT 0.5 MU 3e-2 COX 6e-3 LAMBDA 0.05 CJ0 4e-14\n.end\n"}
+    for name, text in texts.items():
+        x, nw = O.Ref(text).dc_gauss_seidel()
+        out[name + "_netlist"] = text
+        out[name + "_x"] = x
+        out[name + "_warnings"] = nw
+        print(f"   dcSolveGaussSeidel {name}: {nw} warning lines, max|x| = {np.abs(x).max():.3e}")
+    np.savez_compressed(os.path.join(OUT, "dc_gauss_seidel.npz"), **out)
+
+
 def main():
     O.build(force=True)
     summary = {}
     if "--sources-only" in sys.argv:
         pin_sources()
         return
+    if "--boundary-only" in sys.argv:
+        pin_boundary()
+        return
     pin_sources()
+    pin_boundary()
 
     # ---- buffer.sp (config 1): full raw waveform
     text = open(os.path.join(REF_TESTS, "buffer.sp")).read()
