@@ -25,6 +25,11 @@ struct Analysis {
     std::vector<std::vector<bool>> pat;                     // structural pattern incl. fill, permuted
     std::vector<std::vector<int>> rows_k, cols_k, ucols;    // elimination rows / pivot-row columns / U columns
     std::vector<bool> col_used_above;
+    // before_pivot[k][i]: at elimination step k the reference's pivot search (include/solver.hpp:46-56: positions k..N-1
+    // in its CURRENT row order, first maximum wins, strict '>') meets the row that ends at position i BEFORE the row
+    // the permutation predicts as pivot.  Such a row takes the pivot on a TIE, so the prediction check must reject
+    // |a(i,k)| >= |pivot| for it and |a(i,k)| > |pivot| for the rows scanned after the pivot.
+    std::vector<std::vector<bool>> before_pivot;
 };
 
 // Throws std::runtime_error when perm is not a permutation of 0..N-1.

@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <map>
 #include <sstream>
+#include <cstdio>
 #include <stdexcept>
 
 
@@ -69,6 +70,18 @@ Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm) {
         for (int i : A.rows_k[k])
             for (int j : A.cols_k[k]) A.pat[i][j] = true;
     }
+    // the reference's row order at every step: rows k and p are exchanged physically when position p wins (solver.hpp:64-67)
+    A.before_pivot.assign(N, std::vector<bool>(N, false));
+    {
+        std::vector<int> cur(N);
+        for (int i = 0; i < N; ++i) cur[i] = i;
+        for (int k = 0; k < N; ++k) {
+            int p = k;
+            while (cur[p] != perm[k]) ++p;
+            for (int q = k; q < p; ++q) A.before_pivot[k][A.pos_of_row[cur[q]]] = true;
+            std::swap(cur[k], cur[p]);
+        }
+    }
     A.ucols.assign(N, {});
     A.col_used_above.assign(N, false);
     for (int i = 0; i < N; ++i)
@@ -81,6 +94,16 @@ Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm) {
 }
 
 namespace {
+// rows the reference scans before the predicted pivot of step k win a tie (Analysis::before_pivot): lane mask
+std::string tie_clause(const Analysis& A, int k) {
+    unsigned mask = 0;
+    for (int i = k + 1; i < A.N; ++i)
+        if (A.before_pivot[k][i]) mask |= 1u << i;
+    if (!mask) return "";
+    char buf[96];
+    std::snprintf(buf, sizeof buf, " || (((0x%xu >> lane) & 1u) && fabs(a%d) == fabs(pk))", mask, k);
+    return buf;
+}
 // must match warp_mem_doubles() in newton_warp.cuh and the carve-up in the generated kernel
 size_t warp_doubles_generic(int n_values) { return 32 * 33 + 3 * 32 + ((n_values + 3) & ~3); }
 size_t warp_doubles_spec(int n_values) { return warp_doubles_generic(n_values) + ((2 * (n_values + 1) + 1) & ~1); }
@@ -225,7 +248,8 @@ SpecHost generate_tran_spec(const HostPlan& hp, const std::vector<int32_t>& perm
     for (int k = 0; k < N; ++k) {
         o << "            {  // step " << k << "\n"
           << "                const double pk = bcast(a" << k << ", " << k << ");\n"
-          << "                bad = bad || (lane > " << k << " && fabs(a" << k << ") > fabs(pk)) || (fabs(pk) < c.lu_eps);\n"
+          << "                bad = bad || (lane > " << k << " && (fabs(a" << k << ") > fabs(pk)" << tie_clause(A, k)
+          << ")) || (fabs(pk) < c.lu_eps);\n"
           << "                const double rk = rcp_seq(pk);\n"
           << "                if (lane == " << k << ") { dg = pk; rdg = rk; }\n";
         if (!A.rows_k[k].empty()) {

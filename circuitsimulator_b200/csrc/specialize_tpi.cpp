@@ -484,12 +484,15 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     auto emit_step = [&](RowGen& R, int k) {
         const int i = R.i;
         const Val a = R.row[k];
-        // the reference would have picked this row instead of the predicted pivot (solver.hpp:46-56)
+        // the reference would have picked this row instead of the predicted pivot (solver.hpp:46-56): a larger
+        // entry always, an EQUAL one when its scan meets this row before the predicted pivot row (first maximum wins)
+        const bool tie_loses = A.before_pivot[k][i];
         if (a.c && Dv[k].c) {
-            if (std::fabs(a.v) > std::fabs(Dv[k].v)) o << ind << "bad@ = true;\n";
+            if (std::fabs(a.v) > std::fabs(Dv[k].v) || (tie_loses && std::fabs(a.v) == std::fabs(Dv[k].v)))
+                o << ind << "bad@ = true;\n";
         } else {
-            o << ind << "bad@ = bad@ || (fabs(" << a.e << ") > " << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")")
-              << ");\n";
+            o << ind << "bad@ = bad@ || (fabs(" << a.e << ") " << (tie_loses ? ">=" : ">") << " "
+              << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")") << ");\n";
         }
         std::snprintf(num, sizeof num, "f%d_%d@", i, k);
         const Val f = divide(a, k, num, ind);

@@ -261,3 +261,54 @@ def test_automatic_mode_adds_variants_then_picks_the_kernel_by_miss_rate(torch):
             assert rates[0] > 0.02, rates
             assert "variant 1 added" in info["log"] or info["kind"] == 2, info["log"]
             assert info["kind"] == 2 or rates[-1] < rates[0] / 3, (rates, info["log"])
+
+
+TIE_NETLIST = """* two voltage sources on one node: an exact tie (|+1| = |+1|) in the first pivot search
+V1 a 0 DC 1
+V2 a b DC 0.5
+R1 b 0 1k
+R2 a c 2k
+C1 c 0 1e-12
+M1 c b 0 n 10e-6 0.35e-6 1
+.MODEL 1 VT 0.5 MU 3e-2 COX 6e-3 LAMBDA 0.05 CJ0 4e-14
+.TRAN 1e-11 1e-9
+"""
+
+
+@pytest.mark.parametrize("jit,opts", [(3, None), (3, "0"), (2, None)])
+def test_exact_tie_goes_to_the_row_the_reference_scans_first(torch, monkeypatch, jit, opts):
+    """include/solver.hpp:46-56 keeps the FIRST maximum of the pivot search.  Rows V1 and V2 tie in column 0 and the
+    reference takes V1's; a kernel specialised for the other choice ([4,3,...]) must notice (the tied row is scanned
+    before its predicted pivot) and redo every solve generically instead of silently factorising in another order."""
+    from circuitsimulator_b200 import capi
+    from circuitsimulator_b200.netlist import Netlist
+    if opts is not None:
+        monkeypatch.setenv("CSIM_TPI_OPTS", opts)  # 0: no constant propagation -> the tie is tested numerically
+    nl = Netlist(TIE_NETLIST)
+    topo = O.Topology(nl.n_unknowns, nl.n_node_eq, nl.elem_type, nl.elem_flags, nl.elem_nodes, nl.elem_branch,
+                      nl.elem_param, nl.n_params, nl.params, nl.node_names, nl.elem_names)
+    B, dt, ns = 7, nl.tran["tstep"], nl.n_steps
+    P = O.monte_carlo(topo, B, 31)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    want = []
+    for b in range(B):
+        od = O.dc(topo, P[b])
+        want.append(O.tran(topo, P[b], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"], trace_cap=4))
+    assert want[0]["trace"].perm[0].tolist() == [3, 4, 2, 0, 1]  # the reference's order: V1's row first
+    for perm, all_redone in (([3, 4, 2, 0, 1], False), ([4, 3, 2, 0, 1], True)):
+        plan = nl.plan()
+        plan.jit_mode(jit)
+        plan.specialize(np.array(perm, np.int32))
+        params = torch.from_numpy(np.ascontiguousarray(P.T)).cuda()
+        d = capi.dc(plan, params)
+        setup = nl.tran_setup(probes=np.arange(nl.n_unknowns, dtype=np.int32))
+        t = capi.tran(plan, params, d["x"], setup, pivot_hash=d["hash"], status=d["status"], want_iters_step=True)
+        torch.cuda.synchronize()
+        info = plan.spec_info()
+        assert info["kind"] == jit
+        assert (info["fallback_solves"] == info["solves"]) if all_redone else (info["fallback_solves"] == 0), info
+        wave = t["wave"].cpu().numpy()
+        for b in range(B):
+            assert_same_bits(wave[b].T, want[b]["wave"], f"perm {perm} inst {b}")
+            assert np.array_equal(t["iters_step"][:, b].cpu().numpy(), want[b]["iters_step"])
+            assert np.uint64(t["hash"][b].item() & 0xFFFFFFFFFFFFFFFF) == np.uint64(want[b]["hash"])
