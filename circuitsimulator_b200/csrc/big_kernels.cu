@@ -479,7 +479,7 @@ dc_big_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double* _
             int count = 0;
             for (int iter = 0; iter < c.dc_max_iters; ++iter) {
                 ++count;
-                if (lane == 0) vt[gmin_slot] = gmin;
+                if (lane == 0 && gmin_slot >= 0) vt[gmin_slot] = gmin;
                 eval_mos(m, params, B, b, c.mos_off_gds, w.xs, vt, lane);
                 __syncwarp();
                 if (big_newton_solve(m, w, M, b, N, c.lu_eps, lane, h)) st |= CSIM_ST_LU_SINGULAR;

@@ -143,6 +143,9 @@ namespace {
 int spec_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     SpecState& sp = plan->spec;
     sp.ready = false;
+    // launches of the old kernel may still be running on other streams (the caller holds spec.mu, so none is being
+    // prepared): retire its module and tables only once the device is idle
+    cudaDeviceSynchronize();
     for (void* d : sp.owned) cudaFree(d);
     sp.owned.clear();
     jit_unload(sp.k);
@@ -244,6 +247,7 @@ int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& pe
     TpiState& tp = plan->tpi;
     tp.ready = false;
     tp.wide_tried = tp.wide_ready = false;
+    cudaDeviceSynchronize();  // see spec_build: running launches of the old kernels finish before they are unloaded
     jit_unload(tp.k_wide);
     if (tp.d_stats) cudaFree(tp.d_stats);
     if (tp.d_miss) cudaFree(tp.d_miss);
@@ -634,6 +638,7 @@ void csim_plan_destroy(csim_plan* plan) {
         jit_unload(plan->tpi.k);
         jit_unload(plan->tpi.k_wide);
         if (plan->tpi.d_stats) cudaFree(plan->tpi.d_stats);
+        if (plan->tpi.d_miss) cudaFree(plan->tpi.d_miss);
         jit_unload(plan->stamp_spec[0].k);
         jit_unload(plan->stamp_spec[1].k);
     }
@@ -805,6 +810,11 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
     T.probes = d_pack + 2 * ns;
     T.skip = g_tran_skip;
     cudaError_t e;
+    // The learned kernel-selection state of the plan (which kernel, its module, statistics buffers) is guarded by
+    // spec.mu from the choice to the launch: another host thread sharing the plan cannot rebuild or unload a kernel
+    // between this thread's spec_prepare and its cudaLaunchKernel (launches themselves are asynchronous).
+    std::unique_lock<std::recursive_mutex> plan_lock(plan->spec.mu, std::defer_lock);
+    if (!big) plan_lock.lock();
     const int kind = big ? -1 : spec_prepare(plan, B, params, x, a->dt, stream);
     if (big && use_dense(plan)) {
         e = launch_tran_dense(plan->dev, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
@@ -1008,6 +1018,16 @@ static int batch_tran_impl(csim_batch* b, const csim_tran_args* a, const double*
         CUC(cudaMemcpyAsync(d_table, a->src_table, bytes, cudaMemcpyHostToDevice, b->stream));
     }
     if (a->src_group_b) {
+        for (int s = 0; s < plan->host.n_sources; ++s) {
+            if (!a->src_mode || a->src_mode[s] == CSIM_SRC_CONST) continue;
+            for (int64_t i = 0; i < B; ++i) {
+                const int32_t gi = a->src_group_b[(size_t)s * B + i];
+                if (gi < 0 || gi >= a->n_groups) {
+                    cleanup();
+                    return fail(CSIM_E_INVALID, "csim_batch_tran: src_group_b entry out of range");
+                }
+            }
+        }
         size_t bytes = sizeof(int32_t) * (size_t)plan->host.n_sources * B;
         CUC(cudaMalloc((void**)&d_group_b, bytes));
         CUC(cudaMemcpyAsync(d_group_b, a->src_group_b, bytes, cudaMemcpyHostToDevice, b->stream));
@@ -1096,7 +1116,21 @@ static int batch_tran_impl(csim_batch* b, const csim_tran_args* a, const double*
     if (pivot_hash) CUC(cudaMemcpyAsync(pivot_hash, b->d_hash, sizeof(uint64_t) * B, cudaMemcpyDeviceToHost, b->stream));
     if (status) CUC(cudaMemcpyAsync(status, b->d_status, sizeof(uint32_t) * B, cudaMemcpyDeviceToHost, b->stream));
     CUC(cudaStreamSynchronize(b->stream));
-    if (chunked) CUC(cudaStreamSynchronize(b->copy_stream));
+    if (chunked) {
+        CUC(cudaStreamSynchronize(b->copy_stream));
+        // rows no step recorded: "never written" = NaN, as the single-launch path returns them
+        const int64_t stride = a->out_stride, r0 = a->out_begin_step / stride;
+        int64_t rec_lo = (a->step_begin + stride) / stride - 1 - r0, rec_hi = (int64_t)a->step_end / stride - r0;
+        if (rec_lo < 0) rec_lo = 0;
+        if (rec_hi > a->wave_ld) rec_hi = a->wave_ld;
+        if (rec_hi < rec_lo) rec_hi = rec_lo;
+        if (rec_lo > 0 || rec_hi < a->wave_ld)
+            for (size_t row = 0; row < (size_t)B * a->n_probes; ++row) {
+                double* w = wave + row * (size_t)a->wave_ld;
+                std::memset(w, 0xFF, sizeof(double) * (size_t)rec_lo);
+                std::memset(w + rec_hi, 0xFF, sizeof(double) * (size_t)(a->wave_ld - rec_hi));
+            }
+    }
     CUC(cudaEventElapsedTime(&b->last_ms, b->ev0, b->ev1));
     cleanup();
 #undef CUC

@@ -487,7 +487,7 @@ dc_dense_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double*
                 int count = 0;
                 for (int iter = 0; iter < c.dc_max_iters; ++iter) {
                     ++count;
-                    if (tid == 0) vt[gmin_slot] = gmin;
+                    if (tid == 0 && gmin_slot >= 0) vt[gmin_slot] = gmin;
                     eval_mos(m, params, B, b, c.mos_off_gds, S.xs, vt, tid, kDnThreads);
                     __syncthreads();
                     if (dn_newton_solve(m, vt, A, N, LD, S, c.lu_eps, tid, h)) st |= CSIM_ST_LU_SINGULAR;

@@ -208,7 +208,7 @@ dc_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double* __res
             int count = 0;
             for (int iter = 0; iter < c.dc_max_iters; ++iter) {
                 ++count;
-                if (lane == 0) w.vt[gmin_slot] = gmin;
+                if (lane == 0 && gmin_slot >= 0) w.vt[gmin_slot] = gmin;
                 eval_mos(m, params, B, b, c.mos_off_gds, w.xs, w.vt, lane);
                 __syncwarp();
                 assemble(m, prog, w, N, lane);

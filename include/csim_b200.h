@@ -123,7 +123,11 @@ typedef struct csim_topology {
     const int32_t* elem_param;  /* [n_elems] offset of the element's first parameter in [0,P)          */
 } csim_topology;
 
-typedef struct csim_plan csim_plan;   /* topology lowered to device tables; immutable, shareable   */
+/* csim_plan: a topology lowered to device tables (immutable) plus the kernels specialised for it at run time and
+ * their selection statistics (learned state, guarded by a lock inside the plan from the choice of a kernel to its
+ * launch; a kernel is retired only after the device is idle).  Host threads may share one plan, each with its own
+ * csim_batch / stream.                                                                                        */
+typedef struct csim_plan csim_plan;
 typedef struct csim_batch csim_batch; /* B instances on one device: owns device buffers + a stream */
 
 #ifndef __CUDACC_RTC__
@@ -317,7 +321,11 @@ typedef struct csim_tran_args {
     const double* src_table;    /* [n_groups][table_steps] device                            */
     const int32_t* src_mode;    /* [n_sources] host array, csim_src_mode                     */
     const int32_t* src_group;   /* [n_sources] host array: group used by every instance, or  */
-    const int32_t* src_group_b; /* [n_sources][B] DEVICE array: per-instance group (overrides src_group when non-NULL) */
+    const int32_t* src_group_b; /* [n_sources][B] DEVICE array: per-instance group (overrides src_group when non-NULL);
+                                 * entries must lie in [0, n_groups) — csim_batch_tran checks its host copy, the
+                                 * device-pointer entry points take them as given.  The tabulated rows carry the
+                                 * sine's freq and phi: the per-instance freq / phi in `params` are not read on the
+                                 * device (td is, for the t < td test), so a swept frequency needs its own row.  */
     /* outputs */
     int32_t n_probes;       /* probed unknowns                                               */
     const int32_t* probes;  /* [n_probes] host array of equation indices                     */
