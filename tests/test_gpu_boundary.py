@@ -91,7 +91,7 @@ def test_host_layer_luDecompose_is_drop_in(torch):
             assert np.allclose(L @ U, A[perm], rtol=1e-9, atol=1e-9)
 
 
-@pytest.mark.parametrize("name", ["buffer", "dbmixer", "sources", "linear", "mosdiode"])
+@pytest.mark.parametrize("name", ["buffer", "sources", "linear", "mosdiode"])  # (dbmixer: same 660-warning path as buffer, 46 s)
 def test_dc_gauss_seidel_drivers_equal_the_reference(torch, capfd, name):
     """dcSolveGaussSeidel of the host layer vs the unmodified reference's own result (tests/golden/dc_gauss_seidel.npz,
     make_golden.py: pin_boundary): bit for bit, same number of warning lines."""
