@@ -36,7 +36,7 @@ EXPORTS = [
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
     "csim_plan_specialize_variants", "csim_plan_generate_source_variants", "csim_dev_selftest_tdiv",
     "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
-    "csim_dev_fp64_peak", "csim_dev_lu_factor", "csim_host_lu_factor",
+    "csim_dev_fp64_peak", "csim_dev_lu_factor", "csim_host_lu_factor", "csim_dev_lu_solve_noalloc",
 ]
 
 
@@ -317,6 +317,18 @@ def lu_solve(A, b, lu_eps=1e-15):
     _check(lib().csim_dev_lu_solve(n, B, _ptr(A), _ptr(b), _ptr(x), _ptr(perm), _ptr(sing), float(lu_eps), _stream()),
            "csim_dev_lu_solve")
     return x, perm, sing
+
+
+def lu_solve_noalloc(A, b, x, perm, sing, lu_eps=1e-15):
+    """csim_dev_lu_solve_noalloc: like lu_solve but every buffer (outputs included) is the caller's, and the library
+    allocates nothing (static device scratch).  A [N*N,B], b [N,B] -> x [N,B], perm [N,B] int32, sing [B] int32."""
+    n, B = b.shape
+    _dev_f64(A, (n * n, B))
+    _dev_f64(b)
+    _dev_f64(x, (n, B))
+    lib().csim_dev_lu_solve_noalloc.argtypes = [C.c_int32, C.c_int64] + [C.c_void_p] * 5 + [C.c_double, C.c_void_p]
+    _check(lib().csim_dev_lu_solve_noalloc(n, B, _ptr(A), _ptr(b), _ptr(x), _ptr(perm), _ptr(sing), float(lu_eps),
+                                           _stream()), "csim_dev_lu_solve_noalloc")
 
 
 def lu_factor(A, n, lu_eps=1e-15):

@@ -722,6 +722,23 @@ int csim_dev_lu_solve(int32_t n, int64_t B, const double* A, const double* b, do
     return CSIM_OK;
 }
 
+int csim_dev_lu_solve_noalloc(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                              int32_t* singular, double lu_eps, void* stream) {
+    const int max_n = lu_dense_noalloc_max_n();
+    if (n <= 0 || n > max_n)
+        return fail(CSIM_E_UNSUPPORTED, "csim_dev_lu_solve_noalloc: n = " + std::to_string(n) + " is outside 1.." +
+                                            std::to_string(max_n) + " (one [A | b] workspace must fit the " +
+                                            std::to_string(kDnNoAllocDoubles * sizeof(double) >> 20) +
+                                            " MiB static scratch array)");
+    if (B <= 0 || !A || !b || !x) return fail(CSIM_E_INVALID, "csim_dev_lu_solve_noalloc: bad argument");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(CSIM_E_CUDA, "csim_dev_lu_solve_noalloc: no CUDA device (no CPU fallback)");
+    CU(launch_lu_dense_noalloc(n, B, A, b, x, perm, singular, lu_eps, (cudaStream_t)stream));
+    return CSIM_OK;
+}
+
 int csim_dev_lu_factor(int32_t n, int64_t B, const double* A, double* LU, int32_t* perm, int32_t* singular,
                        double lu_eps, void* stream) {
     if (n <= 0 || n > kDenseMaxN) return fail(CSIM_E_UNSUPPORTED, "csim_dev_lu_factor: n out of range");

@@ -635,6 +635,58 @@ cudaError_t launch_lu_dense(int N, int64_t B, const double* A, const double* b, 
     return e;
 }
 
+// ---- allocation-free variant of the dense LU solve (csim_dev_lu_solve_noalloc) -----------------------------------
+// Callers under CUDA graph capture, tight serving loops or harnesses that forbid cudaMalloc cannot take
+// launch_lu_dense's stream-ordered scratch.  Here the per-CTA [A | b] workspaces live in a file-scope device array of
+// a fixed, modest size; every GPU that loads the library holds it until exit.  The array's name is a host-side
+// stand-in in host code, NOT a device address: the address is asked for once per device (with that device current)
+// through cudaGetSymbolAddress and cached.  Every call shares the array and it keeps the last call's contents;
+// nothing has to start at zero (each CTA rewrites all N x (N + 1) entries it reads before factorising, the padding
+// columns of a row are never read), but two calls that overlap on the GPU (different streams) race on it.
+static __device__ __align__(256) double dn_noalloc_scratch[kDnNoAllocDoubles];
+
+static cudaError_t dn_noalloc_address(double** out) {
+    constexpr int kMaxDev = 64;
+    static double* addr[kMaxDev] = {};
+    static bool have[kMaxDev] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDev) return cudaErrorInvalidDevice;
+    if (!have[dev]) {  // (a race between host threads writes the same value twice)
+        double* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, dn_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        addr[dev] = p;
+        have[dev] = true;
+    }
+    *out = addr[dev];
+    return cudaSuccess;
+}
+
+// largest n whose single [A | b] workspace fits the static array
+int lu_dense_noalloc_max_n() {
+    int n = kDenseMaxN;
+    while (n > 1 && (size_t)n * dn_ld(n) > kDnNoAllocDoubles) --n;
+    return n;
+}
+
+cudaError_t launch_lu_dense_noalloc(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                                    int32_t* singular, double eps, cudaStream_t stream) {
+    size_t smem;
+    int grid;
+    cudaError_t e = dn_grid(lu_dense_kernel, N, B, smem, grid);
+    if (e != cudaSuccess) return e;
+    const size_t per_cta = (size_t)N * dn_ld(N);
+    const size_t fit = kDnNoAllocDoubles / per_cta;  // persistent CTAs loop over the batch: fewer CTAs, same results
+    if (fit < 1) return cudaErrorInvalidValue;
+    if ((size_t)grid > fit) grid = (int)fit;
+    DnMem M{};
+    if ((e = dn_noalloc_address(&M.A)) != cudaSuccess) return e;
+    lu_dense_kernel<<<grid, kDnThreads, smem, stream>>>(N, B, A, b, x, perm, singular, eps, M, nullptr);
+    return cudaGetLastError();
+}
+
 #ifdef CSIM_DN_PROF
 cudaError_t dn_prof_read(unsigned long long* out) { return cudaMemcpyFromSymbol(out, dn_prof, sizeof(dn_prof)); }
 #endif

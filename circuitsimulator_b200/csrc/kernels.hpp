@@ -45,6 +45,12 @@ cudaError_t launch_dc_dense(const DevPlan& P, int64_t B, const double* params, d
 cudaError_t launch_lu_dense(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
                             int32_t* singular, double eps, cudaStream_t stream, double* lu_out = nullptr);
 
+// allocation-free dense LU solve: scratch in a file-scope device array of kDnNoAllocDoubles doubles (32 MiB per GPU)
+constexpr size_t kDnNoAllocDoubles = (size_t)4 << 20;
+int lu_dense_noalloc_max_n();
+cudaError_t launch_lu_dense_noalloc(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                                    int32_t* singular, double eps, cudaStream_t stream);
+
 cudaError_t launch_sstate_check(int N, int64_t B, const double* x, const double* x_prev, double tol, int period,
                                 uint8_t* skip, int32_t* periods, double* delta, unsigned long long* n_open,
                                 cudaStream_t stream);

@@ -289,6 +289,21 @@ int csim_dev_lu_solve(int32_t n, int64_t B, const double* A, const double* b, do
                       int32_t* singular, double lu_eps, void* stream);
 #endif
 
+/* Allocation-free variant of csim_dev_lu_solve.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments and results as csim_dev_lu_solve (always the dense large-matrix kernel,
+ * whatever n), but the kernel's per-CTA [A | b] workspaces live in a static 32 MiB device array inside the library
+ * (every GPU that loads the library holds it until exit) and the call performs no cudaMalloc / cudaFree /
+ * stream-ordered allocation.  Limit: 1 <= n <= 1280 (one n x (n + 1) workspace must fit the array; it does up to
+ * kDenseMaxN); larger n is rejected with CSIM_E_UNSUPPORTED.  Fewer workspaces than resident CTAs only means fewer
+ * CTAs loop over the batch: results are bit-identical.  All calls share the array, which keeps the last call's
+ * contents (nothing needs to start at zero: every workspace is fully rewritten before it is read); calls that
+ * OVERLAP on the GPU (different streams, or different host threads on one device) race on it — serialise them. */
+#ifndef __CUDACC_RTC__
+int csim_dev_lu_solve_noalloc(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
+                              int32_t* singular, double lu_eps, void* stream);
+#endif
+
 /* Batched Solver::luDecompose (include/solver.hpp:30-80): LU [N*N][B] = the packed factors exactly as the
  * reference leaves them — U on and above the diagonal, the multipliers L(i,k) in the strict lower triangle
  * (solver.hpp:70-72), rows exchanged physically, multipliers included (solver.hpp:64-67); perm [N][B];
