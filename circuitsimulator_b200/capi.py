@@ -36,7 +36,7 @@ EXPORTS = [
     "csim_plan_stamp_info", "csim_plan_generate_stamp_source", "csim_plan_generate_source_kind",
     "csim_plan_specialize_variants", "csim_plan_generate_source_variants", "csim_dev_selftest_tdiv",
     "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
-    "csim_dev_fp64_peak", "csim_dev_lu_factor", "csim_host_lu_factor", "csim_dev_lu_solve_noalloc",
+    "csim_dev_fp64_peak", "csim_dev_lu_factor", "csim_host_lu_factor", "csim_dev_lu_solve_noalloc", "csim_dev_selftest_tdiv_mul",
 ]
 
 
@@ -585,6 +585,18 @@ def selftest_tdiv(a, b):
     _check(lib().csim_dev_selftest_tdiv(a.numel(), _ptr(a), _ptr(b), _ptr(q), _ptr(qr), _ptr(ok), _stream()),
            "csim_dev_selftest_tdiv")
     return q, qr, ok
+
+
+def selftest_tdiv_mul(a, b):
+    """csim_dev_selftest_tdiv_mul -> (q, q_ref, flags): bit 0 range guard accepts, bit 1 pivot guard fires."""
+    torch = _torch()
+    q = torch.empty_like(a)
+    qr = torch.empty_like(a)
+    fl = torch.empty(a.shape, dtype=torch.int32, device=a.device)
+    lib().csim_dev_selftest_tdiv_mul.argtypes = [C.c_int64] + [C.c_void_p] * 6
+    _check(lib().csim_dev_selftest_tdiv_mul(a.numel(), _ptr(a), _ptr(b), _ptr(q), _ptr(qr), _ptr(fl), _stream()),
+           "csim_dev_selftest_tdiv_mul")
+    return q, qr, fl
 
 
 def selftest_div(a, b):

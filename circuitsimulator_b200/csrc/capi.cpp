@@ -1504,6 +1504,13 @@ int csim_dev_selftest_tdiv(int64_t n, const double* a, const double* b, double* 
     return CSIM_OK;
 }
 
+int csim_dev_selftest_tdiv_mul(int64_t n, const double* a, const double* b, double* q, double* q_ref, int32_t* flags,
+                               void* stream) {
+    if (n <= 0 || !a || !b || !q || !q_ref || !flags) return fail(CSIM_E_INVALID, "csim_dev_selftest_tdiv_mul: bad argument");
+    CU(launch_tdiv_mul_selftest(n, a, b, q, q_ref, flags, (cudaStream_t)stream));
+    return CSIM_OK;
+}
+
 float csim_batch_last_kernel_ms(const csim_batch* b) { return b ? b->last_ms : 0.f; }
 
 int csim_dev_fp64_peak(int device, double* tflops_mul_add) {

@@ -594,6 +594,24 @@ __global__ void tdiv_selftest_kernel(int64_t n, const double* __restrict__ a, co
     }
 }
 
+// tdiv_mul (the multiplier division with folded guards): flags bit 0 = the range guard accepts the division (then q
+// must equal q_ref bit for bit), bit 1 = the pivot guard fires (|q| >= 1 on the high word)
+__global__ void tdiv_mul_selftest_kernel(int64_t n, const double* __restrict__ a, const double* __restrict__ b,
+                                         double* __restrict__ q, double* __restrict__ q_ref, int32_t* __restrict__ flags) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        unsigned int gacc = 0u, pmx = 0u;
+        q[i] = tdiv_mul(a[i], b[i], rcp_seq(b[i]), gacc, pmx);
+        q_ref[i] = a[i] / b[i];
+        flags[i] = (gacc <= kTdivTMax ? 1 : 0) | (pmx >= kTdivTOne ? 2 : 0);
+    }
+}
+
+cudaError_t launch_tdiv_mul_selftest(int64_t n, const double* a, const double* b, double* q, double* q_ref,
+                                     int32_t* flags, cudaStream_t stream) {
+    tdiv_mul_selftest_kernel<<<1184, 256, 0, stream>>>(n, a, b, q, q_ref, flags);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_tdiv_selftest(int64_t n, const double* a, const double* b, double* q, double* q_ref,
                                  int32_t* in_range, cudaStream_t stream) {
     tdiv_selftest_kernel<<<1184, 256, 0, stream>>>(n, a, b, q, q_ref, in_range);

@@ -65,6 +65,8 @@ cudaError_t launch_harmonics(int64_t n_signals, int M, int64_t ld, const double*
 
 cudaError_t launch_tdiv_selftest(int64_t n, const double* a, const double* b, double* q, double* q_ref,
                                  int32_t* in_range, cudaStream_t stream);
+cudaError_t launch_tdiv_mul_selftest(int64_t n, const double* a, const double* b, double* q, double* q_ref,
+                                     int32_t* flags, cudaStream_t stream);
 cudaError_t launch_div_selftest(int64_t n, const double* a, const double* b, double* q_split, double* q_ref,
                                 cudaStream_t stream);
 

@@ -261,6 +261,12 @@ int csim_dev_selftest_div(int64_t n, const double* a, const double* b, double* q
  * (elsewhere the kernel redoes the solve with true divisions). */
 int csim_dev_selftest_tdiv(int64_t n, const double* a, const double* b, double* q, double* q_ref, int32_t* in_range,
                            void* stream);
+/* The multiplier division of the thread-per-instance kernel with its guards folded into unsigned accumulators
+ * (2^-1021 <= |b| <= 2^1021): flags[i] bit 0 = the range guard accepts the division — q must then equal q_ref bit
+ * for bit; bit 1 = the pivot guard fires (|q| >= 1 judged on the high word): it must fire whenever |a| > |b| and
+ * may only fire when |a| >= |b|.                                                                        */
+int csim_dev_selftest_tdiv_mul(int64_t n, const double* a, const double* b, double* q, double* q_ref, int32_t* flags,
+                               void* stream);
 #endif
 
 /* ===================== device-pointer entry points ======================== */

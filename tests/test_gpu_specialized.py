@@ -106,6 +106,52 @@ def test_guarded_division_of_the_thread_per_instance_kernel(torch):
     assert ok[plain].all() and plain.sum() > n // 2
 
 
+def test_multiplier_division_with_folded_guards(torch):
+    """tdiv_mul / tdiv_nz (spec_runtime.cuh): one unsigned accumulator instead of exponent min/max bookkeeping.
+    (1) wherever the range guard accepts, the quotient is IEEE a / b bit for bit; (2) ordinary magnitudes are
+    accepted; exact-zero, denormal and non-finite numerators are not (the solve is redone); (3) the pivot guard fires
+    for EVERY |a| > |b| (a row the reference's pivot search would have preferred, include/solver.hpp:46-56) and only
+    for |a| >= |b|; pairs one ulp apart and exact ties included."""
+    from circuitsimulator_b200 import capi
+    rng = np.random.default_rng(2)
+    n = 1 << 22
+    a = rng.normal(size=n) * 10.0 ** rng.uniform(-30, 30, n)
+    b = rng.normal(size=n) * 10.0 ** rng.uniform(-30, 30, n)
+    k = 1 << 18
+    a[:k] = np.ldexp(rng.uniform(1, 2, k), rng.integers(-1074, 1023, k)) * rng.choice([-1.0, 1.0], k)
+    b[:k] = np.ldexp(rng.uniform(1, 2, k), rng.integers(-1021, 1021, k)) * rng.choice([-1.0, 1.0], k)
+    b[k:2 * k] = np.nextafter(np.ldexp(1.0, rng.integers(-500, 500, k)), 0)        # mantissa all ones
+    a[k:2 * k] = b[k:2 * k] * rng.choice([-1.0, 1.0], k)                              # exact ties
+    a[2 * k:3 * k] = rng.choice([0.0, -0.0], k)                                       # exact zeros
+    a[3 * k:4 * k] = rng.integers(1, 1 << 30, k) * 5e-324 * rng.choice([-1.0, 1.0], k)  # denormal numerators
+    b[3 * k:4 * k] = rng.integers(1, 64, k).astype(float)
+    # neighbours: |a| one ulp above / below |b|, every sign combination
+    bb = np.ldexp(rng.uniform(1, 2, k), rng.integers(-300, 300, k))
+    up = np.nextafter(bb, np.inf)
+    dn = np.nextafter(bb, 0)
+    b[4 * k:5 * k] = bb * rng.choice([-1.0, 1.0], k)
+    a[4 * k:5 * k] = np.where(rng.uniform(size=k) < 0.5, up, dn) * rng.choice([-1.0, 1.0], k)
+    a[5 * k:6 * k] = np.array([np.inf, -np.inf, np.nan])[rng.integers(0, 3, k)]
+    b[b == 0.0] = 1.0
+    q, qr, fl = capi.selftest_tdiv_mul(dev(torch, a), dev(torch, b))
+    torch.cuda.synchronize()
+    q, qr, fl = q.cpu().numpy(), qr.cpu().numpy(), fl.cpu().numpy()
+    ok, piv = (fl & 1).astype(bool), (fl & 2).astype(bool)
+    with np.errstate(all="ignore"):
+        host = a / b
+    nan = np.isnan(host)
+    assert np.array_equal(qr[~nan].view(np.uint64), host[~nan].view(np.uint64))
+    diff = ok & (q.view(np.uint64) != qr.view(np.uint64))
+    assert not diff.any(), (int(diff.sum()), [(float.hex(x), float.hex(y)) for x, y in zip(a[diff][:6], b[diff][:6])])
+    assert not ok[2 * k:4 * k].any() and not ok[5 * k:6 * k].any()
+    plain = (np.abs(a) > 1e-200) & (np.abs(a) < 1e200) & (np.abs(host) > 1e-200) & (np.abs(host) < 1e200)
+    assert ok[plain].all() and plain.sum() > n // 2
+    bigger, smaller = ok & (np.abs(a) > np.abs(b)), ok & (np.abs(a) < np.abs(b))
+    assert piv[bigger].all() and bigger[4 * k:5 * k].sum() > k // 4
+    assert not piv[smaller].any() and smaller[4 * k:5 * k].sum() > k // 4
+    assert piv[k:2 * k][ok[k:2 * k]].all()                 # exact ties go to the redo path (conservative)
+
+
 KINDS = pytest.mark.parametrize("kind", [2, 3])  # 2: warp per instance (csim_tran_spec), 3: thread per instance (csim_tran_tpi)
 ENTRY = {2: "csim_tran_spec", 3: "csim_tran_tpi"}
 
