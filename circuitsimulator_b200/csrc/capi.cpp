@@ -194,7 +194,7 @@ int spec_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     return CSIM_OK;
 }
 
-// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bits 8-9: replicas - 1, bits 12-14: warps per CTA, bits 16-19: rows in flight); unset = defaults.
+// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bit 5: folded division guards, bit 6: opaque row parking; bits 8-9: replicas - 1, bits 12-14: warps per CTA, bits 16-19: rows in flight); unset = defaults.
 TpiOptions tpi_options_from_env() {
     TpiOptions opt;
     if (const char* env = std::getenv("CSIM_TPI_OPTS")) {
@@ -204,6 +204,8 @@ TpiOptions tpi_options_from_env() {
         opt.mos_in_smem = m & 4;
         opt.q_in_smem = m & 8;
         opt.mos_branchless = m & 16;
+        opt.fold_guards = m & 32;
+        opt.opaque_park = m & 64;
         opt.replicas = 1 + ((m >> 8) & 3);
         opt.warps_per_cta = (m >> 12) & 7;
         if ((m >> 16) & 15) opt.rows_in_flight = (m >> 16) & 15;

@@ -128,17 +128,20 @@ struct Val {
     double v = 0.0;
     std::string e;
     int t = 0;  // dependency-chain estimate: cycle at which the value is available (kLat* below)
+    bool z = false;  // may routinely be an EXACT zero (a MOSFET's gm while it is off, and what is built from it)
     static Val K(double x) {
         Val r;
         r.c = true;
         r.v = x;
         r.e = lit(x);
+        r.z = x == 0.0;
         return r;
     }
-    static Val E(const std::string& s, int t = 0) {
+    static Val E(const std::string& s, int t = 0, bool z = false) {
         Val r;
         r.e = s;
         r.t = t;
+        r.z = z;
         return r;
     }
 };
@@ -151,16 +154,16 @@ constexpr int kLatOp = 8, kLatDiv = 28, kLatRcp = 64, kLatMos = 96, kLatSmem = 3
 Val neg(const Val& a) {
     if (a.c) return Val::K(-a.v);
     if (a.e.size() > 3 && a.e.compare(0, 2, "(-") == 0 && a.e.back() == ')' && a.e.find('(', 1) == std::string::npos)
-        return Val::E(a.e.substr(2, a.e.size() - 3), a.t);
-    return Val::E("(-" + a.e + ")", a.t);
+        return Val::E(a.e.substr(2, a.e.size() - 3), a.t, a.z);
+    return Val::E("(-" + a.e + ")", a.t, a.z);
 }
 Val add(const Val& a, const Val& b) {
     if (a.c && b.c) return Val::K(a.v + b.v);
-    return Val::E("d_add(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp);
+    return Val::E("d_add(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp, a.z && b.z);
 }
 Val sub(const Val& a, const Val& b) {
     if (a.c && b.c) return Val::K(a.v - b.v);
-    return Val::E("d_sub(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp);
+    return Val::E("d_sub(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp, a.z && b.z);
 }
 Val mul(const Val& a, const Val& b) {
     if (a.c && b.c) return Val::K(a.v * b.v);
@@ -168,7 +171,7 @@ Val mul(const Val& a, const Val& b) {
     if (b.c && b.v == 1.0) return a;
     if (a.c && a.v == -1.0) return neg(b);
     if (b.c && b.v == -1.0) return neg(a);
-    return Val::E("d_mul(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp);
+    return Val::E("d_mul(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp, a.z || b.z);
 }
 
 }  // namespace
@@ -234,8 +237,11 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
             if (s.kind == SK_ONE) is_const[s.out] = false;  // (gmin stays a literal either way)
     for (const StepOp& s : mp.step_ops) kind[s.out] = STEP;
     for (const SrcOp& s : mp.src_ops) kind[s.out] = SRC;
-    for (const MosOp& m : mp.mos_ops)
+    std::set<int> mos_gm;  // value ids of the gate transconductance terms (gd, gg, gs, cst at m.out + 0..3)
+    for (const MosOp& m : mp.mos_ops) {
         for (int t = 0; t < 4; ++t) kind[m.out + t] = MOS;
+        mos_gm.insert(m.out + 1);
+    }
 
     // ---- shared-memory slots: Y first and contiguous (probe scratch), the rest on demand -------------
     int n_slots = 0;
@@ -303,8 +309,9 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
                 if (!prm_slot.count(m.param + t)) prm_slot[m.param + t] = alloc();
     auto val = [&](int v) -> Val {  // per-iteration operand
         if (is_const[v]) return Val::K(const_val[v]);
-        if (kind[v] == MOS)
-            return opt.mos_in_smem ? Val::E(S(mos_slot.at(v)), kLatMos + kLatSmem) : Val::E("m" + std::to_string(v) + "@", kLatMos);
+        if (kind[v] == MOS)  // (gm is exactly zero while the device is off: src/element.cpp:240-247)
+            return opt.mos_in_smem ? Val::E(S(mos_slot.at(v)), kLatMos + kLatSmem, mos_gm.count(v) > 0)
+                                   : Val::E("m" + std::to_string(v) + "@", kLatMos, mos_gm.count(v) > 0);
         return Val::E(S(val_slot.at(v)));
     };
 
@@ -381,7 +388,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
          "        for (int iter = 0; iter < " << C.tran_max_iters << "; ++iter) {\n"
          "            if (__all_sync(0xFFFFFFFFu, ALL(done@))) break;\n"
          "            bool bad@ = degen@;\n"
-         "            unsigned int glo@ = 0xFFFFFFFFu, ghi@ = 0u;\n";
+         "            unsigned int glo@ = 0xFFFFFFFFu, ghi@ = 0u, gacc@ = 0u, pmx@ = 0u;\n";
     // ---- MOSFET linearisation -------------------------------------------------------------------------
     for (const MosOp& op : mp.mos_ops) {
         auto prm = [&](int k) { return opt.mos_in_smem ? S(prm_slot.at(k)) : "PRM(" + std::to_string(k) + ", bb@)"; };
@@ -417,6 +424,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
              "                bad@ = degen@;\n"
              "                glo@ = 0xFFFFFFFFu;\n"
              "                ghi@ = 0u;\n"
+             "                gacc@ = 0u;\n"
+             "                pmx@ = 0u;\n"
              "            }\n";
     }
     const int n_common = n_slots;  // slots below are shared by all variants; each variant parks its LU above
@@ -437,14 +446,23 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     char num[64];
     auto fabs_lit = [&](double v) { return lit(std::fabs(v)); };
     // a / pivot(k): exact rewrites for +-1 pivots, constant folding, otherwise the guarded split division
-    auto divide = [&](const Val& a, int k, const std::string& tmp, const char* ind) -> Val {
+    // true -> divide() emits a division whose guards also judge the pivot rule (tdiv_mul): no explicit comparison needed
+    auto folded_mult = [&](const Val& a, int k) {
+        const Val& d = Dv[k];
+        return opt.fold_guards && !a.z && !(d.c && (d.v == 1.0 || d.v == -1.0)) && !(a.c && d.c);
+    };
+    auto divide = [&](const Val& a, int k, const std::string& tmp, const char* ind, bool mult) -> Val {
         const Val& d = Dv[k];
         if (d.c && d.v == 1.0) return a;
         if (d.c && d.v == -1.0) return neg(a);
         if (a.c && d.c) return Val::K(a.v / d.v);
-        o << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo@, ghi@);\n";
+        if (opt.fold_guards && !a.z)
+            o << ind << "const double " << tmp << " = " << (mult ? "tdiv_mul(" : "tdiv_nz(") << a.e << ", " << d.e << ", "
+              << RDv[k].e << ", gacc@" << (mult ? ", pmx@" : "") << ");\n";
+        else
+            o << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo@, ghi@);\n";
         H.n_lu_divs++;
-        return Val::E(tmp, std::max(a.t, RDv[k].t) + kLatDiv);
+        return Val::E(tmp, std::max(a.t, RDv[k].t) + kLatDiv, a.z);
     };
     struct RowGen {
         int i = 0;
@@ -465,7 +483,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
         if (v.e == name) return;
         o << ind << (R.declared.count(j) ? "" : "double ") << name << " = " << v.e << ";\n";
         R.declared.insert(j);
-        R.row[j] = Val::E(name, v.t);
+        R.row[j] = Val::E(name, v.t, v.z);
     };
     auto emit_assembly = [&](RowGen& R) {
         const int i = R.i;
@@ -487,7 +505,9 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
         // the reference would have picked this row instead of the predicted pivot (solver.hpp:46-56): a larger
         // entry always, an EQUAL one when its scan meets this row before the predicted pivot row (first maximum wins)
         const bool tie_loses = A.before_pivot[k][i];
-        if (a.c && Dv[k].c) {
+        if (folded_mult(a, k)) {
+            // judged on the quotient by tdiv_mul (|f| >= 1 on the high word: never misses, ties included)
+        } else if (a.c && Dv[k].c) {
             if (std::fabs(a.v) > std::fabs(Dv[k].v) || (tie_loses && std::fabs(a.v) == std::fabs(Dv[k].v)))
                 o << ind << "bad@ = true;\n";
         } else {
@@ -495,7 +515,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
               << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")") << ");\n";
         }
         std::snprintf(num, sizeof num, "f%d_%d@", i, k);
-        const Val f = divide(a, k, num, ind);
+        const Val f = divide(a, k, num, ind, true);
         for (int j : A.cols_k[k]) {
             assign(R, j, sub(R.row[j], mul(f, Uv[k].at(j))));
             H.n_elim_updates++;
@@ -529,14 +549,14 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
             } else {
                 const int su = alloc();
                 o << ind << S(su) << " = " << u.e << ";\n";
-                Uv[i][j] = Val::E(S(su), u.t + kLatSmem);
+                Uv[i][j] = Val::E(S(su), u.t + kLatSmem, u.z);
             }
         }
         if (R.row[N].c) {
             Yv[i] = R.row[N];
         } else {
             o << ind << S(Y0 + i) << " = rb" << i << "@;\n";
-            Yv[i] = Val::E(S(Y0 + i), R.row[N].t + kLatSmem);
+            Yv[i] = Val::E(S(Y0 + i), R.row[N].t + kLatSmem, R.row[N].z);
         }
         parked[i] = true;
     };
@@ -588,10 +608,10 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
             H.n_back_terms++;
             if (!s.c && (++t % 3) == 0) {  // keep expressions shallow
                 o << "                const double s" << t << "@ = " << s.e << ";\n";
-                s = Val::E("s" + std::to_string(t) + "@", s.t);
+                s = Val::E("s" + std::to_string(t) + "@", s.t, s.z);
             }
         }
-        const Val q = divide(s, i, "qq@", "                ");
+        const Val q = divide(s, i, "qq@", "                ", false);
         o << "                q" << i << "@ = " << q.e << ";\n";
         // solver.hpp:124-127 zeroes the unknown of a pivot below 1e-15; the pivot check above sends every
         // |pivot| < lu_eps to the generic path, so the test is dead code unless lu_eps was lowered
@@ -615,7 +635,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     H.crit_cycles += 5 * kLatOp + 5 * kLatOp + kLatSqrt;  // damped update + square, 32-leaf tree, sqrt
     // ---- prediction check / per-lane generic redo ------------------------------------------------------------
     if (K > 1)
-        o << "            if (need@) missed@ = bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu);\n"
+        o << "            if (need@) missed@ = bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (pmx@ >= kTdivTOne);\n"
              "            need@ = false;\n"
              "            if (pass == 0 && missed@ && !degen@ && T.miss) {\n"
              "                const int w = (int)T.miss[TPI_SUCC0 + var@] - 1;\n"
@@ -628,7 +648,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
              "            }  // pass\n"
              "            const bool redo@ = missed@;\n";
     else
-    o << "            const bool redo@ = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu)) && !done@;\n";
+    o << "            const bool redo@ = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (pmx@ >= kTdivTOne)) && !done@;\n";
     o << ""
          "            if (__any_sync(0xFFFFFFFFu, ANY(redo@))) {\n"
          "                //@BEGIN\n"
