@@ -522,6 +522,39 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
         }
         assign(R, N, sub(R.row[N], mul(f, Yv[k])));
     };
+    // opaque parking (opt.opaque_park): (slot, value) pairs of the row, flushed by asm blocks that define tok<i>
+    std::vector<std::pair<int, std::string>> park_list;
+    int ldp_uid = 0;
+    auto PK = [&](int slot, int row) {  // read expression of a parked slot
+        return opt.opaque_park ? "ldp<SOFF(" + std::to_string(slot) + ", @R), __LINE__>(sbase, tok" + std::to_string(row) +
+                                     "_v" + std::to_string(v) + "@)"
+                               : S(slot);
+    };
+    auto park = [&](int slot, const std::string& value) {
+        if (opt.opaque_park) park_list.push_back({slot, value});
+        else o << ind << S(slot) << " = " << value << ";\n";
+    };
+    auto park_flush = [&](int row) {
+        if (!opt.opaque_park) return;
+        const std::string tok = "tok" + std::to_string(row) + "_v" + std::to_string(v) + "@";
+        const size_t kChunk = 12;  // (an asm statement takes at most 30 operands)
+        std::string base = "sbase";
+        for (size_t c0 = 0, ci = 0;; c0 += kChunk, ++ci) {
+            const size_t c1 = std::min(park_list.size(), c0 + kChunk);
+            const bool last = c1 >= park_list.size();
+            const std::string out = last ? tok : tok + "c" + std::to_string(ci);
+            o << ind << "unsigned int " << out << ";\n" << ind << "asm volatile(\"";
+            for (size_t e = 0; e < c1 - c0; ++e) o << "st.shared.f64 [%1+%" << (2 * e + 2) << "], %" << (2 * e + 3) << "; ";
+            o << "mov.b32 %0, %1;\" : \"=r\"(" << out << ") : \"r\"(" << base << ")";
+            for (size_t e = c0; e < c1; ++e)
+                o << ", \"n\"(SOFF(" << park_list[e].first << ", @R)), \"d\"(" << park_list[e].second << ")";
+            o << ");\n";
+            base = out;
+            if (last) break;
+        }
+        park_list.clear();
+    };
+    (void)ldp_uid;
     auto emit_park = [&](RowGen& R) {
         const int i = R.i;
         // pivot of this position: singular / non-finite pivots go to the generic path
@@ -536,10 +569,12 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
             // (rcp_seq needs a normal reciprocal: 2^-1021 <= |pivot| <= 2^1021; anything else is redone generically)
             o << ind << "bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(std::max(C.lu_eps, 0x1p-1021)) << " && fabs(" << dn
               << ") <= 0x1p+1021);\n"
-              << ind << S(sd) << " = " << dn << ";\n"
-              << ind << S(srd) << " = rcp_seq(" << dn << ");\n";
-            Dv[i] = Val::E(S(sd), d.t + kLatSmem);
-            RDv[i] = Val::E(S(srd), d.t + kLatRcp + kLatSmem);
+              ;
+            if (opt.opaque_park) o << ind << "const double rd" << i << "@ = rcp_seq(" << dn << ");\n";
+            park(sd, dn);
+            park(srd, opt.opaque_park ? "rd" + std::to_string(i) + "@" : "rcp_seq(" + dn + ")");
+            Dv[i] = Val::E(PK(sd, i), d.t + kLatSmem);
+            RDv[i] = Val::E(PK(srd, i), d.t + kLatRcp + kLatSmem);
             H.n_rcp++;
         }
         for (int j : A.ucols[i]) {
@@ -548,16 +583,17 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
                 Uv[i][j] = u;
             } else {
                 const int su = alloc();
-                o << ind << S(su) << " = " << u.e << ";\n";
-                Uv[i][j] = Val::E(S(su), u.t + kLatSmem, u.z);
+                park(su, u.e);
+                Uv[i][j] = Val::E(PK(su, i), u.t + kLatSmem, u.z);
             }
         }
         if (R.row[N].c) {
             Yv[i] = R.row[N];
         } else {
-            o << ind << S(Y0 + i) << " = rb" << i << "@;\n";
-            Yv[i] = Val::E(S(Y0 + i), R.row[N].t + kLatSmem, R.row[N].z);
+            park(Y0 + i, "rb" + std::to_string(i) + "@");
+            Yv[i] = Val::E(PK(Y0 + i, i), R.row[N].t + kLatSmem, R.row[N].z);
         }
+        park_flush(i);
         parked[i] = true;
     };
     {
@@ -787,6 +823,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
            "#define SPEC_N " << N << "\n"
            "#define SPEC_NV " << mp.n_values << "\n"
            "#define SM(k, r) sm[((k) + (r) * NSLOTS) * TPB + tid]\n"
+           "#define SOFF(k, r) ((((k) + (r) * NSLOTS) * TPB) * 8)\n"
            "#define PRM(k, bb) ld_nohoist(params + (long long)(k) * B + (bb))\n"
            "#define TPI_SUCC0 " << kTpiMissEntries * kTpiMissStride << "\n"
            "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kSmemPerSm / (H.smem_bytes + kCtaReserve)))
@@ -798,6 +835,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
            "              unsigned long long* __restrict__ stats) {\n"
            "    extern __shared__ double sm[];\n"
            "    const int tid = threadIdx.x;\n"
+           "    const unsigned int sbase = (unsigned int)__cvta_generic_to_shared(sm) + 8u * tid;\n"
 
            "    const double dt = T.dt;\n"
            "    const unsigned long long F = 0x" << std::hex << (((unsigned long long)H.hash_hi << 32) | H.hash_lo) << std::dec
