@@ -206,6 +206,7 @@ TpiOptions tpi_options_from_env() {
         opt.mos_branchless = m & 16;
         opt.fold_guards = m & 32;
         opt.opaque_park = m & 64;
+        opt.int_pivot_guard = m & 128;
         opt.replicas = 1 + ((m >> 8) & 3);
         opt.warps_per_cta = (m >> 12) & 7;
         if ((m >> 16) & 15) opt.rows_in_flight = (m >> 16) & 15;

@@ -388,7 +388,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
          "        for (int iter = 0; iter < " << C.tran_max_iters << "; ++iter) {\n"
          "            if (__all_sync(0xFFFFFFFFu, ALL(done@))) break;\n"
          "            bool bad@ = degen@;\n"
-         "            unsigned int glo@ = 0xFFFFFFFFu, ghi@ = 0u, gacc@ = 0u, pmx@ = 0u;\n";
+         "            unsigned int glo@ = 0xFFFFFFFFu, ghi@ = 0u, gacc@ = 0u, pmx@ = 0u, dacc@ = 0u;\n";
     // ---- MOSFET linearisation -------------------------------------------------------------------------
     for (const MosOp& op : mp.mos_ops) {
         auto prm = [&](int k) { return opt.mos_in_smem ? S(prm_slot.at(k)) : "PRM(" + std::to_string(k) + ", bb@)"; };
@@ -426,8 +426,10 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
              "                ghi@ = 0u;\n"
              "                gacc@ = 0u;\n"
              "                pmx@ = 0u;\n"
+             "                dacc@ = 0u;\n"
              "            }\n";
     }
+    unsigned dacc_limit = 0xFFFFFFFFu;  // pivot range accumulator's acceptance limit (fold_guards)
     const int n_common = n_slots;  // slots below are shared by all variants; each variant parks its LU above
     int n_slots_max = n_slots;
     TpiHost H0;  // statistics of variant 0
@@ -567,9 +569,23 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
             const std::string dn = "r" + std::to_string(i) + "_" + std::to_string(i) + "@";
             if (d.c) o << ind << "const double " << dn << " = " << d.e << ";\n";
             // (rcp_seq needs a normal reciprocal: 2^-1021 <= |pivot| <= 2^1021; anything else is redone generically)
-            o << ind << "bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(std::max(C.lu_eps, 0x1p-1021)) << " && fabs(" << dn
-              << ") <= 0x1p+1021);\n"
-              ;
+            if (opt.fold_guards && opt.int_pivot_guard) {
+                // on the high word, conservatively: accept 2^e_lo <= |pivot| < 2^1021 with 2^e_lo the smallest power of
+                // two >= max(lu_eps, 2^-1021) — a pivot between lu_eps and 2^e_lo only costs a generic redo.  One
+                // unsigned accumulator: t = 2*hi - 2*HI(2^e_lo) wraps above the limit for everything too small
+                // (zero and subnormals included) and exceeds it for everything too large, infinities and NaNs included.
+                int e_lo = 0;
+                std::frexp(std::max(C.lu_eps, 0x1p-1021), &e_lo);  // value = m * 2^e_lo, 0.5 <= m < 1  ->  2^e_lo >= value
+                const unsigned hi_lo = (unsigned)(e_lo + 1023) << 20, hi_hi = (unsigned)(1020 + 1023) << 20 | 0xFFFFFu;  // |pivot| < 2^1021
+                char buf[160];
+                std::snprintf(buf, sizeof buf, "dacc@ = max(dacc@, 2u * (unsigned int)__double2hiint(%s) - 0x%xu);  // <= 0x%xu\n",
+                              dn.c_str(), 2u * hi_lo, 2u * (hi_hi - hi_lo) + 1u);
+                o << ind << buf;
+                dacc_limit = 2u * (hi_hi - hi_lo) + 1u;
+            } else {
+                o << ind << "bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(std::max(C.lu_eps, 0x1p-1021)) << " && fabs(" << dn
+                  << ") <= 0x1p+1021);\n";
+            }
             if (opt.opaque_park) o << ind << "const double rd" << i << "@ = rcp_seq(" << dn << ");\n";
             park(sd, dn);
             park(srd, opt.opaque_park ? "rd" + std::to_string(i) + "@" : "rcp_seq(" + dn + ")");
@@ -671,7 +687,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     H.crit_cycles += 5 * kLatOp + 5 * kLatOp + kLatSqrt;  // damped update + square, 32-leaf tree, sqrt
     // ---- prediction check / per-lane generic redo ------------------------------------------------------------
     if (K > 1)
-        o << "            if (need@) missed@ = bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (pmx@ >= kTdivTOne);\n"
+        o << "            if (need@) missed@ = bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (pmx@ >= kTdivTOne) || (dacc@ > DACC_LIMIT);\n"
              "            need@ = false;\n"
              "            if (pass == 0 && missed@ && !degen@ && T.miss) {\n"
              "                const int w = (int)T.miss[TPI_SUCC0 + var@] - 1;\n"
@@ -684,7 +700,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
              "            }  // pass\n"
              "            const bool redo@ = missed@;\n";
     else
-    o << "            const bool redo@ = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (pmx@ >= kTdivTOne)) && !done@;\n";
+    o << "            const bool redo@ = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (pmx@ >= kTdivTOne) || (dacc@ > DACC_LIMIT)) && !done@;\n";
     o << ""
          "            if (__any_sync(0xFFFFFFFFu, ANY(redo@))) {\n"
          "                //@BEGIN\n"
@@ -825,6 +841,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
            "#define SM(k, r) sm[((k) + (r) * NSLOTS) * TPB + tid]\n"
            "#define SOFF(k, r) ((((k) + (r) * NSLOTS) * TPB) * 8)\n"
            "#define PRM(k, bb) ld_nohoist(params + (long long)(k) * B + (bb))\n"
+           "#define DACC_LIMIT 0x" << std::hex << dacc_limit << std::dec << "u\n"
            "#define TPI_SUCC0 " << kTpiMissEntries * kTpiMissStride << "\n"
            "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kSmemPerSm / (H.smem_bytes + kCtaReserve)))
         << ")\n"
