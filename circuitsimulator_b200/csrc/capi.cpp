@@ -1309,7 +1309,7 @@ int csim_dev_harmonics(int64_t n_signals, int32_t n_samples, int64_t ld, const d
                        const double* cos_tab, const double* sin_tab, double* re, double* im, void* stream) {
     if (n_signals <= 0 || n_samples <= 0 || ld < n_samples || !samples || !cos_tab || !sin_tab || !re || !im)
         return fail(CSIM_E_INVALID, "csim_dev_harmonics: bad argument");
-    if (n_harm < 0 || n_harm > kHarmonicsMax) return fail(CSIM_E_UNSUPPORTED, "csim_dev_harmonics: n_harm out of range (0..16)");
+    if (n_harm < 0 || n_harm > kHarmonicsMax) return fail(CSIM_E_UNSUPPORTED, "csim_dev_harmonics: n_harm out of range (0..64)");
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0) return fail(CSIM_E_CUDA, "csim_dev_harmonics: no CUDA device (no CPU fallback)");

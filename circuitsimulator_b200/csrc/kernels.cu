@@ -449,7 +449,7 @@ cudaError_t launch_gauss_seidel(int n, int64_t B, const double* A, const double*
 // of L1/L2, but a load-then-use in the compute loop stalled every row on the L2 latency: ncu long-scoreboard
 // 4.3 per issue), so the compute loop touches shared memory only.  Per signal the order of the definition is
 // untouched.
-static_assert(kHarmonicsMax == 16, "csim_b200.h documents n_harm <= 16");
+static_assert(kHarmonicsMax == 64, "csim_b200.h documents n_harm <= 64");
 constexpr int kHarmSig = 8;     // signals per warp
 constexpr int kHarmGrp = 4;     // harmonics per pass over the samples (H <= 3: one pass = 8 bytes of HBM per sample)
 constexpr int kHarmWarps = 4;   // warps per CTA

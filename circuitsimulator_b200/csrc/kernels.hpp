@@ -59,7 +59,7 @@ constexpr int kGaussSeidelMaxN = 200;  // two iterates of n doubles for 64 syste
 cudaError_t launch_gauss_seidel(int n, int64_t B, const double* A, const double* rhs, double* x, int max_iters,
                                 double tol, int32_t* sweeps, cudaStream_t stream);
 
-constexpr int kHarmonicsMax = 16;
+constexpr int kHarmonicsMax = 64;  // the reference's own card asks for 50 (tests/dbmixer.sp:45 ".hb 100e6 50")
 cudaError_t launch_harmonics(int64_t n_signals, int M, int64_t ld, const double* x, int H, const double* ct,
                              const double* st, double* re, double* im, cudaStream_t stream);
 

@@ -13,6 +13,7 @@
 #include "csim/dcanalysis.hpp"
 #include "csim/solver.hpp"
 #include "csim/lower.hpp"
+#include "csim/montecarlo.hpp"
 #include "csim/sstateanalysis.hpp"
 #include "csim/parser.hpp"
 #include "csim/tanalisis.hpp"
@@ -181,6 +182,49 @@ int csimh_sin_table(double freq, double td, double phi, double dt, int32_t n_ste
         out[s] = std::sin(w * tau + phi);
     }
     return 0;
+}
+
+// `.MC instances [seed [rel]]` card (include/csim/montecarlo.hpp); returns 1 when present
+int csimh_mc_cfg(const csimh_netlist* h, int64_t* instances, uint64_t* seed, double* rel) {
+    if (!h) return -1;
+    if (instances) *instances = h->sim.mc.instances;
+    if (seed) *seed = h->sim.mc.seed;
+    if (rel) *rel = h->sim.mc.rel;
+    return h->sim.mc.enabled ? 1 : 0;
+}
+
+// csim::monteCarloParams: out [P][B] instance-minor, instances [first, first + B) of the batch drawn from `seed`
+int csimh_monte_carlo(const csimh_netlist* h, int64_t B, uint64_t seed, double rel, int64_t first, double* out) {
+    if (!h || !out) return -1;
+    try {
+        const std::vector<double> p = csim::monteCarloParams(h->low, B, seed, rel, first);
+        std::memcpy(out, p.data(), p.size() * sizeof(double));
+        return 0;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return -1;
+    }
+}
+
+// csim::runMonteCarloTransientBatch: the `.MC` card as one batched DC + transient.  Outputs sized by the caller from
+// csimh_mc_cfg (B) and the .TRAN card: x_final [N][B], wave [B][n_probes][n_out], iters_total / hash / status [B].
+// Returns n_out (recorded points per probe) or -1.
+int csimh_run_mc_tran(const csimh_netlist* h, int32_t n_probes, const int32_t* probes, int32_t out_stride,
+                      double* x_final, double* wave, int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status) {
+    if (!h || (n_probes > 0 && !probes)) return -1;
+    try {
+        const std::vector<int32_t> pr(probes, probes + n_probes);
+        const csim::BatchResult R = csim::runMonteCarloTransientBatch(h->ckt, h->sim, pr, out_stride);
+        if (x_final) std::memcpy(x_final, R.x_final.data(), R.x_final.size() * sizeof(double));
+        if (wave) std::memcpy(wave, R.wave.data(), R.wave.size() * sizeof(double));
+        if (iters_total) std::memcpy(iters_total, R.iters_total.data(), R.iters_total.size() * sizeof(int32_t));
+        if (pivot_hash) std::memcpy(pivot_hash, R.pivot_hash.data(), R.pivot_hash.size() * sizeof(uint64_t));
+        if (status) std::memcpy(status, R.status.data(), R.status.size() * sizeof(uint32_t));
+        return R.n_out;
+    } catch (const std::exception& e) {
+        g_herr = e.what();
+        return -1;
+    }
 }
 
 // dcSolveGaussSeidel of the host layer (src/dcanalysis.cpp:251-257) on the nominal circuit; x: [N].

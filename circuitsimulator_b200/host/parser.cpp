@@ -301,6 +301,21 @@ void NetlistParser::card(const Statement& st) {
             cfg.nHarm = std::stoi(t[2]);
             cfg.enabled = true;
             sim.hb = cfg;
+        } else if (head == ".mc") {  // superset card (montecarlo.hpp); the reference reports it as unsupported
+            if (t.size() < 2) {
+                complain(st, "invalid .MC syntax");
+                return;
+            }
+            MonteCarloConfig cfg;
+            cfg.instances = std::stoll(t[1]);
+            if (t.size() >= 3) cfg.seed = std::stoull(t[2]);
+            if (t.size() >= 4) cfg.rel = parseSpiceNumber(t[3]);
+            if (cfg.instances <= 0 || !(cfg.rel >= 0.0)) {
+                complain(st, "invalid .MC syntax");
+                return;
+            }
+            cfg.enabled = true;
+            sim.mc = cfg;
         } else if (head == ".print") {
             printCard(st);
         } else if (head == ".plotnv") {

@@ -166,6 +166,46 @@ class Netlist:
         out[lo:, mask] = self.params[mask] * (1.0 + rel * u[lo:, mask])
         return np.ascontiguousarray(out.T)
 
+    def monte_carlo_host(self, B: int, seed: int, rel: float = 0.05, first: int = 0) -> np.ndarray:
+        """The same batch as monte_carlo(), drawn by the C++ host layer (csim::monteCarloParams: numpy's SeedSequence +
+        PCG64 restated) — what a C++ caller of the `.MC` card gets."""
+        out = np.empty((self.n_params, B), np.float64)
+        L = _hlib()
+        L.csimh_monte_carlo.argtypes = [C.c_void_p, C.c_int64, C.c_uint64, C.c_double, C.c_int64, C.c_void_p]
+        if L.csimh_monte_carlo(C.c_void_p(self._h), int(B), int(seed), float(rel), int(first), out.ctypes.data_as(C.c_void_p)):
+            raise capi.CsimError("csimh_monte_carlo: " + L.csimh_last_error().decode(errors="replace"))
+        return out
+
+    def mc_card(self):
+        """The netlist's `.MC instances [seed [rel]]` card, or None."""
+        n, sd, rel = C.c_int64(), C.c_uint64(), C.c_double()
+        L = _hlib()
+        L.csimh_mc_cfg.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        if L.csimh_mc_cfg(C.c_void_p(self._h), C.byref(n), C.byref(sd), C.byref(rel)) != 1:
+            return None
+        return dict(instances=int(n.value), seed=int(sd.value), rel=float(rel.value))
+
+    def run_mc_card(self, probes=None, out_stride: int = 1) -> dict:
+        """csim::runMonteCarloTransientBatch: the netlist's `.MC` card as one batched DC + full .TRAN (C++ host layer)."""
+        card = self.mc_card()
+        if card is None:
+            raise capi.CsimError("the netlist has no .MC card")
+        B, N = card["instances"], self.n_unknowns
+        probes = np.ascontiguousarray(self.plot_probes if probes is None else probes, np.int32)
+        n_out = self.n_steps // out_stride
+        out = dict(x_final=np.empty((N, B)), wave=np.empty((B, probes.size, max(n_out, 1))), iters_total=np.empty(B, np.int32),
+                   hash=np.empty(B, np.uint64), status=np.empty(B, np.uint32))
+        L = _hlib()
+        L.csimh_run_mc_tran.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32] + [C.c_void_p] * 5
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        rc = L.csimh_run_mc_tran(C.c_void_p(self._h), int(probes.size), vp(probes), int(out_stride), vp(out["x_final"]),
+                                 vp(out["wave"]), vp(out["iters_total"]), vp(out["hash"]), vp(out["status"]))
+        if rc < 0:
+            raise capi.CsimError("csimh_run_mc_tran: " + L.csimh_last_error().decode(errors="replace"))
+        assert rc == n_out or self.tran["tstart"] > 0
+        out["wave"] = out["wave"].reshape(-1)[: B * probes.size * rc].reshape(B, probes.size, rc)
+        return out
+
     def sin_source_sweep(self, source_name: str, va_values, freq_values, n_steps: int, dt: float | None = None,
                          out_stride: int = 1, probes=None):
         """Sweep of one SIN source over amplitude x frequency (BASELINE config 4): instance b = ia*len(freq)+ifr

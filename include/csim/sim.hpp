@@ -122,6 +122,14 @@ struct HbConfig {
     double f0 = 0.0;
     int nHarm = 0;
 };
+// `.MC instances [seed [rel]]` — Monte-Carlo batch card (superset; see montecarlo.hpp).  Not an analysis of its own:
+// it says how many instances the batched transient / DC drivers run.
+struct MonteCarloConfig {
+    bool enabled = false;
+    long long instances = 0;
+    unsigned long long seed = 0;
+    double rel = 0.05;
+};
 struct ProbeSpec {
     ProbeKind kind = ProbeKind::NodeVoltage;
     std::string expr, node1, node2, eleName, elePort;
@@ -138,6 +146,7 @@ public:
     TranConfig tran;
     AcConfig ac;
     HbConfig hb;
+    MonteCarloConfig mc;
     std::vector<PrintCommand> printCommands;
 
     bool hasAnyAnalysis() const { return doOp || !dcSweeps.empty() || tran.enabled || ac.enabled || hb.enabled; }

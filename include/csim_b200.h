@@ -233,7 +233,11 @@ int csim_host_gauss_seidel(int32_t n, int64_t B, const double* A, const double* 
  * Summation order (part of the definition): partial sum l (l = 0..31) adds the samples n = l, l+32, ... in
  * ascending order, every product and sum separately rounded (no FMA); the 32 partial sums are combined
  * pairwise by the xor butterfly with strides 16, 8, 4, 2, 1; then one division by M.
- * re, im: [n_harm+1][n_signals] device.  n_harm <= 16.  The reference has no counterpart: parity unpinned. */
+ * re, im: [n_harm+1][n_signals] device.  n_harm <= 64 (the reference's own card, tests/dbmixer.sp:45, asks for 50).
+ * Harmonics are taken four per pass over the samples.  Cost: 4 separately rounded FP64 operations per sample and
+ * harmonic against 8 bytes per sample and pass, so only n_harm <= 3 (one pass) is HBM-bound; from there on the
+ * bound is the FP64 pipe (no FMA: the definition rounds every product and sum), e.g. 204 operations per sample
+ * at n_harm = 50.  The reference has no counterpart: parity unpinned. */
 #ifndef __CUDACC_RTC__
 int csim_dev_harmonics(int64_t n_signals, int32_t n_samples, int64_t ld, const double* samples, int32_t n_harm,
                        const double* cos_tab, const double* sin_tab, double* re, double* im, void* stream);

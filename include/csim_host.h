@@ -28,6 +28,15 @@ int csimh_elem_name(const csimh_netlist* h, int32_t idx, char* out, int32_t cap)
 int csimh_csv_header(const csimh_netlist* h, char* out, int32_t cap);
 int csimh_tran_cfg(const csimh_netlist* h, double* tstep, double* tstop, double* tstart, int32_t* enabled);
 int csimh_hb_cfg(const csimh_netlist* h, double* f0, int32_t* n_harm, int32_t* enabled);
+/* `.MC instances [seed [rel]]` card (superset of the reference grammar; include/csim/montecarlo.hpp): 1 = present */
+int csimh_mc_cfg(const csimh_netlist* h, int64_t* instances, uint64_t* seed, double* rel);
+/* Monte-Carlo parameters, out [P][B] instance-minor: instances [first, first + B) of the batch that
+ * numpy.random.Generator(PCG64(seed)).uniform(-1, 1, (n, P)) defines (SURVEY.md 8(d) recipe), restated in C++ */
+int csimh_monte_carlo(const csimh_netlist* h, int64_t B, uint64_t seed, double rel, int64_t first, double* out);
+/* The `.MC` card as one batched DC + transient (csim::runMonteCarloTransientBatch); returns the recorded points per
+ * probe (n_out) or -1.  x_final [N][B], wave [B][n_probes][n_out], iters_total / pivot_hash / status [B]; NULL ok. */
+int csimh_run_mc_tran(const csimh_netlist* h, int32_t n_probes, const int32_t* probes, int32_t out_stride,
+                      double* x_final, double* wave, int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status);
 int csimh_plot_probes(const csimh_netlist* h, int32_t* out, int32_t cap);
 int csimh_tabulate_sources(const csimh_netlist* h, double dt, int32_t n_steps, int32_t* mode, int32_t* group,
                            double* table, int32_t* n_groups);

@@ -100,7 +100,17 @@ def test_harmonics_match_definition_and_dft(torch):
     assert_same_bits(re2[:, 1, 2].cpu().numpy(), ore, "ragged re")
     assert_same_bits(im2[:, 1, 2].cpu().numpy(), oim, "ragged im")
     with pytest.raises(capi.CsimError):
-        capi.harmonics(t["wave"], spp, 17)
+        capi.harmonics(t["wave"], spp, 65)
+    # the reference's own card: `.hb 100e6 50` (tests/dbmixer.sp:45) -> 50 harmonics, 13 passes of four
+    re50, im50 = capi.harmonics(t["wave"], spp, 50, tables)
+    torch.cuda.synchronize()
+    re50, im50 = re50.cpu().numpy(), im50.cpu().numpy()
+    assert re50.shape == (51, B, 6)
+    for b, p in ((0, 0), (B - 1, 1)):
+        ore, oim = O.harmonics(wave[b, p, -spp:], 50, *tables)
+        assert_same_bits(re50[:, b, p], ore, "50 harmonics, real parts")
+        assert_same_bits(im50[:, b, p], oim, "50 harmonics, imaginary parts")
+    assert_same_bits(re50[: H + 1], re, "the first harmonics do not depend on how many are asked for")
 
 
 def test_gauss_seidel_batch_bit_exact(torch):
@@ -193,3 +203,22 @@ def test_current_source_and_pulse_pwl_waveforms_in_transient(torch, case, jit):
         assert_same_bits(wave[b].T, ot["wave"], f"instance {b}")
         assert np.array_equal(t["iters_step"][:, b].cpu().numpy(), ot["iters_step"])
         assert np.uint64(t["hash"][b].item() & 0xFFFFFFFFFFFFFFFF) == np.uint64(ot["hash"])
+
+
+def test_monte_carlo_card_runs_the_batch_the_recipe_defines(torch):
+    """Row (f)3: `.MC instances seed rel` through the C++ host layer (csim::runMonteCarloTransientBatch): parameters from
+    the C++ restatement of numpy's PCG64, DC + full .TRAN on the device; every instance against the oracle run with
+    the Python recipe's parameters."""
+    from circuitsimulator_b200.netlist import Netlist
+    g, topo = load_golden("buffer")
+    nl = Netlist(str(g["netlist"]).replace(".end", ".MC 7 20261107 0.05\n.end"))
+    r = nl.run_mc_card(probes=np.arange(nl.n_unknowns, dtype=np.int32))
+    P = O.monte_carlo(topo, 7, 20261107)
+    dt, ns = float(g["dt"]), nl.n_steps
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    for b in range(7):
+        od = O.dc(topo, P[b])
+        ot = O.tran(topo, P[b], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(r["wave"][b].T, ot["wave"], f".MC instance {b}")
+        assert r["hash"][b] == np.uint64(ot["hash"]) and r["iters_total"][b] == ot["total"]
+    assert_same_bits(r["wave"][0].T, g["wave"], "instance 0 is the nominal circuit (golden)")

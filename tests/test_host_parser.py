@@ -115,3 +115,23 @@ M1 d b 0 n 1e-6 .5e-6 2
         assert np.array_equal(getattr(nl, k), getattr(t, k)), k
     assert_same_bits(nl.params, t.params, "params")
     assert nl.node_names == t.node_names and nl.elem_names == t.elem_names
+
+
+def test_monte_carlo_card_and_cpp_generator_equal_numpy():
+    """`.MC instances seed rel` (superset card, include/csim/montecarlo.hpp): the C++ host layer restates numpy's
+    SeedSequence + PCG64 + uniform, so its batch equals the Python recipe's bit for bit — shards
+    (bit_generator.advance) and 64-bit seeds included."""
+    import numpy as np
+    from circuitsimulator_b200.netlist import Netlist
+    from support import load_golden
+    g, _ = load_golden("dbmixer")
+    text = str(g["netlist"]).replace(".end", ".MC 1024 20261104 0.05\n.end")
+    nl = Netlist(text)
+    assert nl.mc_card() == dict(instances=1024, seed=20261104, rel=0.05)
+    assert Netlist(str(g["netlist"])).mc_card() is None
+    for seed, B, first, rel in ((20261104, 300, 0, 0.05), (20261104, 77, 4096, 0.05), (0, 5, 0, 0.1),
+                                (2**63 + 12345, 9, 3, 0.02), (7, 1, 0, 0.05)):
+        a = nl.monte_carlo(B, seed, rel, first)
+        b = nl.monte_carlo_host(B, seed, rel, first)
+        assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), (seed, B, first)
+    assert np.array_equal(nl.monte_carlo_host(4, 1)[:, 0], nl.params)  # global instance 0 is the nominal circuit
