@@ -37,6 +37,8 @@ EXPORTS = [
     "csim_plan_specialize_variants", "csim_plan_generate_source_variants", "csim_dev_selftest_tdiv",
     "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
     "csim_dev_fp64_peak", "csim_dev_lu_factor", "csim_host_lu_factor", "csim_dev_lu_solve_noalloc", "csim_dev_selftest_tdiv_mul",
+    "csim_multi_create", "csim_multi_destroy", "csim_multi_shard", "csim_multi_set_params", "csim_multi_dc", "csim_multi_tran",
+    "csim_multi_last_kernel_ms", "csim_set_last_error",
 ]
 
 
@@ -565,6 +567,82 @@ class Batch:
     @property
     def last_kernel_ms(self) -> float:
         return float(lib().csim_batch_last_kernel_ms(self.handle))
+
+
+class Multi:
+    """csim_multi: one batch of B instances sharded over several GPUs below the C ABI (one host thread, plan, batch
+    and stream per device; contiguous shards).  Host numpy arrays in, host numpy arrays out."""
+
+    def __init__(self, topo_arrays, B: int, devices, consts: Constants | None = None):
+        n_unknowns, n_node_eq, elem_type, elem_flags, elem_nodes, elem_branch, elem_param, n_params = topo_arrays
+        self._keep = [_i32(elem_type), _i32(elem_flags), _i32(np.asarray(elem_nodes).reshape(-1, 4)), _i32(elem_branch),
+                      _i32(elem_param)]
+        ty, fl, nd, br, po = self._keep
+        topo = TopologyC(int(n_unknowns), int(n_node_eq), int(ty.shape[0]), int(n_params), _ip(ty), _ip(fl), _ip(nd),
+                         _ip(br), _ip(po))
+        self.consts = consts or default_constants()
+        self.N, self.P, self.B = int(n_unknowns), int(n_params), int(B)
+        dev = _i32(devices)
+        L = lib()
+        L.csim_multi_create.argtypes = [C.POINTER(TopologyC), C.POINTER(Constants), C.c_int32, C.POINTER(C.c_int32), C.c_int64,
+                                        C.POINTER(C.c_void_p)]
+        L.csim_multi_destroy.argtypes = [C.c_void_p]
+        L.csim_multi_shard.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.csim_multi_set_params.argtypes = [C.c_void_p, C.c_void_p]
+        L.csim_multi_dc.argtypes = [C.c_void_p] + [C.c_void_p] * 4
+        L.csim_multi_tran.argtypes = [C.c_void_p, C.POINTER(TranArgsC)] + [C.c_void_p] * 6
+        L.csim_multi_last_kernel_ms.restype = C.c_float
+        L.csim_multi_last_kernel_ms.argtypes = [C.c_void_p]
+        h = C.c_void_p()
+        _check(L.csim_multi_create(C.byref(topo), C.byref(self.consts), int(dev.size), _ip(dev), int(B), C.byref(h)),
+               "csim_multi_create")
+        self.handle, self.n_shards = h, int(dev.size)
+
+    def close(self):
+        if getattr(self, "handle", None):
+            lib().csim_multi_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def shard(self, rank: int):
+        d, f, c = C.c_int32(), C.c_int64(), C.c_int64()
+        _check(lib().csim_multi_shard(self.handle, rank, C.byref(d), C.byref(f), C.byref(c)), "csim_multi_shard")
+        return int(d.value), int(f.value), int(c.value)
+
+    def set_params(self, params):
+        params = np.ascontiguousarray(params, np.float64)
+        assert params.shape == (self.P, self.B)
+        _check(lib().csim_multi_set_params(self.handle, params.ctypes.data_as(C.c_void_p)), "csim_multi_set_params")
+
+    def dc(self):
+        x = np.empty((self.N, self.B), np.float64)
+        it = np.empty((self.consts.dc_ramp_steps, self.B), np.int32)
+        h = np.empty(self.B, np.uint64)
+        st = np.empty(self.B, np.uint32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+        _check(lib().csim_multi_dc(self.handle, vp(x), vp(it), vp(h), vp(st)), "csim_multi_dc")
+        return dict(x=x, iters=it, hash=h, status=st)
+
+    def tran(self, setup: "TranSetup"):
+        npr, ld = int(setup.probes.size), max(setup.n_out, 1)
+        out = dict(x_dc=np.empty((self.N, self.B)), x_final=np.empty((self.N, self.B)),
+                   wave=np.empty((self.B, npr, ld)), iters_total=np.empty(self.B, np.int32),
+                   hash=np.empty(self.B, np.uint64), status=np.empty(self.B, np.uint32))
+        gb = setup.src_group_b
+        a = setup.args(0, setup.n_steps, setup.table.ctypes.data, gb.ctypes.data if gb is not None else None, ld)
+        vp = lambda a_: a_.ctypes.data_as(C.c_void_p)  # noqa: E731
+        _check(lib().csim_multi_tran(self.handle, C.byref(a), vp(out["x_dc"]), vp(out["x_final"]), vp(out["wave"]),
+                                     vp(out["iters_total"]), vp(out["hash"]), vp(out["status"])), "csim_multi_tran")
+        return out
+
+    @property
+    def last_kernel_ms(self) -> float:
+        return float(lib().csim_multi_last_kernel_ms(self.handle))
 
 
 def fp64_peak(device: int = 0) -> float:

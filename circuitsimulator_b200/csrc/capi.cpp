@@ -519,6 +519,7 @@ cudaError_t tpi_launch(const csim_plan* plan, const DevTran& T, int64_t B, const
 extern "C" {
 
 const char* csim_last_error(void) { return g_err.c_str(); }
+void csim_set_last_error(const char* msg) { g_err = msg ? msg : ""; }  // (multi.cpp reports through the same slot)
 int csim_abi_version(void) { return CSIM_ABI_VERSION; }
 
 void csim_default_constants(csim_constants* c) {

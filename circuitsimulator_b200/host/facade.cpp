@@ -211,10 +211,21 @@ int csimh_monte_carlo(const csimh_netlist* h, int64_t B, uint64_t seed, double r
 // Returns n_out (recorded points per probe) or -1.
 int csimh_run_mc_tran(const csimh_netlist* h, int32_t n_probes, const int32_t* probes, int32_t out_stride,
                       double* x_final, double* wave, int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status) {
-    if (!h || (n_probes > 0 && !probes)) return -1;
+    return csimh_run_mc_tran_devices(h, 0, nullptr, n_probes, probes, out_stride, x_final, wave, iters_total, pivot_hash,
+                                     status);
+}
+
+// ... n_devices > 0: sharded over those CUDA devices (csim::runMonteCarloTransientMultiGpu)
+int csimh_run_mc_tran_devices(const csimh_netlist* h, int32_t n_devices, const int32_t* devices, int32_t n_probes,
+                              const int32_t* probes, int32_t out_stride, double* x_final, double* wave,
+                              int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status) {
+    if (!h || (n_probes > 0 && !probes) || (n_devices > 0 && !devices)) return -1;
     try {
         const std::vector<int32_t> pr(probes, probes + n_probes);
-        const csim::BatchResult R = csim::runMonteCarloTransientBatch(h->ckt, h->sim, pr, out_stride);
+        const csim::BatchResult R =
+            n_devices > 0 ? csim::runMonteCarloTransientMultiGpu(h->ckt, h->sim, pr, out_stride,
+                                                                 std::vector<int32_t>(devices, devices + n_devices))
+                          : csim::runMonteCarloTransientBatch(h->ckt, h->sim, pr, out_stride);
         if (x_final) std::memcpy(x_final, R.x_final.data(), R.x_final.size() * sizeof(double));
         if (wave) std::memcpy(wave, R.wave.data(), R.wave.size() * sizeof(double));
         if (iters_total) std::memcpy(iters_total, R.iters_total.data(), R.iters_total.size() * sizeof(int32_t));

@@ -22,6 +22,10 @@ struct BatchGuard {
     csim_batch* b = nullptr;
     ~BatchGuard() { csim_batch_destroy(b); }
 };
+struct MultiGuard {
+    csim_multi* m = nullptr;
+    ~MultiGuard() { csim_multi_destroy(m); }
+};
 void putSource(const SourceSpec& s, std::vector<double>& out) {
     out.insert(out.end(), {s.dcValue, s.tran.sine.v0, s.tran.sine.va, s.tran.sine.freq, s.tran.sine.td,
                            s.tran.sine.phi});
@@ -215,6 +219,69 @@ BatchResult runTransientAnalysisBackwardEulerBatch(const Circuit& ckt, const Sim
                         R.iters_total.data(), nullptr, R.pivot_hash.data(), R.status.data()))
         raise("csim_batch_tran");
     R.kernel_ms = csim_batch_last_kernel_ms(bg.b);
+    return R;
+}
+
+// The same batch sharded over several GPUs (csim_multi_*: one host thread, plan, batch and stream per device,
+// contiguous shards, every device copies its slice into R's global arrays); bit-identical to the single-device call.
+BatchResult runTransientAnalysisBackwardEulerMultiGpu(const Circuit& ckt, const SimulationConfig& sim,
+                                                   const std::vector<double>& params, int64_t B,
+                                                   const std::vector<int32_t>& probes, int out_stride,
+                                                       const std::vector<int32_t>& devices) {
+    const TranConfig& cfg = sim.tran;
+    if (!cfg.enabled) throw std::runtime_error("Transient analysis is not enabled (.TRAN missing).");
+    if (cfg.tstep <= 0.0 || cfg.tstop <= 0.0)
+        throw std::runtime_error("Invalid .TRAN card: tstep and tstop must be > 0.");
+    Lowered L = lower(ckt);
+    if (static_cast<int64_t>(params.size()) != static_cast<int64_t>(L.n_params) * B)
+        throw std::runtime_error("runTransientAnalysisBackwardEulerBatch: params must hold P*B doubles");
+    const int32_t n_steps = static_cast<int32_t>(std::floor(cfg.tstop / cfg.tstep + 1e-12));  // tanalisis.cpp:238
+    SourceTables S = tabulate_sources(ckt, cfg.tstep, n_steps);
+    // first step whose time passes the reference's "t < tstart -> skip" filter (tanalisis.cpp:209)
+    int32_t first = 0;
+    while (first < n_steps && (first + 1) * cfg.tstep < cfg.tstart) ++first;
+
+    csim_topology t = L.view();
+    if (devices.empty()) throw std::runtime_error("runTransientAnalysisBackwardEulerMultiGpu: no devices");
+    MultiGuard mg;
+    if (csim_multi_create(&t, nullptr, static_cast<int32_t>(devices.size()), devices.data(), B, &mg.m)) raise("csim_multi_create");
+    if (csim_multi_set_params(mg.m, params.data())) raise("csim_multi_set_params");
+
+    BatchResult R;
+    R.B = B;
+    R.n_steps = n_steps;
+    R.n_probes = static_cast<int32_t>(probes.size());
+    if (out_stride < 1) out_stride = 1;
+    R.n_out = n_steps / out_stride - first / out_stride;
+    const std::size_t NB = static_cast<std::size_t>(L.n_unknowns) * B;
+    R.x_dc.resize(NB);
+    R.x_final.resize(NB);
+    R.wave.assign(static_cast<std::size_t>(B) * R.n_probes * (R.n_out > 0 ? R.n_out : 1),
+                  std::numeric_limits<double>::quiet_NaN());
+    R.iters_total.resize(B);
+    R.pivot_hash.resize(B);
+    R.status.resize(B);
+
+    csim_tran_args a;
+    std::memset(&a, 0, sizeof(a));
+    a.dt = cfg.tstep;
+    a.step_begin = 0;
+    a.step_end = n_steps;
+    a.n_groups = S.n_groups;
+    a.table_steps = n_steps;
+    a.src_table = S.table.data();
+    a.src_mode = S.mode.data();
+    a.src_group = S.group.data();
+    a.src_group_b = nullptr;
+    a.n_probes = R.n_probes;
+    a.probes = probes.data();
+    a.out_stride = out_stride;
+    a.out_begin_step = first;
+    a.wave_ld = R.n_out > 0 ? R.n_out : 1;
+    if (csim_multi_tran(mg.m, &a, R.x_dc.data(), R.x_final.data(), R.n_probes ? R.wave.data() : nullptr,
+                        R.iters_total.data(), R.pivot_hash.data(), R.status.data()))
+        raise("csim_multi_tran");
+    R.kernel_ms = csim_multi_last_kernel_ms(mg.m);
     return R;
 }
 

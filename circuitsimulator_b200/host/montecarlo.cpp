@@ -113,4 +113,12 @@ BatchResult runMonteCarloTransientBatch(const Circuit& ckt, const SimulationConf
     return runTransientAnalysisBackwardEulerBatch(ckt, sim, params, sim.mc.instances, probes, out_stride, device);
 }
 
+BatchResult runMonteCarloTransientMultiGpu(const Circuit& ckt, const SimulationConfig& sim, const std::vector<int32_t>& probes,
+                                           int out_stride, const std::vector<int32_t>& devices) {
+    if (!sim.mc.enabled) throw std::runtime_error("runMonteCarloTransientMultiGpu: the netlist has no .MC card");
+    const Lowered L = lower(ckt);
+    const std::vector<double> params = monteCarloParams(L, sim.mc.instances, sim.mc.seed, sim.mc.rel);
+    return runTransientAnalysisBackwardEulerMultiGpu(ckt, sim, params, sim.mc.instances, probes, out_stride, devices);
+}
+
 }  // namespace csim

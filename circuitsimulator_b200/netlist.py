@@ -122,6 +122,11 @@ class Netlist:
         if rc:
             raise capi.CsimError("csimh_set_source_waveform failed")
 
+    def multi(self, B: int, devices) -> "capi.Multi":
+        """csim_multi over `devices` for B instances of this netlist."""
+        return capi.Multi((self.n_unknowns, self.n_node_eq, self.elem_type, self.elem_flags, self.elem_nodes,
+                           self.elem_branch, self.elem_param, self.n_params), B, devices)
+
     def source_tables(self, dt: float | None = None, n_steps: int | None = None):
         """(src_mode, src_group, table[n_groups, n_steps]) tabulated with the host libm."""
         dt = self.tran["tstep"] if dt is None else dt
@@ -185,7 +190,7 @@ class Netlist:
             return None
         return dict(instances=int(n.value), seed=int(sd.value), rel=float(rel.value))
 
-    def run_mc_card(self, probes=None, out_stride: int = 1) -> dict:
+    def run_mc_card(self, probes=None, out_stride: int = 1, devices=None) -> dict:
         """csim::runMonteCarloTransientBatch: the netlist's `.MC` card as one batched DC + full .TRAN (C++ host layer)."""
         card = self.mc_card()
         if card is None:
@@ -196,10 +201,12 @@ class Netlist:
         out = dict(x_final=np.empty((N, B)), wave=np.empty((B, probes.size, max(n_out, 1))), iters_total=np.empty(B, np.int32),
                    hash=np.empty(B, np.uint64), status=np.empty(B, np.uint32))
         L = _hlib()
-        L.csimh_run_mc_tran.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32] + [C.c_void_p] * 5
+        L.csimh_run_mc_tran_devices.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32] + [C.c_void_p] * 5
         vp = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
-        rc = L.csimh_run_mc_tran(C.c_void_p(self._h), int(probes.size), vp(probes), int(out_stride), vp(out["x_final"]),
-                                 vp(out["wave"]), vp(out["iters_total"]), vp(out["hash"]), vp(out["status"]))
+        dev = np.ascontiguousarray(devices if devices is not None else [], np.int32)
+        rc = L.csimh_run_mc_tran_devices(C.c_void_p(self._h), int(dev.size), vp(dev) if dev.size else None, int(probes.size),
+                                         vp(probes), int(out_stride), vp(out["x_final"]), vp(out["wave"]),
+                                         vp(out["iters_total"]), vp(out["hash"]), vp(out["status"]))
         if rc < 0:
             raise capi.CsimError("csimh_run_mc_tran: " + L.csimh_last_error().decode(errors="replace"))
         assert rc == n_out or self.tran["tstart"] > 0

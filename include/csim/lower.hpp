@@ -55,6 +55,12 @@ BatchResult runTransientAnalysisBackwardEulerBatch(const Circuit& ckt, const Sim
                                                    const std::vector<double>& params, int64_t B,
                                                    const std::vector<int32_t>& probes, int out_stride = 1,
                                                    int device = 0);
+// The same over several GPUs of one box: contiguous shards of the batch, one host thread + stream per device
+// (csim_multi_*, include/csim_b200.h); `devices` lists CUDA device ordinals.  Results equal the single-device call's.
+BatchResult runTransientAnalysisBackwardEulerMultiGpu(const Circuit& ckt, const SimulationConfig& sim,
+                                                      const std::vector<double>& params, int64_t B,
+                                                      const std::vector<int32_t>& probes, int out_stride,
+                                                      const std::vector<int32_t>& devices);
 // DC operating points only: returns x [N][B].
 std::vector<double> dcSolveBatch(const Circuit& ckt, const std::vector<double>& params, int64_t B, int device = 0);
 

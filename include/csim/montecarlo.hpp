@@ -35,5 +35,8 @@ std::vector<double> monteCarloParams(const Lowered& L, int64_t B, uint64_t seed,
 // runTransientAnalysisBackwardEulerBatch.  Throws std::runtime_error when the card is absent.
 BatchResult runMonteCarloTransientBatch(const Circuit& ckt, const SimulationConfig& sim, const std::vector<int32_t>& probes,
                                         int out_stride = 1, int device = 0);
+// ... sharded over several GPUs (runTransientAnalysisBackwardEulerMultiGpu)
+BatchResult runMonteCarloTransientMultiGpu(const Circuit& ckt, const SimulationConfig& sim, const std::vector<int32_t>& probes,
+                                           int out_stride, const std::vector<int32_t>& devices);
 
 }  // namespace csim

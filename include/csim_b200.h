@@ -442,6 +442,29 @@ int csim_host_stamp_csr(const csim_plan* plan, int mode, int64_t B, const double
 int csim_host_lu_solve(int32_t n, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
                        int32_t* singular, double lu_eps);
 #endif
+/* ---- one batch over several GPUs of one box ------------------------------------------------------------ *
+ * SURVEY.md 8(b) "Threading" / 8(e): the reference is single-threaded and has no counterpart; its CPU baseline runs
+ * one instance per host core, this runs one contiguous shard of the batch per GPU.  B instances are split into
+ * n_devices contiguous shards (remainder to the low ranks: csim_multi_shard tells which); every device gets its own
+ * plan, batch and stream, every call below runs one host thread per device, there is no data-path collective and
+ * the "final gather" is each device copying its slice into the caller's host buffers.  devices == NULL: 0..n-1; a
+ * device may be listed more than once (two shards share it).  All arrays are the GLOBAL host arrays of
+ * csim_batch_* ([K][B] instance-minor, wave [B][n_probes][wave_ld]); per-step Newton counts are not returned.
+ * Results are bit-identical to one csim_batch over all B instances (instances never interact).           */
+typedef struct csim_multi csim_multi;
+#ifndef __CUDACC_RTC__
+int csim_multi_create(const csim_topology* topo, const csim_constants* consts, int32_t n_devices, const int32_t* devices,
+                      int64_t B, csim_multi** out);
+void csim_multi_destroy(csim_multi* m);
+int csim_multi_shard(const csim_multi* m, int32_t rank, int32_t* device, int64_t* first, int64_t* count);
+int csim_multi_set_params(csim_multi* m, const double* params /*[P][B] host*/);
+int csim_multi_dc(csim_multi* m, double* x, int32_t* iters, uint64_t* pivot_hash, uint32_t* status);
+int csim_multi_tran(csim_multi* m, const csim_tran_args* args, double* x_dc, double* x_final, double* wave,
+                    int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status);
+float csim_multi_last_kernel_ms(const csim_multi* m); /* slowest device of the last call */
+void csim_set_last_error(const char* msg);            /* internal: lets the multi-GPU layer report through csim_last_error() */
+#endif
+
 /* Milliseconds of the kernels of the last csim_batch_* call, measured with CUDA
  * events on the batch's stream (copies excluded).                               */
 #ifndef __CUDACC_RTC__

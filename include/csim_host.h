@@ -37,6 +37,9 @@ int csimh_monte_carlo(const csimh_netlist* h, int64_t B, uint64_t seed, double r
  * probe (n_out) or -1.  x_final [N][B], wave [B][n_probes][n_out], iters_total / pivot_hash / status [B]; NULL ok. */
 int csimh_run_mc_tran(const csimh_netlist* h, int32_t n_probes, const int32_t* probes, int32_t out_stride,
                       double* x_final, double* wave, int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status);
+int csimh_run_mc_tran_devices(const csimh_netlist* h, int32_t n_devices, const int32_t* devices, int32_t n_probes,
+                              const int32_t* probes, int32_t out_stride, double* x_final, double* wave,
+                              int32_t* iters_total, uint64_t* pivot_hash, uint32_t* status);
 int csimh_plot_probes(const csimh_netlist* h, int32_t* out, int32_t cap);
 int csimh_tabulate_sources(const csimh_netlist* h, double dt, int32_t n_steps, int32_t* mode, int32_t* group,
                            double* table, int32_t* n_groups);
