@@ -61,7 +61,7 @@ def test_cpp_host_layer_multi_gpu_driver(torch):
     """runTransientAnalysisBackwardEulerMultiGpu (through the `.MC` card's facade) == the single-device driver."""
     from circuitsimulator_b200.netlist import Netlist
     g, _ = load_golden("buffer")
-    nl = Netlist(str(g["netlist"]).replace(".end", ".MC 11 5 0.05\n.end"))
+    nl = Netlist(str(g["netlist"]) + "\n.MC 11 5 0.05\n")
     probes = np.arange(nl.n_unknowns, dtype=np.int32)
     ndev = torch.cuda.device_count()
     one = nl.run_mc_card(probes=probes)

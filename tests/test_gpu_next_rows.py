@@ -211,7 +211,7 @@ def test_monte_carlo_card_runs_the_batch_the_recipe_defines(torch):
     the Python recipe's parameters."""
     from circuitsimulator_b200.netlist import Netlist
     g, topo = load_golden("buffer")
-    nl = Netlist(str(g["netlist"]).replace(".end", ".MC 7 20261107 0.05\n.end"))
+    nl = Netlist(str(g["netlist"]) + "\n.MC 7 20261107 0.05\n")
     r = nl.run_mc_card(probes=np.arange(nl.n_unknowns, dtype=np.int32))
     P = O.monte_carlo(topo, 7, 20261107)
     dt, ns = float(g["dt"]), nl.n_steps
