@@ -38,7 +38,7 @@ EXPORTS = [
     "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
     "csim_dev_fp64_peak", "csim_dev_lu_factor", "csim_host_lu_factor", "csim_dev_lu_solve_noalloc", "csim_dev_selftest_tdiv_mul",
     "csim_multi_create", "csim_multi_destroy", "csim_multi_shard", "csim_multi_set_params", "csim_multi_dc", "csim_multi_tran",
-    "csim_multi_last_kernel_ms", "csim_set_last_error",
+    "csim_multi_last_kernel_ms", "csim_set_last_error", "csim_plan_specialize_dc_variants", "csim_plan_dc_spec_info",
 ]
 
 
@@ -223,6 +223,22 @@ class Plan:
         _check(lib().csim_plan_spec_info(self.handle, C.byref(act), _ip(perm), C.byref(fb), C.byref(sv), log, len(log)),
                "csim_plan_spec_info")
         return dict(active=bool(act.value), kind=int(act.value), perm=perm, fallback_solves=int(fb.value), solves=int(sv.value),
+                    log=log.value.decode(errors="replace"))
+
+    def specialize_dc_variants(self, perms):
+        """Thread-per-instance DC kernel with the given predicted permutations, perms[n_variants][N]."""
+        perms = np.ascontiguousarray(perms, np.int32).reshape(-1, self.n_unknowns)
+        lib().csim_plan_specialize_dc_variants.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32)]
+        _check(lib().csim_plan_specialize_dc_variants(self.handle, perms.shape[0], _ip(perms)), "csim_plan_specialize_dc_variants")
+
+    def dc_spec_info(self):
+        act, nv, fb, sv = C.c_int32(), C.c_int32(), C.c_uint64(), C.c_uint64()
+        log = C.create_string_buffer(1 << 14)
+        lib().csim_plan_dc_spec_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_uint64),
+                                                 C.POINTER(C.c_uint64), C.c_char_p, C.c_int32]
+        _check(lib().csim_plan_dc_spec_info(self.handle, C.byref(act), C.byref(nv), C.byref(fb), C.byref(sv), log, len(log)),
+               "csim_plan_dc_spec_info")
+        return dict(active=bool(act.value), n_variants=int(nv.value), fallback_solves=int(fb.value), solves=int(sv.value),
                     log=log.value.decode(errors="replace"))
 
     def spec_source(self) -> str:

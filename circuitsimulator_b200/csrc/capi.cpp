@@ -105,6 +105,8 @@ struct csim_plan {
     mutable SpecState spec;
     mutable StampSpecState stamp_spec[2];
     mutable TpiState tpi;
+    mutable TpiState tpi_dc;      // thread-per-instance DC kernel (csim_dc_tpi): same machinery, own variants and statistics
+    mutable bool dc_tried = false;
     int force_big = 0;  // 0: by size; 1: large path (dense kernels); 2: large path (sparse-skipping warp kernels)
 };
 
@@ -217,22 +219,22 @@ TpiOptions tpi_options_from_env() {
 // Generates, compiles and loads one variant of the thread-per-instance kernel specialised to `perm`.
 // warps_per_cta: 1, or 0 = the CTA width that packs most warps into an SM's shared memory.
 int tpi_build_variant(const csim_plan* plan, const std::vector<std::vector<int32_t>>& perms, int warps_per_cta,
-                      TpiHost& host, JitKernel& k, int& warps_per_sm, std::string& log) {
+                      TpiHost& host, JitKernel& k, int& warps_per_sm, std::string& log, bool dc = false) {
     jit_unload(k);
     TpiOptions opt = tpi_options_from_env();
     if (opt.warps_per_cta == 0) opt.warps_per_cta = warps_per_cta;
     try {
-        host = generate_tran_tpi(plan->host, perms, opt);
+        host = dc ? generate_dc_tpi(plan->host, perms, opt) : generate_tran_tpi(plan->host, perms, opt);
     } catch (const std::exception& e) {
         log = e.what();
         return fail(CSIM_E_UNSUPPORTED, log);
     }
     std::vector<char> cubin;
-    if (!jit_compile(host.source, "csim_tran_tpi.cu", jit_library_dir() + "/csrc", cubin, log)) {
+    if (!jit_compile(host.source, dc ? "csim_dc_tpi.cu" : "csim_tran_tpi.cu", jit_library_dir() + "/csrc", cubin, log)) {
         log = "NVRTC: " + log;
         return fail(CSIM_E_CUDA, log);
     }
-    CU(jit_load(cubin, "csim_tran_tpi", k));
+    CU(jit_load(cubin, dc ? "csim_dc_tpi" : "csim_tran_tpi", k));
     CU(cudaKernelSetAttributeForDevice(k.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)host.smem_bytes,
                                        plan->device));
     int ctas = 0;
@@ -242,12 +244,12 @@ int tpi_build_variant(const csim_plan* plan, const std::vector<std::vector<int32
     return CSIM_OK;
 }
 
-int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& perms);
+int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& perms, bool dc = false);
 int tpi_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     return tpi_build(plan, std::vector<std::vector<int32_t>>{perm});
 }
-int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& perms) {
-    TpiState& tp = plan->tpi;
+int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& perms, bool dc) {
+    TpiState& tp = dc ? plan->tpi_dc : plan->tpi;
     tp.ready = false;
     tp.wide_tried = tp.wide_ready = false;
     cudaDeviceSynchronize();  // see spec_build: running launches of the old kernels finish before they are unloaded
@@ -256,7 +258,7 @@ int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& pe
     if (tp.d_miss) cudaFree(tp.d_miss);
     tp.d_stats = tp.d_miss = nullptr;
     std::string log;
-    const int rc = tpi_build_variant(plan, perms, 1, tp.host, tp.k, tp.warps_per_sm, log);
+    const int rc = tpi_build_variant(plan, perms, 1, tp.host, tp.k, tp.warps_per_sm, log, dc);
     if (rc) {
         tp.log = log;
         return rc;
@@ -266,7 +268,7 @@ int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& pe
     CU(cudaMemset(tp.d_stats, 0, 2 * sizeof(unsigned long long)));
     CU(cudaMalloc((void**)&tp.d_miss, sizeof(unsigned long long) * kTpiMissWords));
     CU(cudaMemset(tp.d_miss, 0, sizeof(unsigned long long) * kTpiMissWords));
-    tp.log = "thread-per-instance: " + std::to_string(tp.host.perms.size()) + " predicted permutation(s), " +
+    tp.log = std::string(dc ? "thread-per-instance DC: " : "thread-per-instance: ") + std::to_string(tp.host.perms.size()) + " predicted permutation(s), " +
              std::to_string(tp.host.n_slots) + " shared doubles per instance, " +
              std::to_string(tp.host.replicas) + " instance(s) per thread, " + std::to_string(tp.host.threads) +
              " threads per CTA, " + std::to_string(tp.warps_per_sm) + " warps resident per SM; per Newton iteration: " +
@@ -424,6 +426,108 @@ int spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const
     if (want == 3 && tpi_build(plan, perm) == CSIM_OK) return sp.kind = 3;
     if (spec_build(plan, perm) == CSIM_OK) return sp.kind = 2;
     return 0;
+}
+
+// ---- thread-per-instance DC kernel (csim_dc_tpi) ------------------------------------------------------------------
+// Pivot order of instance 0's FIRST DC solve (x = 0, first ramp step, base gmin): a prediction to start from; the
+// ramp then walks through the circuit's operating regions and the redo log teaches the other orders.
+int dc_pilot(const csim_plan* plan, int64_t B, const double* d_params, cudaStream_t stream, std::vector<int32_t>& perm) {
+    const int N = plan->host.N, P = plan->host.n_params;
+    const ModeProgram& mp = plan->host.mode[CSIM_MODE_DC];
+    const csim_constants& c = plan->host.consts;
+    std::vector<double> p(P > 0 ? P : 1), x(N, 0.0);
+    CU(cudaStreamSynchronize(stream));
+    if (P > 0) CU(cudaMemcpy2D(p.data(), sizeof(double), d_params, sizeof(double) * B, sizeof(double), P, cudaMemcpyDeviceToHost));
+    const double scale = 1.0 / (double)(c.dc_ramp_steps > 0 ? c.dc_ramp_steps : 1);
+    const double gmin = c.gmin_high_base * (1.0 - scale) + c.gmin_low_base * scale;
+    std::vector<double> vals(mp.colidx.size()), rhs(N);
+    g_generic_stamp_only = true;
+    int rc = csim_host_stamp_csr(plan, CSIM_MODE_DC, 1, p.data(), x.data(), nullptr, nullptr, 0.0, scale, gmin, vals.data(),
+                                 rhs.data());
+    g_generic_stamp_only = false;
+    if (rc) return rc;
+    std::vector<double> A((size_t)N * N, 0.0), sol(N);
+    for (int i = 0; i < N; ++i)
+        for (int k = mp.rowptr[i]; k < mp.rowptr[i + 1]; ++k) A[(size_t)i * N + mp.colidx[k]] = vals[k];
+    perm.assign(N, 0);
+    int32_t singular = 0;
+    rc = csim_host_lu_solve(N, 1, A.data(), rhs.data(), sol.data(), perm.data(), &singular, c.lu_eps);
+    if (rc) return rc;
+    if (singular) return fail(CSIM_E_UNSUPPORTED, "DC pilot factorisation is singular");
+    return CSIM_OK;
+}
+
+// true -> launch csim_dc_tpi (built on first use; between launches one more predicted permutation is added while
+// more than kTpiAdaptMissRate of the solves miss, the rule of the transient kernel).  Caller holds spec.mu.
+bool dc_prepare(const csim_plan* plan, int64_t B, const double* d_params, cudaStream_t stream) {
+    SpecState& sp = plan->spec;
+    TpiState& tp = plan->tpi_dc;
+    if (sp.mode == 0 || sp.mode == 2 || !plan->host.has_mos) return false;
+    if (const char* env = std::getenv("CSIM_JIT"))
+        if (env[0] == '0' || env[0] == '2') return false;
+    if (const char* env = std::getenv("CSIM_DC_TPI"))
+        if (env[0] == '0') return false;
+    if (!plan->dc_tried) {
+        plan->dc_tried = true;
+        if (!spec_unsupported_reason(plan->host).empty()) return false;
+        std::vector<int32_t> perm;
+        if (dc_pilot(plan, B, d_params, stream, perm) != CSIM_OK) {
+            tp.log = std::string("DC pilot failed: ") + csim_last_error();
+            return false;
+        }
+        if (tpi_build(plan, std::vector<std::vector<int32_t>>{perm}, true) != CSIM_OK) return false;
+        return true;
+    }
+    if (!tp.ready) return false;
+    unsigned long long st[2] = {0, 0};
+    cudaStreamSynchronize(stream);
+    const bool have = tp.d_stats && cudaMemcpy(st, tp.d_stats, sizeof(st), cudaMemcpyDeviceToHost) == cudaSuccess &&
+                      st[1] >= kTpiMinSolves;
+    if (have && (double)st[0] > kTpiAdaptMissRate * (double)st[1] && tp.d_miss && (int)tp.host.perms.size() < kTpiMaxVariants) {
+        std::vector<unsigned long long> tab((size_t)kTpiMissEntries * kTpiMissStride, 0);
+        int best = -1;
+        if (cudaMemcpy(tab.data(), tp.d_miss, tab.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess)
+            for (int e = 0; e < kTpiMissEntries; ++e) {
+                const unsigned long long hsh = tab[(size_t)e * kTpiMissStride], cnt = tab[(size_t)e * kTpiMissStride + 1];
+                if (!hsh || std::find(tp.host.hashes.begin(), tp.host.hashes.end(), hsh) != tp.host.hashes.end()) continue;
+                if (best < 0 || cnt > tab[(size_t)best * kTpiMissStride + 1]) best = e;
+            }
+        if (best >= 0 && tab[(size_t)best * kTpiMissStride + 1] * 4 >= st[0] / 10) {
+            std::vector<std::vector<int32_t>> perms = tp.host.perms;
+            std::vector<int32_t> np(plan->host.N);
+            for (int i = 0; i < plan->host.N; ++i) np[i] = (int32_t)tab[(size_t)best * kTpiMissStride + 2 + i];
+            perms.push_back(np);
+            const std::vector<std::vector<int32_t>> old = tp.host.perms;
+            const std::string hist = tp.history;
+            tp.history += "\n" + std::to_string(st[0]) + " of " + std::to_string(st[1]) +
+                          " DC solves missed the predicted pivot order -> variant " + std::to_string(perms.size() - 1) +
+                          " added (met " + std::to_string(tab[(size_t)best * kTpiMissStride + 1]) + " times)";
+            if (tpi_build(plan, perms, true) != CSIM_OK) {
+                tp.history = hist;
+                if (tpi_build(plan, old, true) != CSIM_OK) return false;
+            }
+        }
+    }
+    return tp.ready;
+}
+
+cudaError_t dc_tpi_launch(const csim_plan* plan, int64_t B, const double* params, double* x, int32_t* iters,
+                          uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream) {
+    TpiState& tp = plan->tpi_dc;
+    DevPlan P = plan->dev;
+    DevTran Tc{};
+    Tc.miss = tp.d_miss;
+    long long Bll = B;
+    double* wave = nullptr;
+    uint8_t* iters_step = nullptr;
+    double* scratch = nullptr;
+    unsigned long long* stats = tp.d_stats;
+    void* args[] = {&P, &Tc, &Bll, &params, &x, &wave, &iters, &iters_step, &pivot_hash, &status, &scratch, &stats};
+    const TpiHost& H = tp.host;
+    const int64_t per_cta = (int64_t)H.threads * H.replicas;
+    const unsigned blocks = (unsigned)((B + per_cta - 1) / per_cta);
+    return cudaLaunchKernel(reinterpret_cast<const void*>(tp.k.kernel), dim3(blocks), dim3(H.threads), args, H.smem_bytes,
+                            stream);
 }
 
 cudaError_t spec_launch(const csim_plan* plan, const DevTran& T, int64_t B, const double* params, double* x,
@@ -643,6 +747,9 @@ void csim_plan_destroy(csim_plan* plan) {
         jit_unload(plan->tpi.k_wide);
         if (plan->tpi.d_stats) cudaFree(plan->tpi.d_stats);
         if (plan->tpi.d_miss) cudaFree(plan->tpi.d_miss);
+        jit_unload(plan->tpi_dc.k);
+        if (plan->tpi_dc.d_stats) cudaFree(plan->tpi_dc.d_stats);
+        if (plan->tpi_dc.d_miss) cudaFree(plan->tpi_dc.d_miss);
         jit_unload(plan->stamp_spec[0].k);
         jit_unload(plan->stamp_spec[1].k);
     }
@@ -766,7 +873,14 @@ int csim_dev_dc(const csim_plan* plan, int64_t B, const double* params, double* 
     if (use_big(plan) && use_dense(plan))
         CU(launch_dc_dense(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
     else if (use_big(plan)) CU(launch_dc_big(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
-    else CU(launch_dc(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
+    else {
+        // (kernel choice and launch under the plan's lock, as in csim_dev_tran)
+        std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
+        if (dc_prepare(plan, B, params, (cudaStream_t)stream))
+            CU(dc_tpi_launch(plan, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
+        else
+            CU(launch_dc(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
+    }
     return CSIM_OK;
 }
 
@@ -1330,6 +1444,8 @@ int csim_plan_jit_mode(csim_plan* plan, int mode) {
     if (mode != plan->spec.mode) {
         plan->spec.tried = false;
         plan->spec.kind = 0;
+        plan->dc_tried = false;
+        plan->tpi_dc.ready = false;
     }
     plan->spec.mode = mode;
     return CSIM_OK;
@@ -1369,6 +1485,39 @@ int csim_plan_specialize_variants(csim_plan* plan, int32_t n_variants, const int
     rc = tpi_build(plan, pv);
     if (rc == CSIM_OK) sp.kind = 3;
     return rc;
+}
+
+int csim_plan_specialize_dc_variants(csim_plan* plan, int32_t n_variants, const int32_t* perms) {
+    int rc = need_device(plan, "csim_plan_specialize_dc_variants");
+    if (rc) return rc;
+    if (!perms || n_variants < 1 || n_variants > kTpiMaxVariants)
+        return fail(CSIM_E_INVALID, "csim_plan_specialize_dc_variants: 1..8 permutations expected");
+    std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
+    if (plan->spec.mode == 0 || plan->spec.mode == 2) plan->spec.mode = 1;
+    const int N = plan->host.N;
+    std::vector<std::vector<int32_t>> pv;
+    for (int v = 0; v < n_variants; ++v) pv.emplace_back(perms + (size_t)v * N, perms + (size_t)(v + 1) * N);
+    plan->dc_tried = true;
+    return tpi_build(plan, pv, true);
+}
+
+int csim_plan_dc_spec_info(const csim_plan* plan, int32_t* active, int32_t* n_variants, uint64_t* fallback_solves,
+                           uint64_t* solves, char* log, int32_t log_cap) {
+    if (!plan) return fail(CSIM_E_INVALID, "csim_plan_dc_spec_info: null plan");
+    std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
+    const TpiState& tp = plan->tpi_dc;
+    if (active) *active = tp.ready ? 1 : 0;
+    if (n_variants) *n_variants = tp.ready ? (int32_t)tp.host.perms.size() : 0;
+    unsigned long long st[2] = {0, 0};
+    if (plan->device >= 0 && tp.ready && tp.d_stats) {
+        cudaSetDevice(plan->device);
+        cudaDeviceSynchronize();
+        cudaMemcpy(st, tp.d_stats, sizeof(st), cudaMemcpyDeviceToHost);
+    }
+    if (fallback_solves) *fallback_solves = st[0];
+    if (solves) *solves = st[1];
+    if (log && log_cap > 0) std::snprintf(log, (size_t)log_cap, "%s", tp.log.c_str());
+    return CSIM_OK;
 }
 
 int csim_plan_generate_source_variants(const csim_plan* plan, int32_t n_variants, const int32_t* perms, char* out,
@@ -1461,9 +1610,11 @@ int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* 
 int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_t* perm, char* out, int32_t cap) {
     if (!plan || !perm) return fail(CSIM_E_INVALID, "csim_plan_generate_source_kind: null argument");
     if (kind == 2) return csim_plan_generate_source(plan, perm, out, cap);
-    if (kind != 3) return fail(CSIM_E_INVALID, "csim_plan_generate_source_kind: kind must be 2 or 3");
+    if (kind != 3 && kind != 4) return fail(CSIM_E_INVALID, "csim_plan_generate_source_kind: kind must be 2, 3 or 4");
     try {
-        TpiHost th = generate_tran_tpi(plan->host, std::vector<int32_t>(perm, perm + plan->host.N), tpi_options_from_env());
+        const std::vector<std::vector<int32_t>> pv{std::vector<int32_t>(perm, perm + plan->host.N)};
+        TpiHost th = kind == 4 ? generate_dc_tpi(plan->host, pv, tpi_options_from_env())
+                               : generate_tran_tpi(plan->host, pv, tpi_options_from_env());
         if (out && cap > 0) std::snprintf(out, (size_t)cap, "%s", th.source.c_str());
         return (int)th.source.size();
     } catch (const std::exception& e) {

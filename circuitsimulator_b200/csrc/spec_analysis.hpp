@@ -12,7 +12,7 @@ struct Term {
     bool sub;
 };
 
-// TRAN assembly + LU of one topology under one (predicted) pivot permutation.  "Position" i holds
+// Assembly (TRAN by default, or DC) + LU of one topology under one (predicted) pivot permutation.  "Position" i holds
 // original row perm[i]; columns keep their original numbering.
 struct Analysis {
     int N = 0;
@@ -33,6 +33,8 @@ struct Analysis {
 };
 
 // Throws std::runtime_error when perm is not a permutation of 0..N-1.
-Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm);
+// mode CSIM_MODE_DC: the gmin contribution is treated as iterate-dependent (the convergence controller changes it
+// between Newton iterations, src/dcanalysis.cpp:268-307).
+Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm, int mode = CSIM_MODE_TRAN);
 
 }  // namespace csim

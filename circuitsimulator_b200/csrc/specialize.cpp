@@ -19,8 +19,8 @@ std::string spec_unsupported_reason(const HostPlan& hp) {
     return "";
 }
 
-Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm) {
-    const ModeProgram& mp = hp.mode[CSIM_MODE_TRAN];
+Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm, int mode) {
+    const ModeProgram& mp = hp.mode[mode];
     Analysis A;
     const int N = A.N = hp.N;
     if ((int)perm.size() != N) throw std::runtime_error("specialize: permutation has the wrong length");
@@ -33,6 +33,9 @@ Analysis analyse(const HostPlan& hp, const std::vector<int32_t>& perm) {
     std::vector<bool> dynamic(mp.n_values, false);  // values that change with the Newton iterate
     for (const MosOp& m : mp.mos_ops)
         for (int t = 0; t < 4; ++t) dynamic[m.out + t] = true;
+    if (mode == CSIM_MODE_DC)
+        for (const StaticOp& so : mp.static_ops)
+            if (so.kind == SK_GMIN) dynamic[so.out] = true;
 
     A.slot.assign(N, std::vector<std::vector<Term>>(N + 1));
     for (const Contribution& c : mp.contribs) {

@@ -72,6 +72,10 @@ struct TpiOptions {
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt = TpiOptions());
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms,
                           const TpiOptions& opt = TpiOptions());
+// The same generator for the DC operating point (dcSolveNewtonLU, src/dcanalysis.cpp:95-163): entry csim_dc_tpi.
+// Source ramp and ConvController on the device per lane, gmin a per-lane variable, x starts at zero.
+TpiHost generate_dc_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms,
+                        const TpiOptions& opt = TpiOptions());
 
 // Device-side log of the permutations the generic redo path met (tpi_generic_solve): kTpiMissEntries entries of
 // kTpiMissStride uint64 = { pivot-hash contribution (0 = free), count, perm[0..31] }.

@@ -186,15 +186,28 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, 
 // permutation if there is one.  Circuits whose pivot order depends on the operating region (buffer.sp while
 // its stages switch) stay on straight-line code that way; lanes of one warp on different variants execute
 // the bodies one after the other.
+namespace {
+TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms, const TpiOptions& opt, int mode);
+}
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms, const TpiOptions& opt) {
+    return generate_tpi(hp, perms, opt, CSIM_MODE_TRAN);
+}
+TpiHost generate_dc_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms, const TpiOptions& opt) {
+    if (!hp.has_mos) throw std::runtime_error("specialize: linear circuits take the direct DC solve");
+    return generate_tpi(hp, perms, opt, CSIM_MODE_DC);
+}
+
+namespace {
+TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms, const TpiOptions& opt, int mode) {
+    const bool DC = mode == CSIM_MODE_DC;
     const std::string why = spec_unsupported_reason(hp);
     if (!why.empty()) throw std::runtime_error("specialize: " + why);
     if (perms.empty()) throw std::runtime_error("specialize: no permutation");
-    const ModeProgram& mp = hp.mode[CSIM_MODE_TRAN];
+    const ModeProgram& mp = hp.mode[mode];
     const csim_constants& C = hp.consts;
     const int K = (int)perms.size();
     std::vector<Analysis> As;
-    for (const auto& pm : perms) As.push_back(analyse(hp, pm));
+    for (const auto& pm : perms) As.push_back(analyse(hp, pm, mode));
     const int N = As[0].N;
     if (K > 1 && opt.replicas > 1) throw std::runtime_error("specialize: variants and replicas cannot be combined");
     TpiHost H;
@@ -217,7 +230,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     H.hash_hi = (uint32_t)(H.hashes[0] >> 32);
 
     // ---- classify values ------------------------------------------------------------------------
-    enum Kind { STATIC, STEP, SRC, MOS };
+    enum Kind { STATIC, STEP, SRC, MOS, GMINV };
     std::vector<Kind> kind(mp.n_values, STATIC);
     std::vector<bool> is_const(mp.n_values, false);
     std::vector<double> const_val(mp.n_values, 0.0);
@@ -227,11 +240,14 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
             is_const[s.out] = true;
             const_val[s.out] = 1.0;
             if (s.kind == SK_IND_ONE) ind_params.push_back(s.param);
-        } else if (s.kind == SK_GMIN) {
+        } else if (s.kind == SK_GMIN && !DC) {
             is_const[s.out] = true;
             const_val[s.out] = C.tran_gmin;
         }
     }
+    if (DC)  // the controller's gmin: a per-lane variable, changes between Newton iterations
+        for (const StaticOp& s : mp.static_ops)
+            if (s.kind == SK_GMIN) kind[s.out] = GMINV;
     if (!opt.const_prop)
         for (const StaticOp& s : mp.static_ops)
             if (s.kind == SK_ONE) is_const[s.out] = false;  // (gmin stays a literal either way)
@@ -287,7 +303,8 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     for (int i = 0; i < N; ++i)
         for (int j = 0; j <= N; ++j)
             for (const Term& t : As[v].rest[i][j])
-                if (kind[t.value] != MOS && !is_const[t.value] && !val_slot.count(t.value)) val_slot[t.value] = alloc();
+                if (kind[t.value] != MOS && kind[t.value] != GMINV && !is_const[t.value] && !val_slot.count(t.value))
+                    val_slot[t.value] = alloc();
     // static values needed again at every step (companion-model conductances) -> global scratch rows
     std::map<int, int> gs_row;
     for (const StepOp& s : mp.step_ops)
@@ -295,7 +312,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
             int r = (int)gs_row.size();
             gs_row[s.g] = r;
         }
-    H.n_scratch_rows = (int)gs_row.size() + N;  // + x_prev for the generic fallback
+    H.n_scratch_rows = DC ? 0 : (int)gs_row.size() + N;  // + x_prev for the generic fallback
     const int XP0 = (int)gs_row.size();
 
     std::map<int, int> mos_slot;
@@ -309,6 +326,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
                 if (!prm_slot.count(m.param + t)) prm_slot[m.param + t] = alloc();
     auto val = [&](int v) -> Val {  // per-iteration operand
         if (is_const[v]) return Val::K(const_val[v]);
+        if (kind[v] == GMINV) return Val::E("gmin@");
         if (kind[v] == MOS)  // (gm is exactly zero while the device is off: src/element.cpp:240-247)
             return opt.mos_in_smem ? Val::E(S(mos_slot.at(v)), kLatMos + kLatSmem, mos_gm.count(v) > 0)
                                    : Val::E("m" + std::to_string(v) + "@", kLatMos, mos_gm.count(v) > 0);
@@ -328,8 +346,10 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     if (K > 1) o << "    int var@ = 0;  // variant (predicted permutation) that held for this lane's last solve\n";
     o << "";
     for (int i = 0; i < N; ++i) {
-        if (opt.x_in_smem) o << "    " << S(X0 + i) << " = xio[(long long)" << i << " * B + bb@];\n";
-        else o << "    double x" << i << "@ = xio[(long long)" << i << " * B + bb@];\n";
+        const std::string x0 = DC ? std::string("0.0")  // x.setZero(N), src/dcanalysis.cpp:110
+                                  : "xio[(long long)" + std::to_string(i) + " * B + bb@]";
+        if (opt.x_in_smem) o << "    " << S(X0 + i) << " = " << x0 << ";\n";
+        else o << "    double x" << i << "@ = " << x0 << ";\n";
     }
     // ---- one-off: static values, base sums ---------------------------------------------------------
     for (const auto& kv : prm_slot)
@@ -360,8 +380,21 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
             acc = std::string(t.second ? "d_sub(" : "d_add(") + acc + ", v" + std::to_string(t.first) + ")";
         o << "        " << S(kv.second) << " = " << acc << ";\n";
     }
-    o << "    }\n    //@END\n"
-         "    const int r0 = T.out_begin_step / T.out_stride;\n"
+    o << "    }\n    //@END\n";
+    if (DC) {
+        // dcSolveNewtonLU's source ramp (src/dcanalysis.cpp:112-117): scale = step / rampSteps, the controller's base
+        // gmin for this step, prevErr = infinity; sources at evalDC(scale) (include/sim.hpp:152-158)
+        o << "    for (int step = 1; step <= " << C.dc_ramp_steps << "; ++step) {\n"
+             "        const double scale = (double)step / (double)" << C.dc_ramp_steps << ";\n"
+             "        const double gbase = tpi_base_gmin(" << lit(C.gmin_high_base) << ", " << lit(C.gmin_low_base) << ", scale);\n"
+             "        double gmin@ = gbase, prevErr@ = CSIM_TPI_INF;\n";
+        for (const SrcOp& op : mp.src_ops) {
+            if (!val_slot.count(op.out)) continue;
+            o << "        " << S(val_slot[op.out]) << " = src_dc_value(params, B, bb@, " << op.param << ", " << (op.is_sin ? 1 : 0)
+              << ", scale);\n";
+        }
+    } else {
+    o << "    const int r0 = T.out_begin_step / T.out_stride;\n"
          "    for (int step = T.step_begin; step < T.step_end; ++step) {\n"
          "        if (__all_sync(0xFFFFFFFFu, ALL(dead@))) break;\n";
     // ---- per step: x_prev -> scratch, companion history terms, source values -------------------------
@@ -383,9 +416,11 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
               << op.param << ", step, tnow);\n";
         }
     }
+    }  // TRAN step head
+    const int max_iters = DC ? C.dc_max_iters : C.tran_max_iters;
     o << "        int count@ = 0;\n"
          "        bool done@ = dead@;\n"
-         "        for (int iter = 0; iter < " << C.tran_max_iters << "; ++iter) {\n"
+         "        for (int iter = 0; iter < " << max_iters << "; ++iter) {\n"
          "            if (__all_sync(0xFFFFFFFFu, ALL(done@))) break;\n"
          "            bool bad@ = degen@;\n"
          "            unsigned int glo@ = 0xFFFFFFFFu, ghi@ = 0u, gacc@ = 0u, pmx@ = 0u, dacc@ = 0u;\n";
@@ -710,6 +745,10 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     if (K > 1) o << "                    unsigned long long pc@ = 0;\n";
     o << "";
     for (int i = 0; i < N; ++i) o << "                    xl[" << i << "] = " << xrd(i) << ";\n";
+    if (DC)
+        o << "                    tpi_generic_solve_dc<SPEC_N, SPEC_NV>(P, T, params, B, bb@, scale, gmin@, xl, xo, h@, st@"
+          << (K > 1 ? ", pc@" : "") << ");\n";
+    else
     o << "                    tpi_generic_solve<SPEC_N, SPEC_NV>(P, T, params, B, bb@, step, xl, scratch + (long long)" << XP0
       << " * B, xo, h@, st@" << (K > 1 ? ", pc@" : "") << ");\n";
     for (int i = 0; i < N; ++i) o << "                    q" << i << "@ = xo[" << i << "];\n";
@@ -739,7 +778,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
         const std::string xi = xrd(i), I = std::to_string(i);
         if (opt.x_in_smem) o << "            const double xo" << I << "@ = " << xi << ";\n";
         const std::string xv = opt.x_in_smem ? "xo" + I + "@" : xi;
-        o << "            const double n" << I << "@ = d_add(" << xv << ", d_mul(" << lit(C.tran_alpha) << ", d_sub(q" << I
+        o << "            const double n" << I << "@ = d_add(" << xv << ", d_mul(" << lit(DC ? C.dc_alpha : C.tran_alpha) << ", d_sub(q" << I
           << "@, " << xv << ")));\n"
           << "            double e" << I << "@ = d_sub(n" << I << "@, " << xv << ");\n"
           << "            e" << I << "@ = d_mul(e" << I << "@, e" << I << "@);\n";
@@ -765,8 +804,22 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     o << "                }\n"
          "                //@END\n"
          "            }\n"
-         "            //@BEGIN\n"
-         "            if (!done@) {\n"
+         "            //@BEGIN\n";
+    if (DC)  // src/dcanalysis.cpp:135-138: gmin *= 10 (capped), the iteration is spent, x stays
+        o << "            bool nf@ = false;\n"
+             "            if (!done@) {\n"
+             "                ++count@;\n"
+             "                if (!fin@) {\n"
+             "                    st@ |= CSIM_ST_NONFINITE;\n"
+             "                    const double g10 = d_mul(gmin@, " << lit(C.dc_nonfinite_mul) << ");\n"
+             "                    gmin@ = g10 < " << lit(C.dc_nonfinite_cap) << " ? g10 : " << lit(C.dc_nonfinite_cap) << ";\n"
+             "                    nf@ = true;\n"
+             "                }\n"
+             "            }\n"
+             "            //@END\n"
+             "            const bool upd@ = !done@ && !nf@;\n";
+    else
+    o << "            if (!done@) {\n"
          "                ++count@;\n"
          "                if (!fin@) {  // the reference throws here\n"
          "                    st@ |= CSIM_ST_NONFINITE;\n"
@@ -782,6 +835,44 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
         else o << "            x" << I << "@ = upd@ ? n" << I << "@ : x" << I << "@;\n";
     }
     o << "            const double err@ = sqrt(ssq@);\n";
+    if (DC) {
+        // ConvController::update (src/dcanalysis.cpp:268-307): gmin for the next iteration from the error trend
+        o << "            //@BEGIN\n"
+             "            if (upd@) {\n"
+             "                double gnext = gbase;\n"
+             "                if (!(iter == 0 || !finite_d(prevErr@))) {\n"
+             "                    if (err@ > d_mul(prevErr@, " << lit(C.slow_conv_ratio) << ")) {\n"
+             "                        const double g2 = d_mul(gmin@, 2.0);\n"
+             "                        gnext = g2 < " << lit(C.gmin_abs_max) << " ? g2 : " << lit(C.gmin_abs_max) << ";\n"
+             "                    } else if (err@ < d_mul(prevErr@, " << lit(C.fast_conv_ratio) << ")) {\n"
+             "                        gnext = d_add(d_mul(0.5, gmin@), d_mul(0.5, gbase));\n"
+             "                    } else {\n"
+             "                        gnext = d_add(d_mul(0.7, gmin@), d_mul(0.3, gbase));\n"
+             "                    }\n"
+             "                }\n"
+             "                gmin@ = gnext;\n"
+             "                prevErr@ = err@;\n"
+             "                if (err@ < " << lit(C.dc_tol) << ") done@ = true;\n"
+             "                else if (iter == " << C.dc_max_iters - 1 << ") st@ |= CSIM_ST_DC_UNCONVERGED;\n"
+             "            }\n"
+             "            //@END\n"
+             "        }\n"
+             "        total@ += count@;\n"
+             "        if (iters_total && live@) iters_total[(long long)(step - 1) * B + b@] = count@;  // iters [ramp][B]\n"
+             "    }\n"
+             "    //@BEGIN\n"
+             "    if (live@) {\n";
+        for (int i = 0; i < N; ++i) o << "        xio[(long long)" << i << " * B + b@] = " << xrd(i) << ";\n";
+        o << "        if (pivot_hash) pivot_hash[b@] = h@;\n"
+             "        if (status) status[b@] |= st@;\n"
+             "        if (stats) {\n"
+             "            if (n_fallback@) atomicAdd(stats, (unsigned long long)n_fallback@);\n"
+             "            atomicAdd(stats + 1, (unsigned long long)total@);\n"
+             "        }\n"
+             "    }\n"
+             "    //@END\n"
+             "}\n";
+    } else {
     o << "            //@BEGIN\n"
          "            if (upd@) {\n"
          "                if (err@ < " << lit(C.tran_tol) << ") done@ = true;\n"
@@ -816,6 +907,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
          "    }\n"
          "    //@END\n"
          "}\n";
+    }  // TRAN tail
 
     H.n_slots = n_slots;
     H.replicas = R;
@@ -845,7 +937,7 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
            "#define TPI_SUCC0 " << kTpiMissEntries * kTpiMissStride << "\n"
            "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kSmemPerSm / (H.smem_bytes + kCtaReserve)))
         << ")\n"
-           "csim_tran_tpi(DevPlan P, DevTran T, long long B, const double* __restrict__ params,\n"
+           "" << (DC ? "csim_dc_tpi" : "csim_tran_tpi") << "(DevPlan P, DevTran T, long long B, const double* __restrict__ params,\n"
            "              double* __restrict__ xio, double* __restrict__ wave, int* __restrict__ iters_total,\n"
            "              unsigned char* __restrict__ iters_step, unsigned long long* __restrict__ pivot_hash,\n"
            "              unsigned int* __restrict__ status, double* __restrict__ scratch,\n"
@@ -860,5 +952,6 @@ TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int3
     H.source = pro.str() + replicate(o.str(), R);
     return H;
 }
+}  // namespace
 
 }  // namespace csim

@@ -180,6 +180,15 @@ int csim_plan_specialize(csim_plan* plan, const int32_t* perm);
  * generically, as always.  In automatic mode the library adds variants itself (one per re-evaluation, the
  * permutation the redo path met most often) while more than 0.2 % of the solves miss.                 */
 int csim_plan_specialize_variants(csim_plan* plan, int32_t n_variants, const int32_t* perms);
+/* The DC operating point of circuits with MOSFETs (dcSolveNewtonLU, src/dcanalysis.cpp:95-163) runs on a generated
+ * thread-per-instance kernel too (csim_dc_tpi: source ramp and ConvController per lane, gmin a per-lane variable),
+ * unless the JIT mode is 0 or 2, CSIM_JIT=0|2 or CSIM_DC_TPI=0 is set, or N > 32.  The ramp walks through the circuit's
+ * operating regions, so the kernel collects predicted permutations (up to 8) over the first launches exactly like
+ * the transient kernel.  csim_plan_specialize_dc_variants installs a set directly; csim_plan_dc_spec_info reports
+ * whether the kernel is loaded, its variants, and solves redone generically / all solves since it was built.       */
+int csim_plan_specialize_dc_variants(csim_plan* plan, int32_t n_variants, const int32_t* perms);
+int csim_plan_dc_spec_info(const csim_plan* plan, int32_t* active, int32_t* n_variants, uint64_t* fallback_solves,
+                           uint64_t* solves, char* log, int32_t log_cap);
 /* active: 0 none / 2 / 3 = kind of the specialised kernel in use; perm [N] (NULL ok); counters since load:
  * Newton solves done by the generic fallback / all Newton solves; log: generator + NVRTC messages. */
 int csim_plan_spec_info(const csim_plan* plan, int32_t* active, int32_t* perm, uint64_t* fallback_solves,
@@ -189,7 +198,7 @@ int csim_plan_spec_source(const csim_plan* plan, char* out, int32_t cap);
 /* Host-only: source the generator emits for perm (no device needed); returns its length. */
 int csim_plan_generate_source(const csim_plan* plan, const int32_t* perm, char* out, int32_t cap);
 /* Same for either specialised transient kernel: kind 2 = warp per instance (csim_tran_spec),
- * kind 3 = thread per instance (csim_tran_tpi). */
+ * kind 3 = thread per instance (csim_tran_tpi); kind 4 = the thread-per-instance DC kernel (csim_dc_tpi). */
 int csim_plan_generate_source_kind(const csim_plan* plan, int kind, const int32_t* perm, char* out, int32_t cap);
 /* Host-only: thread-per-instance source for perms[n_variants][N]. */
 int csim_plan_generate_source_variants(const csim_plan* plan, int32_t n_variants, const int32_t* perms, char* out,

@@ -1,0 +1,114 @@
+"""GPU: the generated thread-per-instance DC kernel (csim_dc_tpi; dcSolveNewtonLU + ConvController, src/dcanalysis.cpp:95-163,
+264-307) against the oracle and the generic warp-per-instance dc_kernel: operating point bits, Newton iterations per
+ramp step, pivot hash, status — on every launch while the kernel is still learning permutation variants, with a
+deliberately wrong prediction, and on Monte-Carlo batches of all three circuits."""
+import numpy as np
+import pytest
+
+from oracle import oraclelib as O
+from support import assert_same_bits, load_golden, make_plan
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    assert torch.cuda.is_available()
+    return torch
+
+
+def u64(t):
+    return t.cpu().numpy().view(np.uint64)
+
+
+def _topo(name):
+    if name == "sources":
+        from test_sources_cpu import load_sources
+        g, topo, _, _ = load_sources()
+        return g, topo
+    return load_golden(name)
+
+
+def _same(a, b, what):
+    assert_same_bits(a["x"].cpu().numpy(), b["x"].cpu().numpy(), what + ": x")
+    assert np.array_equal(a["iters"].cpu().numpy(), b["iters"].cpu().numpy()), what + ": iterations per ramp step"
+    assert np.array_equal(u64(a["hash"]), u64(b["hash"])), what + ": pivot hash"
+    assert np.array_equal(a["status"].cpu().numpy(), b["status"].cpu().numpy()), what + ": status"
+
+
+@pytest.mark.parametrize("name", ["buffer", "dbmixer", "sources"])
+def test_dc_tpi_equals_generic_kernel_and_oracle_while_learning(torch, name):
+    from circuitsimulator_b200 import capi
+    g, topo = _topo(name)
+    B = 3000
+    P = O.monte_carlo(topo, B, 20261104 + 3)
+    params = torch.from_numpy(np.ascontiguousarray(P.T)).cuda()
+    gen = make_plan(topo)
+    gen.jit_mode(0)
+    want = capi.dc(gen, params)
+    assert not gen.dc_spec_info()["active"]
+    plan = make_plan(topo)
+    seen = []
+    for launch in range(6):  # variants are added between launches; results never depend on them
+        got = capi.dc(plan, params)
+        torch.cuda.synchronize()
+        info = plan.dc_spec_info()
+        assert info["active"], info["log"]
+        seen.append((info["n_variants"], info["fallback_solves"], info["solves"]))
+        _same(got, want, f"{name} launch {launch}")
+    assert seen[-1][2] > 0
+    if name == "buffer":  # the ramp crosses operating regions: more than one pivot order
+        assert seen[-1][0] > 1, seen
+    assert_same_bits(want["x"][:, 0].cpu().numpy(), g["x_dc" if name != "sources" else "const_x_dc"], "nominal vs golden")
+    for b in list(range(12)) + [B - 1]:
+        od = O.dc(topo, P[b])
+        assert_same_bits(got["x"][:, b].cpu().numpy(), od["x"], f"{name} instance {b} vs oracle")
+        assert np.array_equal(got["iters"][:, b].cpu().numpy(), od["iters"])
+        assert u64(got["hash"])[b] == np.uint64(od["hash"]) and int(got["status"][b]) == od["status"]
+
+
+def test_dc_tpi_wrong_prediction_is_redone_generically(torch):
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    N = topo.n_unknowns
+    B = 70
+    P = O.monte_carlo(topo, B, 5)
+    params = torch.from_numpy(np.ascontiguousarray(P.T)).cuda()
+    plan = make_plan(topo)
+    plan.specialize_dc_variants(np.arange(N)[::-1].copy())  # nobody's matrix takes this order
+    got = capi.dc(plan, params)
+    torch.cuda.synchronize()
+    info = plan.dc_spec_info()
+    assert info["active"] and info["fallback_solves"] == info["solves"] > 0
+    for b in range(0, B, 7):
+        od = O.dc(topo, P[b])
+        assert_same_bits(got["x"][:, b].cpu().numpy(), od["x"], f"instance {b}")
+        assert np.array_equal(got["iters"][:, b].cpu().numpy(), od["iters"]) and u64(got["hash"])[b] == np.uint64(od["hash"])
+
+
+def test_dc_tpi_degenerate_and_nonfinite_paths(torch):
+    """R = 0 (stamp skipped), L <= 0 (singular -> zero vector) and a huge transconductance (non-finite solve -> gmin x 10):
+    the controller's branches, lane by lane."""
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    P = np.repeat(topo.params[None], 6, 0)
+    e_l = [e for e in range(topo.n_elems) if topo.elem_type[e] == O.ELEM_L]
+    e_r = [e for e in range(topo.n_elems) if topo.elem_type[e] == O.ELEM_R]
+    e_m = [e for e in range(topo.n_elems) if topo.elem_type[e] == O.ELEM_MOS]
+    P[1, topo.elem_param[e_l[0]]] = 0.0
+    P[2, topo.elem_param[e_r[1]]] = 0.0
+    P[3, topo.elem_param[e_m[0]] + 1] = 1e300     # K: overflows the linearisation
+    P[4, topo.elem_param[e_m[1]] + 1] = 1e-300
+    P[5, topo.elem_param[e_m[2]]] = 1e3           # Vth: never on
+    params = torch.from_numpy(np.ascontiguousarray(P.T)).cuda()
+    plan = make_plan(topo)
+    for launch in range(2):
+        got = capi.dc(plan, params)
+        torch.cuda.synchronize()
+        assert plan.dc_spec_info()["active"]
+        for b in range(6):
+            od = O.dc(topo, P[b])
+            assert_same_bits(got["x"][:, b].cpu().numpy(), od["x"], f"instance {b}")
+            assert np.array_equal(got["iters"][:, b].cpu().numpy(), od["iters"]), b
+            assert u64(got["hash"])[b] == np.uint64(od["hash"]) and int(got["status"][b]) == od["status"], b
