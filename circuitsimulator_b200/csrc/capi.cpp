@@ -345,7 +345,7 @@ constexpr unsigned long long kTpiMinSolves = 20000;
 // Before giving the kernel up, further predicted permutations are added (one per re-evaluation, the one the
 // redo path met most often) while more than kTpiAdaptMissRate of the solves miss.
 constexpr double kTpiAdaptMissRate = 0.002;
-constexpr int kTpiMaxVariants = 8;
+constexpr int kTpiMaxVariants = 16;  // (TPI_CAND masks are 16 bits wide)
 
 // Kernel to use for this launch: 0 generic, 2 warp-per-instance, 3 thread-per-instance (compiled on first use).
 int spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const double* d_x, double dt,
@@ -493,15 +493,30 @@ bool dc_prepare(const csim_plan* plan, int64_t B, const double* d_params, cudaSt
                 if (best < 0 || cnt > tab[(size_t)best * kTpiMissStride + 1]) best = e;
             }
         if (best >= 0 && tab[(size_t)best * kTpiMissStride + 1] * 4 >= st[0] / 10) {
+            // every logged order worth a variant (>= 2.5 % of the misses), most frequent first: the ramp crosses many
+            // operating regions, and one variant per launch would take a dozen launches (and compilations) to settle
+            std::vector<int> order;
+            for (int e = 0; e < kTpiMissEntries; ++e) {
+                const unsigned long long hsh = tab[(size_t)e * kTpiMissStride], cnt = tab[(size_t)e * kTpiMissStride + 1];
+                if (!hsh || cnt * 4 < st[0] / 10) continue;
+                if (std::find(tp.host.hashes.begin(), tp.host.hashes.end(), hsh) != tp.host.hashes.end()) continue;
+                order.push_back(e);
+            }
+            std::sort(order.begin(), order.end(), [&](int a, int b) {
+                return tab[(size_t)a * kTpiMissStride + 1] > tab[(size_t)b * kTpiMissStride + 1];
+            });
             std::vector<std::vector<int32_t>> perms = tp.host.perms;
-            std::vector<int32_t> np(plan->host.N);
-            for (int i = 0; i < plan->host.N; ++i) np[i] = (int32_t)tab[(size_t)best * kTpiMissStride + 2 + i];
-            perms.push_back(np);
+            for (int e : order) {
+                if ((int)perms.size() >= kTpiMaxVariants) break;
+                std::vector<int32_t> np(plan->host.N);
+                for (int i = 0; i < plan->host.N; ++i) np[i] = (int32_t)tab[(size_t)e * kTpiMissStride + 2 + i];
+                perms.push_back(np);
+            }
             const std::vector<std::vector<int32_t>> old = tp.host.perms;
             const std::string hist = tp.history;
             tp.history += "\n" + std::to_string(st[0]) + " of " + std::to_string(st[1]) +
-                          " DC solves missed the predicted pivot order -> variant " + std::to_string(perms.size() - 1) +
-                          " added (met " + std::to_string(tab[(size_t)best * kTpiMissStride + 1]) + " times)";
+                          " DC solves missed the predicted pivot order -> " + std::to_string(perms.size() - old.size()) +
+                          " variant(s) added (" + std::to_string(perms.size()) + " now)";
             if (tpi_build(plan, perms, true) != CSIM_OK) {
                 tp.history = hist;
                 if (tpi_build(plan, old, true) != CSIM_OK) return false;
@@ -1474,7 +1489,7 @@ int csim_plan_specialize_variants(csim_plan* plan, int32_t n_variants, const int
     int rc = need_device(plan, "csim_plan_specialize_variants");
     if (rc) return rc;
     if (!perms || n_variants < 1 || n_variants > kTpiMaxVariants)
-        return fail(CSIM_E_INVALID, "csim_plan_specialize_variants: 1..8 permutations expected");
+        return fail(CSIM_E_INVALID, "csim_plan_specialize_variants: 1..16 permutations expected");
     std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
     SpecState& sp = plan->spec;
     sp.tried = true;
@@ -1491,7 +1506,7 @@ int csim_plan_specialize_dc_variants(csim_plan* plan, int32_t n_variants, const 
     int rc = need_device(plan, "csim_plan_specialize_dc_variants");
     if (rc) return rc;
     if (!perms || n_variants < 1 || n_variants > kTpiMaxVariants)
-        return fail(CSIM_E_INVALID, "csim_plan_specialize_dc_variants: 1..8 permutations expected");
+        return fail(CSIM_E_INVALID, "csim_plan_specialize_dc_variants: 1..16 permutations expected");
     std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
     if (plan->spec.mode == 0 || plan->spec.mode == 2) plan->spec.mode = 1;
     const int N = plan->host.N;

@@ -80,7 +80,7 @@ TpiHost generate_dc_tpi(const HostPlan& hp, const std::vector<std::vector<int32_
 // Device-side log of the permutations the generic redo path met (tpi_generic_solve): kTpiMissEntries entries of
 // kTpiMissStride uint64 = { pivot-hash contribution (0 = free), count, perm[0..31] }.
 // Behind them kTpiSuccEntries uint64: succ[v] = 1 + the variant a lane moved to when it last left variant v (0 = none).
-constexpr int kTpiMissEntries = 16, kTpiMissStride = 34, kTpiSuccEntries = 8;
+constexpr int kTpiMissEntries = 16, kTpiMissStride = 34, kTpiSuccEntries = 16;
 constexpr int kTpiMissWords = kTpiMissEntries * kTpiMissStride + kTpiSuccEntries;
 
 // ---- standalone assembly kernel (specialize_stamp.cpp) ---------------------------------------

@@ -454,8 +454,11 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         o << "            bool need@ = !done@, missed@ = false;\n"
              "            int var_before@ = var@;\n"
              "#pragma unroll 1\n"
-             "            for (int pass = 0; pass < 2; ++pass) {\n"
+             "            unsigned int tried@ = 0u;\n"
+             "            int kf@ = SPEC_N;  // first elimination step at which the running variant's pivot prediction failed\n"
+             "            for (int pass = 0; pass < 3; ++pass) {\n"
              "            if (need@) {\n"
+             "                kf@ = SPEC_N;\n"
              "                bad@ = degen@;\n"
              "                glo@ = 0xFFFFFFFFu;\n"
              "                ghi@ = 0u;\n"
@@ -465,6 +468,25 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
              "            }\n";
     }
     unsigned dacc_limit = 0xFFFFFFFFu;  // pivot range accumulator's acceptance limit (fold_guards)
+    // TPI_CAND[v * N + k]: variants with the same pivots as v before step k and another one at k
+    std::string cand_table;
+    if (K > 1) {
+        std::ostringstream ct;
+        ct << "__constant__ unsigned short TPI_CAND[" << K * N << "] = {";
+        for (int v = 0; v < K; ++v)
+            for (int k = 0; k < N; ++k) {
+                unsigned mask = 0;
+                for (int u = 0; u < K; ++u) {
+                    if (u == v || perms[u][k] == perms[v][k]) continue;
+                    bool same = true;
+                    for (int t = 0; t < k; ++t) same = same && perms[u][t] == perms[v][t];
+                    if (same) mask |= 1u << u;
+                }
+                ct << (v + k ? ", " : "") << mask;
+            }
+        ct << "};\n";
+        cand_table = ct.str();
+    }
     const int n_common = n_slots;  // slots below are shared by all variants; each variant parks its LU above
     int n_slots_max = n_slots;
     TpiHost H0;  // statistics of variant 0
@@ -486,7 +508,8 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     // true -> divide() emits a division whose guards also judge the pivot rule (tdiv_mul): no explicit comparison needed
     auto folded_mult = [&](const Val& a, int k) {
         const Val& d = Dv[k];
-        return opt.fold_guards && !a.z && !(d.c && (d.v == 1.0 || d.v == -1.0)) && !(a.c && d.c);
+        // (several variants: the failing STEP is needed to pick the next candidate, so the rule is tested explicitly)
+        return K == 1 && opt.fold_guards && !a.z && !(d.c && (d.v == 1.0 || d.v == -1.0)) && !(a.c && d.c);
     };
     auto divide = [&](const Val& a, int k, const std::string& tmp, const char* ind, bool mult) -> Val {
         const Val& d = Dv[k];
@@ -494,8 +517,8 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         if (d.c && d.v == -1.0) return neg(a);
         if (a.c && d.c) return Val::K(a.v / d.v);
         if (opt.fold_guards && !a.z)
-            o << ind << "const double " << tmp << " = " << (mult ? "tdiv_mul(" : "tdiv_nz(") << a.e << ", " << d.e << ", "
-              << RDv[k].e << ", gacc@" << (mult ? ", pmx@" : "") << ");\n";
+            o << ind << "const double " << tmp << " = " << (mult && K == 1 ? "tdiv_mul(" : "tdiv_nz(") << a.e << ", " << d.e
+              << ", " << RDv[k].e << ", gacc@" << (mult && K == 1 ? ", pmx@" : "") << ");\n";
         else
             o << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo@, ghi@);\n";
         H.n_lu_divs++;
@@ -546,7 +569,10 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
             // judged on the quotient by tdiv_mul (|f| >= 1 on the high word: never misses, ties included)
         } else if (a.c && Dv[k].c) {
             if (std::fabs(a.v) > std::fabs(Dv[k].v) || (tie_loses && std::fabs(a.v) == std::fabs(Dv[k].v)))
-                o << ind << "bad@ = true;\n";
+                o << ind << (K > 1 ? "kf@ = min(kf@, " + std::to_string(k) + ");\n" : std::string("bad@ = true;\n"));
+        } else if (K > 1) {
+            o << ind << "if (fabs(" << a.e << ") " << (tie_loses ? ">=" : ">") << " "
+              << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")") << ") kf@ = min(kf@, " << k << ");\n";
         } else {
             o << ind << "bad@ = bad@ || (fabs(" << a.e << ") " << (tie_loses ? ">=" : ">") << " "
               << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")") << ");\n";
@@ -722,12 +748,21 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     H.crit_cycles += 5 * kLatOp + 5 * kLatOp + kLatSqrt;  // damped update + square, 32-leaf tree, sqrt
     // ---- prediction check / per-lane generic redo ------------------------------------------------------------
     if (K > 1)
-        o << "            if (need@) missed@ = bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (pmx@ >= kTdivTOne) || (dacc@ > DACC_LIMIT);\n"
+        // A lane whose variant failed at elimination step kf retries — at most twice — a variant with the SAME pivots
+        // before kf and a different one at kf (TPI_CAND, from the permutations' common prefixes): the matrix up to
+        // step kf is the same under all of them, so they are the only known orders that can hold.  Among several
+        // candidates the one that last followed this variant (succ[], a racy global hint) goes first, then the
+        // earliest-learned (most frequent).  Failures that are not about the order (range guards) go straight to the redo.
+        o << "            const bool order_only@ = !bad@ && !((glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (dacc@ > DACC_LIMIT));\n"
+             "            if (need@) missed@ = !order_only@ || kf@ < SPEC_N;\n"
+             "            const bool was@ = need@;\n"
              "            need@ = false;\n"
-             "            if (pass == 0 && missed@ && !degen@ && T.miss) {\n"
-             "                const int w = (int)T.miss[TPI_SUCC0 + var@] - 1;\n"
-             "                if (w >= 0 && w < " << K << " && w != var@) {\n"
-             "                    var@ = w;\n"
+             "            if (was@ && pass < 2 && missed@ && order_only@ && !degen@) {\n"
+             "                tried@ |= 1u << var@;\n"
+             "                const unsigned int cand = (unsigned int)TPI_CAND[var@ * SPEC_N + kf@] & ~tried@;\n"
+             "                if (cand) {\n"
+             "                    const int hint = T.miss ? (int)T.miss[TPI_SUCC0 + var@] - 1 : -1;\n"
+             "                    var@ = (hint >= 0 && hint < " << K << " && ((cand >> hint) & 1u)) ? hint : (__ffs(cand) - 1);\n"
              "                    need@ = true;\n"
              "                }\n"
              "            }\n"
@@ -934,6 +969,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
            "#define SOFF(k, r) ((((k) + (r) * NSLOTS) * TPB) * 8)\n"
            "#define PRM(k, bb) ld_nohoist(params + (long long)(k) * B + (bb))\n"
            "#define DACC_LIMIT 0x" << std::hex << dacc_limit << std::dec << "u\n"
+        << cand_table <<
            "#define TPI_SUCC0 " << kTpiMissEntries * kTpiMissStride << "\n"
            "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kSmemPerSm / (H.smem_bytes + kCtaReserve)))
         << ")\n"

@@ -175,7 +175,7 @@ int csim_plan_dims(const csim_plan* plan, int32_t* n_unknowns, int32_t* n_params
 int csim_plan_jit_mode(csim_plan* plan, int mode);
 /* Specialise now for perm[N] (perm[i] = original row expected at pivot position i). */
 int csim_plan_specialize(csim_plan* plan, const int32_t* perm);
-/* Thread-per-instance kernel with several predicted permutations, perms[n_variants][N] (1 <= n_variants <= 8):
+/* Thread-per-instance kernel with several predicted permutations, perms[n_variants][N] (1 <= n_variants <= 16):
  * every lane runs the variant whose permutation its last solve took; a solve no variant predicts is redone
  * generically, as always.  In automatic mode the library adds variants itself (one per re-evaluation, the
  * permutation the redo path met most often) while more than 0.2 % of the solves miss.                 */
@@ -183,7 +183,7 @@ int csim_plan_specialize_variants(csim_plan* plan, int32_t n_variants, const int
 /* The DC operating point of circuits with MOSFETs (dcSolveNewtonLU, src/dcanalysis.cpp:95-163) runs on a generated
  * thread-per-instance kernel too (csim_dc_tpi: source ramp and ConvController per lane, gmin a per-lane variable),
  * unless the JIT mode is 0 or 2, CSIM_JIT=0|2 or CSIM_DC_TPI=0 is set, or N > 32.  The ramp walks through the circuit's
- * operating regions, so the kernel collects predicted permutations (up to 8) over the first launches exactly like
+ * operating regions, so the kernel collects predicted permutations (up to 16) over the first launches exactly like
  * the transient kernel.  csim_plan_specialize_dc_variants installs a set directly; csim_plan_dc_spec_info reports
  * whether the kernel is loaded, its variants, and solves redone generically / all solves since it was built.       */
 int csim_plan_specialize_dc_variants(csim_plan* plan, int32_t n_variants, const int32_t* perms);
