@@ -209,6 +209,8 @@ TpiOptions tpi_options_from_env() {
         opt.fold_guards = m & 32;
         opt.opaque_park = m & 64;
         opt.int_pivot_guard = m & 128;
+        opt.cand_retry = !(m & 1024);
+        opt.cand_retry_tran = m & 2048;
         opt.replicas = 1 + ((m >> 8) & 3);
         opt.warps_per_cta = (m >> 12) & 7;
         if ((m >> 16) & 15) opt.rows_in_flight = (m >> 16) & 15;
@@ -346,6 +348,14 @@ constexpr unsigned long long kTpiMinSolves = 20000;
 // redo path met most often) while more than kTpiAdaptMissRate of the solves miss.
 constexpr double kTpiAdaptMissRate = 0.002;
 constexpr int kTpiMaxVariants = 16;  // (TPI_CAND masks are 16 bits wide)
+// How many variants the automatic mode collects by itself: every variant is one more straight-line body the lanes of
+// a warp may be spread over.  Transient (lanes stay in one operating region for many solves): 8 (measured optimum on
+// buffer.sp); DC ramp (every lane crosses every region once): 16.  CSIM_TPI_MAX_VARIANTS / CSIM_DC_MAX_VARIANTS override.
+int auto_variant_cap(bool dc) {
+    const char* env = std::getenv(dc ? "CSIM_DC_MAX_VARIANTS" : "CSIM_TPI_MAX_VARIANTS");
+    const int v = env ? std::atoi(env) : (dc ? 16 : 8);
+    return v < 1 ? 1 : (v > kTpiMaxVariants ? kTpiMaxVariants : v);
+}
 
 // Kernel to use for this launch: 0 generic, 2 warp-per-instance, 3 thread-per-instance (compiled on first use).
 int spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const double* d_x, double dt,
@@ -361,7 +371,7 @@ int spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const
                           st[1] >= kTpiMinSolves;
         // first remedy: one more predicted permutation — the one the redo path met most often
         if (have && (double)st[0] > kTpiAdaptMissRate * (double)st[1] && tp.d_miss &&
-            (int)tp.host.perms.size() < kTpiMaxVariants) {
+            (int)tp.host.perms.size() < auto_variant_cap(false)) {
             std::vector<unsigned long long> tab((size_t)kTpiMissEntries * kTpiMissStride, 0);
             int best = -1;
             if (cudaMemcpy(tab.data(), tp.d_miss, tab.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) ==
@@ -391,7 +401,7 @@ int spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const
             }
         }
         if (sp.mode == 1 && sp.kind == 3 && have && st[1] >= kTpiMinSolves && (double)st[0] > kTpiMaxMissRate * (double)st[1] &&
-            (int)tp.host.perms.size() >= kTpiMaxVariants) {
+            (int)tp.host.perms.size() >= auto_variant_cap(false)) {
             tp.log += "\nautomatic mode: " + std::to_string(st[0]) + " of " + std::to_string(st[1]) +
                       " solves missed the predicted pivot order -> warp-per-instance kernel";
             sp.kind = 2;
@@ -483,7 +493,7 @@ bool dc_prepare(const csim_plan* plan, int64_t B, const double* d_params, cudaSt
     cudaStreamSynchronize(stream);
     const bool have = tp.d_stats && cudaMemcpy(st, tp.d_stats, sizeof(st), cudaMemcpyDeviceToHost) == cudaSuccess &&
                       st[1] >= kTpiMinSolves;
-    if (have && (double)st[0] > kTpiAdaptMissRate * (double)st[1] && tp.d_miss && (int)tp.host.perms.size() < kTpiMaxVariants) {
+    if (have && (double)st[0] > kTpiAdaptMissRate * (double)st[1] && tp.d_miss && (int)tp.host.perms.size() < auto_variant_cap(true)) {
         std::vector<unsigned long long> tab((size_t)kTpiMissEntries * kTpiMissStride, 0);
         int best = -1;
         if (cudaMemcpy(tab.data(), tp.d_miss, tab.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess)
@@ -507,7 +517,7 @@ bool dc_prepare(const csim_plan* plan, int64_t B, const double* d_params, cudaSt
             });
             std::vector<std::vector<int32_t>> perms = tp.host.perms;
             for (int e : order) {
-                if ((int)perms.size() >= kTpiMaxVariants) break;
+                if ((int)perms.size() >= auto_variant_cap(true)) break;
                 std::vector<int32_t> np(plan->host.N);
                 for (int i = 0; i < plan->host.N; ++i) np[i] = (int32_t)tab[(size_t)e * kTpiMissStride + 2 + i];
                 perms.push_back(np);

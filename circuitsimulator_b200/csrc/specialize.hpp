@@ -64,6 +64,8 @@ struct TpiOptions {
     bool mos_branchless = false; // evaluate both MOSFET regions and select (measured slower on dbmixer)
     bool fold_guards = true;     // divisions whose numerator cannot be an exact zero: guards folded into one unsigned accumulator, pivot rule judged on the quotient (tdiv_nz / tdiv_mul)
     bool int_pivot_guard = false; // (with fold_guards) pivot range test on the high word in an unsigned accumulator instead of two FP64 compares per row
+    bool cand_retry_tran = false; // ... the same in the transient kernel (B200, buffer.sp, 65,536 instances: 210 ms against 117 ms with the successor hint: resolved misses stop the learning of further variants and every retry costs the warp extra bodies)
+    bool cand_retry = true;      // DC kernel, several variants (buffer.sp DC ramp, 65,536 instances: 61 ms against 85 ms): a lane whose variant fails at elimination step k retries variants with the same pivot prefix and another pivot at k (else: one global successor hint, folded pivot guards)
     bool opaque_park = false;    // parked LU rows (pivot, reciprocal, U entries, y) stored by asm blocks and re-read by asm loads: the compiler cannot forward the stored registers to later rows (long live ranges, spills)
     int rows_in_flight = 2;      // matrix rows whose elimination chains are interleaved in the generated source (B200, dbmixer: 1 -> 111.4, 2 -> 113.9, 3 -> 113.4, 4 -> slower; M instance-timepoints/s)
     int warps_per_cta = 0;       // 0 = whatever packs most warps into an SM's shared memory (1, 2 or 4)

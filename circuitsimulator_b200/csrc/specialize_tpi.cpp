@@ -206,6 +206,8 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     const ModeProgram& mp = hp.mode[mode];
     const csim_constants& C = hp.consts;
     const int K = (int)perms.size();
+    // candidate retry by first failing step (else: one successor hint); measured per mode, see TpiOptions
+    const bool CAND = K > 1 && (mode == CSIM_MODE_DC ? opt.cand_retry : opt.cand_retry_tran);
     std::vector<Analysis> As;
     for (const auto& pm : perms) As.push_back(analyse(hp, pm, mode));
     const int N = As[0].N;
@@ -456,7 +458,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
              "#pragma unroll 1\n"
              "            unsigned int tried@ = 0u;\n"
              "            int kf@ = SPEC_N;  // first elimination step at which the running variant's pivot prediction failed\n"
-             "            for (int pass = 0; pass < 3; ++pass) {\n"
+             "            for (int pass = 0; pass < " << (CAND ? 3 : 2) << "; ++pass) {\n"
              "            if (need@) {\n"
              "                kf@ = SPEC_N;\n"
              "                bad@ = degen@;\n"
@@ -509,7 +511,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     auto folded_mult = [&](const Val& a, int k) {
         const Val& d = Dv[k];
         // (several variants: the failing STEP is needed to pick the next candidate, so the rule is tested explicitly)
-        return K == 1 && opt.fold_guards && !a.z && !(d.c && (d.v == 1.0 || d.v == -1.0)) && !(a.c && d.c);
+        return !CAND && opt.fold_guards && !a.z && !(d.c && (d.v == 1.0 || d.v == -1.0)) && !(a.c && d.c);
     };
     auto divide = [&](const Val& a, int k, const std::string& tmp, const char* ind, bool mult) -> Val {
         const Val& d = Dv[k];
@@ -517,8 +519,8 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         if (d.c && d.v == -1.0) return neg(a);
         if (a.c && d.c) return Val::K(a.v / d.v);
         if (opt.fold_guards && !a.z)
-            o << ind << "const double " << tmp << " = " << (mult && K == 1 ? "tdiv_mul(" : "tdiv_nz(") << a.e << ", " << d.e
-              << ", " << RDv[k].e << ", gacc@" << (mult && K == 1 ? ", pmx@" : "") << ");\n";
+            o << ind << "const double " << tmp << " = " << (mult && !CAND ? "tdiv_mul(" : "tdiv_nz(") << a.e << ", " << d.e
+              << ", " << RDv[k].e << ", gacc@" << (mult && !CAND ? ", pmx@" : "") << ");\n";
         else
             o << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo@, ghi@);\n";
         H.n_lu_divs++;
@@ -569,8 +571,8 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
             // judged on the quotient by tdiv_mul (|f| >= 1 on the high word: never misses, ties included)
         } else if (a.c && Dv[k].c) {
             if (std::fabs(a.v) > std::fabs(Dv[k].v) || (tie_loses && std::fabs(a.v) == std::fabs(Dv[k].v)))
-                o << ind << (K > 1 ? "kf@ = min(kf@, " + std::to_string(k) + ");\n" : std::string("bad@ = true;\n"));
-        } else if (K > 1) {
+                o << ind << (CAND ? "kf@ = min(kf@, " + std::to_string(k) + ");\n" : std::string("bad@ = true;\n"));
+        } else if (CAND) {
             o << ind << "if (fabs(" << a.e << ") " << (tie_loses ? ">=" : ">") << " "
               << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")") << ") kf@ = min(kf@, " << k << ");\n";
         } else {
@@ -747,7 +749,20 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     H.crit_lu_cycles = H.crit_cycles;
     H.crit_cycles += 5 * kLatOp + 5 * kLatOp + kLatSqrt;  // damped update + square, 32-leaf tree, sqrt
     // ---- prediction check / per-lane generic redo ------------------------------------------------------------
-    if (K > 1)
+    if (K > 1 && !CAND)
+        o << "            if (need@) missed@ = bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (pmx@ >= kTdivTOne) || (dacc@ > DACC_LIMIT);\n"
+             "            need@ = false;\n"
+             "            if (pass == 0 && missed@ && !degen@ && T.miss) {\n"
+             "                const int w = (int)T.miss[TPI_SUCC0 + var@] - 1;\n"
+             "                if (w >= 0 && w < " << K << " && w != var@) {\n"
+             "                    var@ = w;\n"
+             "                    need@ = true;\n"
+             "                }\n"
+             "            }\n"
+             "            if (!__any_sync(0xFFFFFFFFu, need@)) break;\n"
+             "            }  // pass\n"
+             "            const bool redo@ = missed@;\n";
+    else if (K > 1)
         // A lane whose variant failed at elimination step kf retries — at most twice — a variant with the SAME pivots
         // before kf and a different one at kf (TPI_CAND, from the permutations' common prefixes): the matrix up to
         // step kf is the same under all of them, so they are the only known orders that can hold.  Among several

@@ -112,3 +112,26 @@ def test_dc_tpi_degenerate_and_nonfinite_paths(torch):
             assert_same_bits(got["x"][:, b].cpu().numpy(), od["x"], f"instance {b}")
             assert np.array_equal(got["iters"][:, b].cpu().numpy(), od["iters"]), b
             assert u64(got["hash"])[b] == np.uint64(od["hash"]) and int(got["status"][b]) == od["status"], b
+
+
+def test_dc_tpi_candidate_retry_recovers_from_a_wrong_variant_without_the_generic_redo(torch):
+    """Two predicted permutations, the first wrong at elimination step 0: every lane's first solve fails there and the
+    candidate table (same pivot prefix, another pivot at the failing step) sends it to the other variant."""
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    N, B = topo.n_unknowns, 64
+    P = O.monte_carlo(topo, B, 9)
+    params = torch.from_numpy(np.ascontiguousarray(P.T)).cuda()
+    first = O.dc(topo, topo.params, trace_cap=4)["trace"].perm[0]
+    wrong = first.copy()
+    wrong[0], wrong[-1] = first[-1], first[0]  # another pivot at step 0
+    only_wrong, both = make_plan(topo), make_plan(topo)
+    only_wrong.specialize_dc_variants(wrong)
+    both.specialize_dc_variants(np.stack([wrong, first]))
+    a, b = capi.dc(only_wrong, params), capi.dc(both, params)
+    torch.cuda.synchronize()
+    _same(a, b, "wrong only vs wrong + right")
+    ia, ib = only_wrong.dc_spec_info(), both.dc_spec_info()
+    assert ia["fallback_solves"] == ia["solves"] == ib["solves"] and ib["fallback_solves"] < ib["solves"] // 2, (ia, ib)
+    od = O.dc(topo, P[5])
+    assert_same_bits(b["x"][:, 5].cpu().numpy(), od["x"], "instance 5 vs oracle")
