@@ -125,13 +125,18 @@ def test_dc_tpi_candidate_retry_recovers_from_a_wrong_variant_without_the_generi
     first = O.dc(topo, topo.params, trace_cap=4)["trace"].perm[0]
     wrong = first.copy()
     wrong[0], wrong[-1] = first[-1], first[0]  # another pivot at step 0
-    only_wrong, both = make_plan(topo), make_plan(topo)
+    only_wrong, only_right, both = make_plan(topo), make_plan(topo), make_plan(topo)
     only_wrong.specialize_dc_variants(wrong)
+    only_right.specialize_dc_variants(first)
     both.specialize_dc_variants(np.stack([wrong, first]))
-    a, b = capi.dc(only_wrong, params), capi.dc(both, params)
+    a, r, b = capi.dc(only_wrong, params), capi.dc(only_right, params), capi.dc(both, params)
     torch.cuda.synchronize()
     _same(a, b, "wrong only vs wrong + right")
-    ia, ib = only_wrong.dc_spec_info(), both.dc_spec_info()
-    assert ia["fallback_solves"] == ia["solves"] == ib["solves"] and ib["fallback_solves"] < ib["solves"] // 2, (ia, ib)
+    _same(r, b, "right only vs wrong + right")
+    ia, ir, ib = only_wrong.dc_spec_info(), only_right.dc_spec_info(), both.dc_spec_info()
+    assert ia["fallback_solves"] == ia["solves"] == ib["solves"] == ir["solves"]
+    # starting every lane on the wrong variant costs no extra generic solves: the first solve's failure at step 0
+    # leads to the right variant through the candidate table (the first solve's order holds for part of the ramp only)
+    assert ib["fallback_solves"] <= ir["fallback_solves"] < ia["fallback_solves"], (ia, ir, ib)
     od = O.dc(topo, P[5])
     assert_same_bits(b["x"][:, 5].cpu().numpy(), od["x"], "instance 5 vs oracle")
