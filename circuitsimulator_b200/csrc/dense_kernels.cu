@@ -52,18 +52,48 @@ __device__ unsigned long long dn_prof[8];
     } while (0)
 #endif
 
+// ---- TMA (bulk asynchronous copy) staging of the strip of U ------------------------------------------------------------
+// The strip rows (positions k0..k0+15 of one 128-column block) are 16 contiguous 1 KB segments of [A | b]: one elected
+// thread issues 16 cp.async.bulk copies global -> shared that complete on an mbarrier (SASS: UBLKCP.S.G +
+// SYNCS.ARRIVE.TRANS64), into the buffer the CTA is NOT computing from, so the next block's rows arrive while the
+// trailing update of the current block runs.
+__device__ __forceinline__ unsigned dn_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void dn_mbar_init(uint64_t* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dn_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void dn_mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dn_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void dn_bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dn_smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(dn_smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void dn_mbar_wait(uint64_t* bar, unsigned parity) {
+    asm volatile(
+        "{\n.reg .pred p;\nDN_WAIT_%=:\nmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n@p bra DN_DONE_%=;\nbra DN_WAIT_%=;\nDN_DONE_%=:\n}" ::"r"(
+            dn_smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// orders the CTA's earlier generic-proxy accesses (st.global of the trailing update, reads of the buffer about to be
+// overwritten) before the bulk copies the calling thread issues next
+__device__ __forceinline__ void dn_fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
 struct DnSmem {
     double* xs;      // [N] Newton iterate
     double* xr;      // [N] raw solution
     double* Pn;      // [N][kDnLDP] panel: positions k0.. (relative), columns k0..k0+NB-1; also scratch [N]
-    double* Us;      // [kDnNB][kDnCW] strip of U
+    double* Us;      // [2][kDnNB][kDnCW] strip of U, double-buffered (16-byte aligned: bulk-copy destination)
+    uint64_t* bar;   // [2] mbarriers of the two strip buffers
+    uint32_t* ph;    // [2] their current phase parity (uniform over the CTA; thread 0 flips it behind a barrier)
     double* redv;    // [8] per-warp pivot candidates / broadcast slot
     int32_t* redp;   // [8]
     int32_t* rowat;  // [N] position -> physical row
 };
 
 __host__ __device__ inline size_t dn_smem_bytes(int N) {
-    return (size_t)N * (8 + 8 + 8 * kDnLDP + 4) + (size_t)kDnNB * kDnCW * 8 + 8 * 8 + 8 * 4 + 64;
+    return (size_t)N * (8 + 8 + 8 * kDnLDP + 4) + (size_t)2 * kDnNB * kDnCW * 8 + 16 + 16 + 8 * 8 + 8 * 4 + 64;
 }
 __host__ __device__ inline int dn_ld(int N) { return (N + 1 + 3) & ~3; }  // row stride of [A | b], 32-byte multiple
 
@@ -73,11 +103,24 @@ __device__ __forceinline__ DnSmem dn_carve(unsigned char* base, int N) {
     s.xs = d;
     s.xr = d + N;
     s.Pn = d + 2 * N;
-    s.Us = s.Pn + (size_t)N * kDnLDP;
-    s.redv = s.Us + kDnNB * kDnCW;
+    s.Us = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(s.Pn + (size_t)N * kDnLDP) + 15) & ~(uintptr_t)15);
+    s.bar = reinterpret_cast<uint64_t*>(s.Us + 2 * kDnNB * kDnCW);
+    s.ph = reinterpret_cast<uint32_t*>(s.bar + 2);
+    s.redv = reinterpret_cast<double*>(s.bar + 3);
     s.redp = reinterpret_cast<int32_t*>(s.redv + 8);
     s.rowat = s.redp + 8;
     return s;
+}
+
+// once per kernel, after dn_carve: the strip buffers' mbarriers (one arrival each: the elected thread's expect_tx)
+__device__ __forceinline__ void dn_init_sync(const DnSmem& S, int tid) {
+    if (tid == 0) {
+        dn_mbar_init(&S.bar[0], 1);
+        dn_mbar_init(&S.bar[1], 1);
+        S.ph[0] = S.ph[1] = 0;
+        dn_fence_proxy_async();
+    }
+    __syncthreads();
 }
 
 // [A | b] := 0, then the ordered gather per slot (reference accumulation order)
@@ -200,15 +243,32 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
                 if (c < nb && c < r) A[(size_t)S.rowat[k0 + r] * LD + k0 + c] = S.Pn[r * kDnLDP + c];
             }
         // ---- columns right of the panel (the right-hand side, column N, included), kDnCW at a time
+        // Full panels: the strip rows travel by TMA (see above), block j0 + kDnCW while block j0 is being used; the
+        // last, partial panel (nb < 16: only column N is left, its address is not 16-byte aligned) loads them directly.
+        const bool tma = nb == kDnNB;
+        auto issue_strip = [&](int j0, int b) {  // thread 0 only; every earlier access to buffer b is behind a barrier
+            const int w = (N + 1 - j0 < kDnCW) ? N + 1 - j0 : kDnCW;
+            const unsigned bytes = (unsigned)((w + 1) & ~1) * 8u;  // (even count: LD pads every row to a multiple of 4)
+            dn_fence_proxy_async();
+            dn_mbar_expect_tx(&S.bar[b], bytes * kDnNB);
+            for (int t = 0; t < kDnNB; ++t)
+                dn_bulk_g2s(S.Us + ((size_t)b * kDnNB + t) * kDnCW, A + (size_t)S.rowat[k0 + t] * LD + j0, bytes, &S.bar[b]);
+        };
+        int buf = 0;
+        if (tma && tid == 0 && k0 + nb <= N) issue_strip(k0 + nb, 0);
         for (int j0 = k0 + nb; j0 <= N; j0 += kDnCW) {
+            double* Ub = S.Us + (size_t)buf * kDnNB * kDnCW;
+            if (tma) dn_mbar_wait(&S.bar[buf], S.ph[buf]);
             // strip of U: rows k0..k0+nb-1 of these columns, triangular solve against the panel's L (ascending k)
             if (tid < kDnCW) {
                 const int j = j0 + tid;
                 if (j <= N) {
-                    double* us = S.Us + tid;
+                    double* us = Ub + tid;
+                    if (!tma) {
 #pragma unroll
-                    for (int t = 0; t < kDnNB; ++t)  // independent loads first
-                        if (t < nb) us[t * kDnCW] = A[(size_t)S.rowat[k0 + t] * LD + j];
+                        for (int t = 0; t < kDnNB; ++t)  // independent loads first
+                            if (t < nb) us[t * kDnCW] = A[(size_t)S.rowat[k0 + t] * LD + j];
+                    }
 #pragma unroll 1
                     for (int t = 1; t < nb; ++t) {
                         double a = us[t * kDnCW];
@@ -223,6 +283,10 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
                 }
             }
             __syncthreads();
+            if (tma && tid == 0) {  // everyone is past the wait on this buffer and past the last use of the other one
+                S.ph[buf] ^= 1u;
+                if (j0 + kDnCW <= N) issue_strip(j0 + kDnCW, buf ^ 1);
+            }
             DN_T(2);
             // trailing update: rows at positions >= k0+nb (only reached with a full panel, nb == kDnNB)
             const int tx = tid & 31, ty = tid >> 5;
@@ -248,7 +312,7 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
 #pragma unroll
                     for (int r = 0; r < kDnRM; ++r) l[r] = S.Pn[prel[r] * kDnLDP + t];
 #pragma unroll
-                    for (int c = 0; c < kDnCN; ++c) u[c] = S.Us[t * kDnCW + tx + 32 * c];
+                    for (int c = 0; c < kDnCN; ++c) u[c] = Ub[t * kDnCW + tx + 32 * c];
 #pragma unroll
                     for (int r = 0; r < kDnRM; ++r)
 #pragma unroll
@@ -264,6 +328,7 @@ __device__ bool dn_lu_solve(double* __restrict__ A, int N, int LD, const DnSmem&
             }
             __syncthreads();
             DN_T(3);
+            buf ^= 1;
         }
     }
     __syncthreads();  // (a singular break leaves the pivot-search slots still being read)
@@ -403,6 +468,7 @@ tran_dense_kernel(DevPlan P, DevTran T, int64_t B, const double* __restrict__ pa
     const csim_constants& c = P.c;
     const int tid = threadIdx.x, N = P.N, LD = dn_ld(N);
     const DnSmem S = dn_carve(dn_smem, N);
+    dn_init_sync(S, tid);
     double* A = M.A + (size_t)blockIdx.x * N * LD;
     double* vt = M.vt + (size_t)blockIdx.x * m.n_values;
     for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
@@ -460,6 +526,7 @@ dc_dense_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double*
     const csim_constants& c = P.c;
     const int tid = threadIdx.x, N = P.N, LD = dn_ld(N);
     const DnSmem S = dn_carve(dn_smem, N);
+    dn_init_sync(S, tid);
     double* A = M.A + (size_t)blockIdx.x * N * LD;
     double* vt = M.vt + (size_t)blockIdx.x * m.n_values;
     int gmin_slot = -1;
@@ -535,6 +602,7 @@ lu_dense_kernel(int N, int64_t B, const double* __restrict__ Ain, const double* 
     extern __shared__ unsigned char dn_smem[];
     const int tid = threadIdx.x, LD = dn_ld(N);
     const DnSmem S = dn_carve(dn_smem, N);
+    dn_init_sync(S, tid);
     double* A = M.A + (size_t)blockIdx.x * N * LD;
     for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
         __syncthreads();

@@ -361,11 +361,16 @@ def lu_decompose(A):
     return LU, perm, bool(rc)
 
 
-def ladder_netlist(stages: int = 200, tstep: float = 1e-11, tstop: float = 2e-9) -> str:
+def ladder_netlist(stages: int = 200, tstep: float = 1e-11, tstop: float = 2e-9, vin_offset: float = 1.5,
+                   vin_ampl: float = 1.5) -> str:
     """BASELINE config 5: a chain of `stages` CMOS inverters, each driving an R-C section,
     written in the reference's netlist grammar.  Nodes: vdd, n0 (input), then o_i / n_{i+1} per stage;
-    N = 2*stages + 2 node equations + 2 branch equations (404 for 200 stages)."""
-    lines = ["* generated inverter / RC ladder", "VDD vdd 0 DC 3", "Vin n0 0 SIN 1.5 1.5 10e6 0"]
+    N = 2*stages + 2 node equations + 2 branch equations (404 for 200 stages).
+    vin_offset = 1.5 is the survey's netlist: the input sits at mid-rail at DC, every stage is at its high-gain
+    point and the reference's own fixed-damping DC ramp does not converge on it (status bits DC_UNCONVERGED,
+    LU_SINGULAR; reproduced by the oracle).  vin_offset = 0 biases the input at a rail: the stages alternate between the
+    rails and the same ramp converges — the variant reported next to it."""
+    lines = ["* generated inverter / RC ladder", "VDD vdd 0 DC 3", f"Vin n0 0 SIN {vin_offset:g} {vin_ampl:g} 10e6 0"]
     for i in range(stages):
         lines += [f"MP{i} o{i} n{i} vdd p 30e-6 0.35e-6 1", f"MN{i} o{i} n{i} 0 n 10e-6 0.35e-6 2",
                   f"R{i} o{i} n{i + 1} 100", f"C{i} n{i + 1} 0 10e-15"]
