@@ -38,7 +38,7 @@ EXPORTS = [
     "csim_dev_sstate", "csim_batch_sstate", "csim_plan_force_large_path", "csim_dev_harmonics", "csim_dev_gauss_seidel", "csim_host_gauss_seidel",
     "csim_dev_fp64_peak", "csim_dev_lu_factor", "csim_host_lu_factor", "csim_dev_lu_solve_noalloc", "csim_dev_selftest_tdiv_mul",
     "csim_multi_create", "csim_multi_destroy", "csim_multi_shard", "csim_multi_set_params", "csim_multi_dc", "csim_multi_tran",
-    "csim_multi_last_kernel_ms", "csim_set_last_error", "csim_plan_specialize_dc_variants", "csim_plan_dc_spec_info",
+    "csim_multi_last_kernel_ms", "csim_set_last_error", "csim_plan_specialize_dc_variants", "csim_plan_dc_spec_info", "csim_dev_margin_probe",
 ]
 
 
@@ -659,6 +659,12 @@ class Multi:
     @property
     def last_kernel_ms(self) -> float:
         return float(lib().csim_multi_last_kernel_ms(self.handle))
+
+
+def margin_probe(margin):
+    """csim_dev_margin_probe: margin = CUDA float64 tensor [B] initialised to +inf (or None to switch the probe off)."""
+    lib().csim_dev_margin_probe.argtypes = [C.c_void_p]
+    _check(lib().csim_dev_margin_probe(_ptr(margin)), "csim_dev_margin_probe")
 
 
 def fp64_peak(device: int = 0) -> float:

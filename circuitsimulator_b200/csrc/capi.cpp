@@ -24,6 +24,7 @@ using namespace csim;
 namespace {
 thread_local std::string g_err;
 thread_local const uint8_t* g_tran_skip = nullptr;  // per-instance skip mask of the steady-state driver
+thread_local double* g_margin = nullptr;  // csim_dev_margin_probe: [B] device buffer the generic kernels record threshold margins into
 thread_local bool g_generic_stamp_only = false;  // set while the pivot pilot runs (it holds the plan's JIT lock)
 int fail(int code, const std::string& msg) {
     g_err = msg;
@@ -898,7 +899,9 @@ int csim_dev_dc(const csim_plan* plan, int64_t B, const double* params, double* 
     if (use_big(plan) && use_dense(plan))
         CU(launch_dc_dense(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
     else if (use_big(plan)) CU(launch_dc_big(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream));
-    else {
+    else if (g_margin) {
+        CU(launch_dc(plan->dev, B, params, x, iters, pivot_hash, status, (cudaStream_t)stream, g_margin));
+    } else {
         // (kernel choice and launch under the plan's lock, as in csim_dev_tran)
         std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
         if (dc_prepare(plan, B, params, (cudaStream_t)stream))
@@ -969,13 +972,14 @@ int csim_dev_tran(const csim_plan* plan, int64_t B, const double* params, const 
     T.src_group_b = a->src_group_b;
     T.probes = d_pack + 2 * ns;
     T.skip = g_tran_skip;
+    T.margin = g_margin;
     cudaError_t e;
     // The learned kernel-selection state of the plan (which kernel, its module, statistics buffers) is guarded by
     // spec.mu from the choice to the launch: another host thread sharing the plan cannot rebuild or unload a kernel
     // between this thread's spec_prepare and its cudaLaunchKernel (launches themselves are asynchronous).
     std::unique_lock<std::recursive_mutex> plan_lock(plan->spec.mu, std::defer_lock);
     if (!big) plan_lock.lock();
-    const int kind = big ? -1 : spec_prepare(plan, B, params, x, a->dt, stream);
+    const int kind = big ? -1 : (g_margin ? 0 : spec_prepare(plan, B, params, x, a->dt, stream));
     if (big && use_dense(plan)) {
         e = launch_tran_dense(plan->dev, T, B, params, x, wave, iters_total, iters_step, pivot_hash, status, stream);
     } else if (big) {
@@ -1681,6 +1685,11 @@ int csim_dev_selftest_tdiv(int64_t n, const double* a, const double* b, double* 
                            void* stream) {
     if (n <= 0 || !a || !b || !q || !q_ref || !in_range) return fail(CSIM_E_INVALID, "csim_dev_selftest_tdiv: bad argument");
     CU(launch_tdiv_selftest(n, a, b, q, q_ref, in_range, (cudaStream_t)stream));
+    return CSIM_OK;
+}
+
+int csim_dev_margin_probe(double* margin) {
+    g_margin = margin;
     return CSIM_OK;
 }
 

@@ -45,6 +45,8 @@ struct DevTran {
     const int32_t* probes;       // [n_probes]
     const uint8_t* skip;         // [B] or nullptr: instances with skip[b] != 0 are left untouched (steady-state driver)
     unsigned long long* miss;    // thread-per-instance kernel: log of the permutations its redo path met, or nullptr
+    double* margin;              // [B] or nullptr (generic kernels only): min over every comparison of a step norm with a
+                                 // threshold of |err - threshold| / threshold (csim_dev_margin_probe)
 };
 
 // Device-side tables of a specialised kernel (built by specialize.cpp).

@@ -163,9 +163,13 @@ __device__ __forceinline__ double base_gmin(const csim_constants& c, double s) {
     return d_add(d_mul(c.gmin_high_base, d_sub(1.0, s)), d_mul(c.gmin_low_base, s));
 }
 
+// relative distance of a step norm from a threshold it is compared with (diagnostic of the one unpinned call, ||.||_2)
+__device__ __forceinline__ double rel_margin(double err, double thr) { return fabs(err - thr) / thr; }
+
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 dc_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double* __restrict__ xout,
-          int32_t* __restrict__ iters, uint64_t* __restrict__ pivot_hash, uint32_t* __restrict__ status) {
+          int32_t* __restrict__ iters, uint64_t* __restrict__ pivot_hash, uint32_t* __restrict__ status,
+          double* __restrict__ margin) {
     extern __shared__ double smem[];
     const DevMode& m = P.m[CSIM_MODE_DC];
     const csim_constants& c = P.c;
@@ -180,6 +184,7 @@ dc_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double* __res
 
     uint64_t h = pivot_hash ? pivot_hash[b] : CSIM_PIVOT_HASH_INIT;
     uint32_t st = 0;
+    double mg = CUDART_INF;
     double x = 0.0;  // lane i holds x(i)
     w.xs[lane] = 0.0;
     eval_static(m, params, B, b, 0.0, 0.0, w.vt, lane);
@@ -227,6 +232,13 @@ dc_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double* __res
                 const double err = warp_norm2(d_sub(xn, x));
                 const double gbase = base_gmin(c, scale);
                 double gnext = gbase;
+                if (margin) {  // every threshold this iteration compares err with
+                    mg = fmin(mg, rel_margin(err, c.dc_tol));
+                    if (!(iter == 0 || !lane_finite(prevErr))) {
+                        mg = fmin(mg, rel_margin(err, d_mul(prevErr, c.slow_conv_ratio)));
+                        if (!(err > d_mul(prevErr, c.slow_conv_ratio))) mg = fmin(mg, rel_margin(err, d_mul(prevErr, c.fast_conv_ratio)));
+                    }
+                }
                 if (!(iter == 0 || !lane_finite(prevErr))) {
                     if (err > d_mul(prevErr, c.slow_conv_ratio)) {
                         double g2 = d_mul(gmin, 2.0);
@@ -253,6 +265,7 @@ dc_kernel(DevPlan P, int64_t B, const double* __restrict__ params, double* __res
     if (lane == 0) {
         if (pivot_hash) pivot_hash[b] = h;
         if (status) status[b] |= st;
+        if (margin) margin[b] = fmin(margin[b], mg);
     }
 }
 
@@ -275,6 +288,7 @@ tran_kernel(DevPlan P, DevTran T, int64_t B, const double* __restrict__ params, 
     uint64_t h = pivot_hash ? pivot_hash[b] : CSIM_PIVOT_HASH_INIT;
     uint32_t st = 0;
     int total = 0;
+    double mg = CUDART_INF;
     double x = lane < N ? xio[(int64_t)lane * B + b] : 0.0;
     w.xs[lane] = x;
     eval_static(m, params, B, b, T.dt, c.tran_gmin, w.vt, lane);
@@ -310,6 +324,7 @@ tran_kernel(DevPlan P, DevTran T, int64_t B, const double* __restrict__ params, 
             __syncwarp();
             w.xs[lane] = x;
             __syncwarp();
+            if (T.margin) mg = fmin(mg, rel_margin(err, c.tran_tol));
             if (err < c.tran_tol) break;
             if (iter == c.tran_max_iters - 1) st |= CSIM_ST_TRAN_UNCONVERGED;
         }
@@ -326,6 +341,7 @@ tran_kernel(DevPlan P, DevTran T, int64_t B, const double* __restrict__ params, 
         if (iters_total) iters_total[b] += total;
         if (pivot_hash) pivot_hash[b] = h;
         if (status) status[b] |= st;
+        if (T.margin) T.margin[b] = fmin(T.margin[b], mg);
     }
 }
 
@@ -706,11 +722,11 @@ cudaError_t launch_lu_solve(int N, int64_t B, const double* A, const double* b, 
 }
 
 cudaError_t launch_dc(const DevPlan& P, int64_t B, const double* params, double* x, int32_t* iters,
-                      uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream) {
+                      uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream, double* margin) {
     size_t smem = newton_smem_bytes(P.m[CSIM_MODE_DC]);
     cudaFuncSetAttribute(dc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int64_t blocks = (B + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    dc_kernel<<<(unsigned)blocks, kWarpsPerBlock * 32, smem, stream>>>(P, B, params, x, iters, pivot_hash, status);
+    dc_kernel<<<(unsigned)blocks, kWarpsPerBlock * 32, smem, stream>>>(P, B, params, x, iters, pivot_hash, status, margin);
     return cudaGetLastError();
 }
 

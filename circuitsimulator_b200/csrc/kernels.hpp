@@ -18,7 +18,7 @@ cudaError_t launch_stamp_csr(const DevPlan& P, int mode, int64_t B, const double
 cudaError_t launch_lu_solve(int N, int64_t B, const double* A, const double* b, double* x, int32_t* perm,
                             int32_t* singular, double eps, cudaStream_t stream, double* lu_out = nullptr);
 cudaError_t launch_dc(const DevPlan& P, int64_t B, const double* params, double* x, int32_t* iters,
-                      uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream);
+                      uint64_t* pivot_hash, uint32_t* status, cudaStream_t stream, double* margin = nullptr);
 cudaError_t launch_tran(const DevPlan& P, const DevTran& T, int64_t B, const double* params, double* x, double* wave,
                         int32_t* iters_total, uint8_t* iters_step, uint64_t* pivot_hash, uint32_t* status,
                         cudaStream_t stream);

@@ -487,6 +487,18 @@ float csim_batch_last_kernel_ms(const csim_batch* batch);
 int csim_dev_fp64_peak(int device, double* tflops_mul_add);
 #endif
 
+/* Diagnostic of the one unpinned call on the path, Eigen's norm() (summation order defined in oracle/csim_norm2.h;
+ * SURVEY.md 8(c)): while `margin` ([B] doubles on the device, initialised to +inf by the caller) is set for the calling
+ * thread, csim_dev_dc and csim_dev_tran (N <= 32) run on the generic kernels and record per instance the smallest
+ *     |err - threshold| / threshold
+ * over every comparison of a Newton step norm with a threshold: err < tol (DC 1e-9, TRAN 1e-6) and the controller's
+ * err > 1.05 prevErr / err < 0.7 prevErr (src/dcanalysis.cpp:286-297, src/tanalisis.cpp:372).  A last-ulp difference in
+ * the norm can only flip a comparison whose margin is ~1e-16; results are bit-identical across kernel families, so the
+ * margins hold for all of them.  margin == NULL switches the probe off again.                                       */
+#ifndef __CUDACC_RTC__
+int csim_dev_margin_probe(double* margin);
+#endif
+
 /* ---- pivot-sequence hash (shared definition, host-callable) ------------- *
  * Every factorisation contributes f = sum_i mix(i, perm[i]) (mod 2^64) and the
  * running hash becomes h' = (h XOR f) * 0x100000001B3.  h starts at
