@@ -13,6 +13,7 @@
 #include "../../include/csim_b200.h"
 #include <cstdlib>
 #include <mutex>
+#include <unistd.h>
 
 #include "jit.hpp"
 #include "kernels.hpp"
@@ -108,6 +109,7 @@ struct csim_plan {
     mutable TpiState tpi;
     mutable TpiState tpi_dc;      // thread-per-instance DC kernel (csim_dc_tpi): same machinery, own variants and statistics
     mutable bool dc_tried = false;
+    uint64_t topo_hash = 0;  // FNV-1a of the topology arrays + constants: key of the on-disk variant cache
     int force_big = 0;  // 0: by size; 1: large path (dense kernels); 2: large path (sparse-skipping warp kernels)
 };
 
@@ -197,6 +199,52 @@ int spec_build(const csim_plan* plan, const std::vector<int32_t>& perm) {
     return CSIM_OK;
 }
 
+// ---- on-disk cache of learned pivot-order variants (opt-in: CSIM_PLAN_CACHE=<directory>) -----------------------------
+// The permutations a plan's kernels were last built with, per topology (hash of the csim_topology arrays and the
+// constants block) and kernel (tran / dc): a new plan of the same topology starts from them instead of the single
+// pilot prediction, so a one-shot user does not pay the learning launches again.  They are predictions like any other:
+// every factorisation still verifies the reference's pivot rule, a stale or foreign file can only cost redos.
+std::string cache_path(const csim_plan* plan, bool dc) {
+    const char* dir = std::getenv("CSIM_PLAN_CACHE");
+    if (!dir || !dir[0] || !plan->topo_hash) return "";
+    char name[64];
+    std::snprintf(name, sizeof name, "/csim_%016llx_%s.perms", (unsigned long long)plan->topo_hash, dc ? "dc" : "tran");
+    return std::string(dir) + name;
+}
+void cache_store(const csim_plan* plan, bool dc, const std::vector<std::vector<int32_t>>& perms) {
+    const std::string path = cache_path(plan, dc);
+    if (path.empty()) return;
+    const std::string tmp = path + ".tmp" + std::to_string((long long)getpid());
+    if (FILE* f = std::fopen(tmp.c_str(), "w")) {
+        std::fprintf(f, "%d %d\n", plan->host.N, (int)perms.size());
+        for (const auto& pm : perms) {
+            for (int32_t v : pm) std::fprintf(f, "%d ", v);
+            std::fprintf(f, "\n");
+        }
+        std::fclose(f);
+        std::rename(tmp.c_str(), path.c_str());
+    }
+}
+bool cache_load(const csim_plan* plan, bool dc, std::vector<std::vector<int32_t>>& perms) {
+    const std::string path = cache_path(plan, dc);
+    if (path.empty()) return false;
+    FILE* f = std::fopen(path.c_str(), "r");
+    if (!f) return false;
+    int n = 0, k = 0;
+    bool ok = std::fscanf(f, "%d %d", &n, &k) == 2 && n == plan->host.N && k >= 1 && k <= 16;
+    perms.assign(ok ? k : 0, std::vector<int32_t>(plan->host.N));
+    for (auto& pm : perms) {
+        std::vector<char> seen(plan->host.N, 0);
+        for (int32_t& v : pm) {
+            ok = ok && std::fscanf(f, "%d", &v) == 1 && v >= 0 && v < plan->host.N && !seen[v];
+            if (ok) seen[v] = 1;
+        }
+    }
+    std::fclose(f);
+    if (!ok) perms.clear();
+    return ok;
+}
+
 // Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bit 5: folded division guards, bit 6: opaque row parking; bits 8-9: replicas - 1, bits 12-14: warps per CTA, bits 16-19: rows in flight); unset = defaults.
 TpiOptions tpi_options_from_env() {
     TpiOptions opt;
@@ -280,6 +328,7 @@ int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& pe
              std::to_string(tp.host.n_g_adds) + "+" + std::to_string(tp.host.n_rhs_adds) + " assembly adds; longest dependency chain " +
              std::to_string(tp.host.crit_cycles) + " cycles" + tp.history + (log.size() > 1 ? "\n" + log : "");
     tp.ready = true;
+    cache_store(plan, dc, tp.host.perms);
     return CSIM_OK;
 }
 
@@ -429,6 +478,13 @@ int spec_prepare(const csim_plan* plan, int64_t B, const double* d_params, const
         sp.log = "not specialised: " + spec_unsupported_reason(plan->host);
         return 0;
     }
+    if (want == 3) {
+        std::vector<std::vector<int32_t>> cached;
+        if (cache_load(plan, false, cached) && tpi_build(plan, cached) == CSIM_OK) {
+            tp.history += "\n" + std::to_string(cached.size()) + " variant(s) from the plan cache";
+            return sp.kind = 3;
+        }
+    }
     std::vector<int32_t> perm;
     if (spec_pilot(plan, B, d_params, d_x, dt, stream, perm) != CSIM_OK) {
         sp.log = std::string("pilot failed: ") + csim_last_error();
@@ -481,6 +537,11 @@ bool dc_prepare(const csim_plan* plan, int64_t B, const double* d_params, cudaSt
     if (!plan->dc_tried) {
         plan->dc_tried = true;
         if (!spec_unsupported_reason(plan->host).empty()) return false;
+        std::vector<std::vector<int32_t>> cached;
+        if (cache_load(plan, true, cached) && tpi_build(plan, cached, true) == CSIM_OK) {
+            tp.history += "\n" + std::to_string(cached.size()) + " variant(s) from the plan cache";
+            return true;
+        }
         std::vector<int32_t> perm;
         if (dc_pilot(plan, B, d_params, stream, perm) != CSIM_OK) {
             tp.log = std::string("DC pilot failed: ") + csim_last_error();
@@ -703,6 +764,22 @@ int csim_plan_create(const csim_topology* topo, const csim_constants* consts, in
         p->host = build_host_plan(*topo, consts);
     } catch (const std::exception& e) {
         return fail(CSIM_E_INVALID, std::string("csim_plan_create: ") + e.what());
+    }
+    {
+        uint64_t hsh = 0xCBF29CE484222325ull;
+        auto mixin = [&](const void* data, size_t bytes) {
+            const unsigned char* c = static_cast<const unsigned char*>(data);
+            for (size_t i = 0; i < bytes; ++i) hsh = (hsh ^ c[i]) * 0x100000001B3ull;
+        };
+        const int32_t dims[4] = {topo->n_unknowns, topo->n_node_eq, topo->n_elems, topo->n_params};
+        mixin(dims, sizeof dims);
+        mixin(topo->elem_type, sizeof(int32_t) * topo->n_elems);
+        mixin(topo->elem_flags, sizeof(int32_t) * topo->n_elems);
+        mixin(topo->elem_nodes, sizeof(int32_t) * 4 * topo->n_elems);
+        mixin(topo->elem_branch, sizeof(int32_t) * topo->n_elems);
+        mixin(topo->elem_param, sizeof(int32_t) * topo->n_elems);
+        mixin(&p->host.consts, sizeof(csim_constants));
+        p->topo_hash = hsh ? hsh : 1;
     }
     p->device = device;
     if (device >= 0) {

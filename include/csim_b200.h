@@ -186,6 +186,10 @@ int csim_plan_specialize_variants(csim_plan* plan, int32_t n_variants, const int
  * operating regions, so the kernel collects predicted permutations (up to 16) over the first launches exactly like
  * the transient kernel.  csim_plan_specialize_dc_variants installs a set directly; csim_plan_dc_spec_info reports
  * whether the kernel is loaded, its variants, and solves redone generically / all solves since it was built.       */
+/* CSIM_PLAN_CACHE=<directory> (opt-in): the permutations a plan's thread-per-instance kernels were last built with are
+ * stored there per topology (hash of the csim_topology arrays and the constants block) and kernel; a new plan of the
+ * same topology starts from them instead of the single pilot prediction.  Predictions only: results cannot depend on
+ * the files, a stale or corrupt one is ignored or costs redos.                                                  */
 int csim_plan_specialize_dc_variants(csim_plan* plan, int32_t n_variants, const int32_t* perms);
 int csim_plan_dc_spec_info(const csim_plan* plan, int32_t* active, int32_t* n_variants, uint64_t* fallback_solves,
                            uint64_t* solves, char* log, int32_t log_cap);

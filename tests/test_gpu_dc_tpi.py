@@ -140,3 +140,41 @@ def test_dc_tpi_candidate_retry_recovers_from_a_wrong_variant_without_the_generi
     assert ib["fallback_solves"] <= ir["fallback_solves"] < ia["fallback_solves"], (ia, ir, ib)
     od = O.dc(topo, P[5])
     assert_same_bits(b["x"][:, 5].cpu().numpy(), od["x"], "instance 5 vs oracle")
+
+
+def test_plan_cache_hands_learned_variants_to_the_next_plan(torch, tmp_path, monkeypatch):
+    """CSIM_PLAN_CACHE=<dir>: the pivot-order variants a plan learned are stored per topology hash; a NEW plan of the same
+    topology starts with them (no learning launches, few redos on its first launch).  Results are unaffected."""
+    from circuitsimulator_b200 import capi
+    monkeypatch.setenv("CSIM_PLAN_CACHE", str(tmp_path))
+    g, topo = load_golden("buffer")
+    B, dt, ns = 3000, float(g["dt"]), 120
+    P = O.monte_carlo(topo, B, 20261104 + 3)
+    params = torch.from_numpy(np.ascontiguousarray(P.T)).cuda()
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    setup = capi.TranSetup(dt, ns, m, grp, tab, probes=np.array([8], np.int32))
+    first = make_plan(topo)
+    for _ in range(5):
+        d1 = capi.dc(first, params)
+        t1 = capi.tran(first, params, d1["x"].clone(), setup, pivot_hash=d1["hash"].clone(), status=d1["status"].clone())
+    torch.cuda.synchronize()
+    i_dc, i_tr = first.dc_spec_info(), first.spec_info()
+    assert i_dc["n_variants"] > 1 and "predicted permutation(s)" in i_tr["log"]
+    assert len(list(tmp_path.glob("csim_*_dc.perms"))) == 1 and len(list(tmp_path.glob("csim_*_tran.perms"))) == 1
+    second = make_plan(topo)
+    d2 = capi.dc(second, params)
+    t2 = capi.tran(second, params, d2["x"].clone(), setup, pivot_hash=d2["hash"].clone(), status=d2["status"].clone())
+    torch.cuda.synchronize()
+    j_dc, j_tr = second.dc_spec_info(), second.spec_info()
+    assert j_dc["n_variants"] == i_dc["n_variants"], (i_dc, j_dc)
+    assert j_dc["fallback_solves"] * 10 < j_dc["solves"]                      # its FIRST launch already runs on the variants
+    assert j_tr["log"].split(" predicted")[0].split()[-1] == i_tr["log"].split(" predicted")[0].split()[-1]
+    _same(d1, d2, "cached variants")
+    assert torch.equal(t1["hash"], t2["hash"]) and torch.equal(t1["x"].view(torch.int64), t2["x"].view(torch.int64))
+    # a corrupt file is ignored
+    for f in tmp_path.glob("*.perms"):
+        f.write_text("13 2\n0 0 0\n")
+    third = make_plan(topo)
+    d3 = capi.dc(third, params)
+    torch.cuda.synchronize()
+    _same(d1, d3, "corrupt cache ignored")
