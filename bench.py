@@ -482,8 +482,9 @@ def run_ours(args):
     tj = None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "tran_traffic.json")))
-        if tj.get("netlist") != args.netlist:
-            tj = None
+        if (tj.get("netlist") != args.netlist or int(tj.get("instances", -1)) != B or int(tj.get("timepoints", -1)) != n_steps
+                or int(tj.get("out_stride", -1)) != args.out_stride):
+            tj = None  # the capture is of another launch size
     except Exception:
         tj = None
     roofline = {"kernel": kname, "bound": "fp64", "achieved": tran_tflops, "peak": fp64_peak,
