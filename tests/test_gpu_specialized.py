@@ -358,3 +358,36 @@ def test_exact_tie_goes_to_the_row_the_reference_scans_first(torch, monkeypatch,
             assert_same_bits(wave[b].T, want[b]["wave"], f"perm {perm} inst {b}")
             assert np.array_equal(t["iters_step"][:, b].cpu().numpy(), want[b]["iters_step"])
             assert np.uint64(t["hash"][b].item() & 0xFFFFFFFFFFFFFFFF) == np.uint64(want[b]["hash"])
+
+
+def test_variants_are_added_between_the_chunks_of_a_resumed_transient(torch, monkeypatch):
+    """csim_batch_tran cuts a run into chunks of timepoints (CSIM_WAVE_CHUNKS); every chunk is a launch, so in automatic
+    mode the thread-per-instance kernel is re-evaluated — and rebuilt with one more predicted permutation — BETWEEN the
+    chunks of one run, with every lane's state (x, variant, hash, totals) carried across.  buffer.sp changes its pivot
+    order while its stages switch: the chunked run must equal the single-launch run and the oracle bit for bit."""
+    from circuitsimulator_b200 import capi
+    g, topo = load_golden("buffer")
+    B, dt, ns = 600, float(g["dt"]), n_steps_of(g)
+    P = perturb(topo.params, topo, B, 11)
+    m, grp, tab = O.make_source_tables(topo, topo.params, dt, ns)
+    setup = capi.TranSetup(dt, ns, m, grp, tab, probes=np.array([8, 1], np.int32))
+    outs, infos = [], []
+    for chunks in ("1", "6"):
+        monkeypatch.setenv("CSIM_WAVE_CHUNKS", chunks)
+        plan = make_plan(topo)  # automatic mode, fresh plan: starts with one variant
+        batch = capi.Batch(plan, B)
+        batch.set_params(P.T)
+        outs.append(batch.tran(setup, want_iters_step=True))
+        infos.append(plan.spec_info())
+    one, many = outs
+    for k in ("x_dc", "x_final", "wave"):
+        assert_same_bits(many[k], one[k], k)
+    for k in ("iters_total", "iters_step", "hash", "status"):
+        assert np.array_equal(many[k], one[k]), k
+    assert "1 predicted permutation(s)" in infos[0]["log"]           # one launch: no chance to adapt
+    assert "variant" in infos[1]["log"] and "added" in infos[1]["log"], infos[1]["log"]  # rebuilt between chunks
+    for b in (0, 7, B - 1):
+        od = O.dc(topo, P[b])
+        ot = O.tran(topo, P[b], dt, 0, ns, m, grp, tab, od["x"], pivot_hash=od["hash"])
+        assert_same_bits(many["wave"][b].T, ot["wave"][:, [8, 1]], f"instance {b} vs oracle")
+        assert many["hash"][b] == np.uint64(ot["hash"]) and many["iters_total"][b] == ot["total"]
