@@ -84,6 +84,12 @@ struct TpiState {
     TpiHost host_wide;
     JitKernel k_wide;
     int warps_per_sm_wide = 0;
+    // Two warps per 32 instances (TpiOptions::pair): shorter Newton iterations for batches that leave SM sub-partitions
+    // idle anyway.  Built on the first launch whose batch fits one wave of its CTAs (transient, one permutation).
+    bool pair_tried = false, pair_ready = false;
+    TpiHost host_pair;
+    JitKernel k_pair;
+    int groups_per_sm_pair = 0;
     unsigned long long* d_stats = nullptr;  // [2]: fallback solves, Newton solves
     unsigned long long* d_miss = nullptr;   // permutations met by the generic redo path (specialize.hpp kTpiMiss*)
     std::string history;                    // one line per variant added by the automatic mode
@@ -245,7 +251,7 @@ bool cache_load(const csim_plan* plan, bool dc, std::vector<std::vector<int32_t>
     return ok;
 }
 
-// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bit 5: folded division guards, bit 6: opaque row parking; bits 8-9: replicas - 1, bits 12-14: warps per CTA, bits 16-19: rows in flight); unset = defaults.
+// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bit 5: folded division guards, bit 6: opaque row parking; bits 8-9: replicas - 1, bits 12-14: warps per CTA, bits 16-19: rows in flight, bit 20: warp pair per 32 instances); unset = defaults.
 TpiOptions tpi_options_from_env() {
     TpiOptions opt;
     if (const char* env = std::getenv("CSIM_TPI_OPTS")) {
@@ -263,6 +269,7 @@ TpiOptions tpi_options_from_env() {
         opt.replicas = 1 + ((m >> 8) & 3);
         opt.warps_per_cta = (m >> 12) & 7;
         if ((m >> 16) & 15) opt.rows_in_flight = (m >> 16) & 15;
+        opt.pair = (m >> 20) & 1;
     }
     return opt;
 }
@@ -270,10 +277,12 @@ TpiOptions tpi_options_from_env() {
 // Generates, compiles and loads one variant of the thread-per-instance kernel specialised to `perm`.
 // warps_per_cta: 1, or 0 = the CTA width that packs most warps into an SM's shared memory.
 int tpi_build_variant(const csim_plan* plan, const std::vector<std::vector<int32_t>>& perms, int warps_per_cta,
-                      TpiHost& host, JitKernel& k, int& warps_per_sm, std::string& log, bool dc = false) {
+                      TpiHost& host, JitKernel& k, int& warps_per_sm, std::string& log, bool dc = false,
+                      bool pair = false) {
     jit_unload(k);
     TpiOptions opt = tpi_options_from_env();
     if (opt.warps_per_cta == 0) opt.warps_per_cta = warps_per_cta;
+    if (!std::getenv("CSIM_TPI_OPTS")) opt.pair = pair;  // (with the development mask set, its bit 20 decides)
     try {
         host = dc ? generate_dc_tpi(plan->host, perms, opt) : generate_tran_tpi(plan->host, perms, opt);
     } catch (const std::exception& e) {
@@ -291,7 +300,7 @@ int tpi_build_variant(const csim_plan* plan, const std::vector<std::vector<int32
     int ctas = 0;
     CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas, reinterpret_cast<const void*>(k.kernel), host.threads,
                                                      host.smem_bytes));
-    warps_per_sm = ctas * (host.threads / 32);
+    warps_per_sm = ctas * (host.inst_per_cta / (32 * host.replicas));  // groups of 32 x replicas instances resident per SM
     return CSIM_OK;
 }
 
@@ -303,8 +312,10 @@ int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& pe
     TpiState& tp = dc ? plan->tpi_dc : plan->tpi;
     tp.ready = false;
     tp.wide_tried = tp.wide_ready = false;
+    tp.pair_tried = tp.pair_ready = false;
     cudaDeviceSynchronize();  // see spec_build: running launches of the old kernels finish before they are unloaded
     jit_unload(tp.k_wide);
+    jit_unload(tp.k_pair);
     if (tp.d_stats) cudaFree(tp.d_stats);
     if (tp.d_miss) cudaFree(tp.d_miss);
     tp.d_stats = tp.d_miss = nullptr;
@@ -326,7 +337,12 @@ int tpi_build(const csim_plan* plan, const std::vector<std::vector<int32_t>>& pe
              std::to_string(tp.host.n_lu_divs) + " multipliers, " + std::to_string(tp.host.n_elim_updates) +
              " row updates, " + std::to_string(tp.host.n_back_terms) + " back-substitution terms, " +
              std::to_string(tp.host.n_g_adds) + "+" + std::to_string(tp.host.n_rhs_adds) + " assembly adds; longest dependency chain " +
-             std::to_string(tp.host.crit_cycles) + " cycles" + tp.history + (log.size() > 1 ? "\n" + log : "");
+             std::to_string(tp.host.crit_cycles) + " cycles" +
+             (tp.host.pair ? "; warp pair per 32 instances, " + std::to_string(tp.host.pair_events) +
+                                 " hand-overs per Newton iteration, LU cost model " + std::to_string(tp.host.pair_cost[0]) +
+                                 " -> " + std::to_string(tp.host.pair_cost[1]) + " / " + std::to_string(tp.host.pair_cost[2])
+                           : std::string()) +
+             tp.history + (log.size() > 1 ? "\n" + log : "");
     tp.ready = true;
     cache_store(plan, dc, tp.host.perms);
     return CSIM_OK;
@@ -361,6 +377,38 @@ bool tpi_use_wide(const csim_plan* plan, int64_t B) {
     const int64_t cap_w = (int64_t)tp.n_sms * tp.warps_per_sm_wide;
     const int64_t waves_w = (warps + cap_w - 1) / cap_w;
     return (double)waves_w * kTpiWidePenalty < (double)waves;
+}
+
+// true -> launch the warp-pair variant for a batch of B instances (builds it on first need).  B200, dbmixer, 8,192
+// instances (256 of 592 sub-partitions busy with one warp each): 5.21 us per Newton iteration against 6.16 us.  A batch
+// beyond one wave of its CTAs is better off with one warp per 32 instances (shared memory holds 2-3 pairs per SM
+// against 3-4 single warps).  CSIM_TPI_PAIR=0 turns it off.
+bool tpi_use_pair(const csim_plan* plan, int64_t B) {
+    TpiState& tp = plan->tpi;
+    std::lock_guard<std::recursive_mutex> lock(plan->spec.mu);
+    if (tp.host.perms.size() != 1 || tp.n_sms <= 0) return false;
+    if (const char* e = std::getenv("CSIM_TPI_PAIR"))
+        if (std::atoi(e) == 0) return false;
+    if (std::getenv("CSIM_TPI_OPTS")) return false;  // (development mask: tp.host itself is what the mask asks for)
+    if (!tp.pair_tried) {
+        if (B > (int64_t)tp.n_sms * 3 * 32) return false;  // cannot fit whatever the kernel needs: do not build yet
+        tp.pair_tried = true;
+        std::string log;
+        if (tpi_build_variant(plan, tp.host.perms, 2, tp.host_pair, tp.k_pair, tp.groups_per_sm_pair, log, false, true) == CSIM_OK &&
+            tp.host_pair.pair) {
+            tp.pair_ready = true;
+            tp.log += "\nwarp-pair variant: " + std::to_string(tp.host_pair.threads) + " threads per CTA for " +
+                      std::to_string(tp.host_pair.inst_per_cta) + " instances, " + std::to_string(tp.host_pair.n_slots) +
+                      " shared doubles per instance, " + std::to_string(tp.host_pair.pair_events) +
+                      " hand-overs per Newton iteration (LU cost model " + std::to_string(tp.host_pair.pair_cost[0]) + " -> " +
+                      std::to_string(tp.host_pair.pair_cost[1]) + " / " + std::to_string(tp.host_pair.pair_cost[2]) + "), " +
+                      std::to_string(tp.groups_per_sm_pair) + " groups of 32 instances resident per SM";
+        } else {
+            jit_unload(tp.k_pair);
+        }
+    }
+    if (!tp.pair_ready) return false;
+    return B <= (int64_t)tp.n_sms * tp.groups_per_sm_pair * 32;
 }
 
 // Pivot order the reference's LU picks for instance 0 of the batch at its current state: one TRAN
@@ -611,7 +659,7 @@ cudaError_t dc_tpi_launch(const csim_plan* plan, int64_t B, const double* params
     unsigned long long* stats = tp.d_stats;
     void* args[] = {&P, &Tc, &Bll, &params, &x, &wave, &iters, &iters_step, &pivot_hash, &status, &scratch, &stats};
     const TpiHost& H = tp.host;
-    const int64_t per_cta = (int64_t)H.threads * H.replicas;
+    const int64_t per_cta = H.inst_per_cta;
     const unsigned blocks = (unsigned)((B + per_cta - 1) / per_cta);
     return cudaLaunchKernel(reinterpret_cast<const void*>(tp.k.kernel), dim3(blocks), dim3(H.threads), args, H.smem_bytes,
                             stream);
@@ -694,13 +742,14 @@ cudaError_t tpi_launch(const csim_plan* plan, const DevTran& T, int64_t B, const
     unsigned long long* stats = tp.d_stats;
     Tc.miss = tp.d_miss;
     void* args[] = {&P, &Tc, &Bll, &params, &x, &wave, &iters_total, &iters_step, &pivot_hash, &status, &scratch, &stats};
-    const bool wide = tpi_use_wide(plan, B);
-    const TpiHost& H = wide ? tp.host_wide : tp.host;
+    const bool pair = tpi_use_pair(plan, B);
+    const bool wide = !pair && tpi_use_wide(plan, B);
+    const TpiHost& H = pair ? tp.host_pair : wide ? tp.host_wide : tp.host;
     const int T_ = H.threads;
-    const int64_t per_cta = (int64_t)T_ * H.replicas;
+    const int64_t per_cta = H.inst_per_cta;
     const unsigned blocks = (unsigned)((B + per_cta - 1) / per_cta);
-    e = cudaLaunchKernel(reinterpret_cast<const void*>((wide ? tp.k_wide : tp.k).kernel), dim3(blocks), dim3(T_), args,
-                         H.smem_bytes, stream);
+    e = cudaLaunchKernel(reinterpret_cast<const void*>((pair ? tp.k_pair : wide ? tp.k_wide : tp.k).kernel), dim3(blocks),
+                         dim3(T_), args, H.smem_bytes, stream);
     cudaFreeAsync(scratch, stream);
     return e;
 }
@@ -848,6 +897,7 @@ void csim_plan_destroy(csim_plan* plan) {
         jit_unload(plan->spec.k);
         jit_unload(plan->tpi.k);
         jit_unload(plan->tpi.k_wide);
+        jit_unload(plan->tpi.k_pair);
         if (plan->tpi.d_stats) cudaFree(plan->tpi.d_stats);
         if (plan->tpi.d_miss) cudaFree(plan->tpi.d_miss);
         jit_unload(plan->tpi_dc.k);

@@ -48,6 +48,10 @@ struct TpiHost {
     std::vector<uint64_t> hashes;              // pivot-hash contribution of each variant's permutation
     std::string source;  // entry: csim_tran_tpi
     int32_t threads = 32, replicas = 1, n_slots = 0, n_scratch_rows = 0;
+    int32_t inst_per_cta = 32;  // instances one CTA advances: threads x replicas, or 32 with a warp PAIR per 32 instances
+    bool pair = false;          // two warps per 32 instances (TpiOptions::pair)
+    int32_t pair_events = 0;    // cross-warp hand-overs per Newton iteration (named barriers)
+    int32_t pair_cost[3] = {0, 0, 0};  // cost model: LU phase of one warp alone, and of the master / helper warp of the pair
     size_t smem_bytes = 0;
     uint32_t hash_lo = 0, hash_hi = 0;
     // statistics of the generated code (per Newton iteration, per instance)
@@ -70,6 +74,13 @@ struct TpiOptions {
     int rows_in_flight = 2;      // matrix rows whose elimination chains are interleaved in the generated source (B200, dbmixer: 1 -> 111.4, 2 -> 113.9, 3 -> 113.4, 4 -> slower; M instance-timepoints/s)
     int warps_per_cta = 0;       // 0 = whatever packs most warps into an SM's shared memory (1, 2 or 4)
     int replicas = 1;            // instances advanced together by one thread (interleaved instruction streams)
+    // Two warps per 32 instances (transient kernel, one predicted permutation): lane l of the MASTER warp runs the
+    // Newton loop of instance l as before but leaves part of the matrix rows (and the MOSFET linearisations only they
+    // need) to lane l of the HELPER warp; parked rows cross through the shared-memory slots they already live in,
+    // ordered by named barriers (bar.arrive / bar.sync).  Which warp computes a row changes no operand and no
+    // operation order: bit-identical.  Why: one warp per SM sub-partition is bound by its own dependency stalls
+    // (1.77 stall cycles per issue), and shared memory, not registers, caps residency at 3-4 warps per SM.
+    bool pair = false;
 };
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt = TpiOptions());
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms,

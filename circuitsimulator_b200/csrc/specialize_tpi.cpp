@@ -16,6 +16,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <map>
 #include <set>
 #include <sstream>
@@ -174,6 +175,132 @@ Val mul(const Val& a, const Val& b) {
     return Val::E("d_mul(" + a.e + ", " + b.e + ")", std::max(a.t, b.t) + kLatOp, a.z || b.z);
 }
 
+// ---- warp pair (TpiOptions::pair): which of the two warps computes which matrix row, and in which order ------------
+// Cost model in cycles of one warp alone on its sub-partition, fitted to the static stall sums of the generated
+// dbmixer kernel per row (tools/sass_phases.py ... rows): assembly 5 + 3 per term, one elimination step 14 + 4 per
+// updated entry (right-hand side included), parking 20 + 3 per U entry, one MOSFET linearisation 180; a hand-over
+// between the warps (bar.arrive -> released bar.sync) 40.
+constexpr int kPairMos = 180;
+int kPairSync = 40;       // (development aid: CSIM_PAIR_SYNC / CSIM_PAIR_EVENTS override these two)
+// named barriers of a CTA: 0 unused, 1 = iteration start, 2 = helper done, 3 = next iterate at the MOSFET terminals,
+// 4..15 = hand-overs
+int kPairMaxEvents = 12;
+
+struct PairModel {
+    int N = 0, W = 1;  // W: rows in flight per warp
+    std::vector<int> asm_cost, park_cost;
+    std::vector<std::vector<std::pair<int, int>>> steps;  // per row: (k, cost) ascending k
+    std::vector<std::vector<int>> mos;                    // per row: MOSFETs whose linearisation its assembly reads
+    int n_mos = 0;
+};
+struct PairAct {
+    enum Kind { ASM, STEP, PARK, WAIT } kind;
+    int role, row, k;  // WAIT: row = the producing warp, k = its park position; PARK: k = park position of the row
+};
+struct PairSchedule {
+    std::vector<PairAct> acts;  // in an order in which every needed row is parked before its use
+    std::set<std::pair<int, int>> handovers;  // (producing warp, park position) followed by an arrive
+    int t[2] = {0, 0};
+    int makespan() const { return std::max(t[0], t[1] + kPairSync); }
+};
+// List scheduling of the two instruction streams: the warp whose modelled clock is behind emits its next segment
+// (its open rows round-robin, as the single-warp generator interleaves them).  A step that needs a row of the other
+// warp waits for a hand-over — the latest one the other warp has reached by then, so later needs are covered too.
+// Every wait points backwards in the emitted order and each stream is a subsequence of it: no circular wait.
+PairSchedule pair_schedule(const PairModel& M, const std::vector<int>& owner) {
+    PairSchedule S;
+    std::vector<char> need[2] = {std::vector<char>(M.n_mos, 0), std::vector<char>(M.n_mos, 0)};
+    for (int i = 0; i < M.N; ++i)
+        for (int m : M.mos[i]) need[owner[i]][m] = 1;
+    for (int r = 0; r < 2; ++r)
+        for (char c : need[r]) S.t[r] += c ? kPairMos : 0;
+    struct Open {
+        int row;
+        size_t next = 0;
+        bool assembled = false;
+    };
+    std::vector<Open> open[2];
+    std::vector<int> queue[2];
+    size_t qnext[2] = {0, 0}, cursor[2] = {0, 0};
+    for (int i = 0; i < M.N; ++i) queue[owner[i]].push_back(i);
+    std::vector<int> T(M.N, -1), pos(M.N, -1);
+    std::vector<int> Tpos[2];
+    int waited[2] = {0, 0};
+    auto pending = [&](int r) { return qnext[r] < queue[r].size() || !open[r].empty(); };
+    while (pending(0) || pending(1)) {
+        bool done = false;
+        const int first = (pending(0) && (!pending(1) || S.t[0] <= S.t[1])) ? 0 : 1;
+        for (int pass = 0; pass < 2 && !done; ++pass) {
+            const int r = pass ? 1 - first : first;
+            if (!pending(r)) continue;
+            std::vector<Open>& op = open[r];
+            while (op.size() < (size_t)M.W && qnext[r] < queue[r].size()) op.push_back(Open{queue[r][qnext[r]++]});
+            for (size_t n = 0; n < op.size() && !done; ++n) {
+                const size_t idx = (cursor[r] + n) % op.size();
+                Open& R = op[idx];
+                if (!R.assembled) {
+                    S.acts.push_back({PairAct::ASM, r, R.row, -1});
+                    S.t[r] += M.asm_cost[R.row];
+                    R.assembled = true;
+                    cursor[r] = idx + 1;
+                    done = true;
+                } else if (R.next < M.steps[R.row].size()) {
+                    const int k = M.steps[R.row][R.next].first;
+                    if (T[k] < 0) continue;  // not parked yet (a lower row, still open in one of the streams)
+                    if (owner[k] != r && pos[k] >= waited[r]) {
+                        const int o = 1 - r, ready = std::max(S.t[r], T[k] + kPairSync);
+                        int q = pos[k];
+                        while (q + 1 < (int)Tpos[o].size() && Tpos[o][q + 1] + kPairSync <= ready) ++q;
+                        waited[r] = q + 1;
+                        S.handovers.insert({o, q});
+                        S.acts.push_back({PairAct::WAIT, r, o, q});
+                        S.t[r] = ready;
+                    }
+                    S.acts.push_back({PairAct::STEP, r, R.row, k});
+                    S.t[r] += M.steps[R.row][R.next].second;
+                    ++R.next;
+                    cursor[r] = idx + 1;
+                    done = true;
+                } else {
+                    S.t[r] += M.park_cost[R.row];
+                    T[R.row] = S.t[r];
+                    pos[R.row] = (int)Tpos[r].size();
+                    Tpos[r].push_back(S.t[r]);
+                    S.acts.push_back({PairAct::PARK, r, R.row, pos[R.row]});
+                    op.erase(op.begin() + (long)idx);
+                    cursor[r] = idx;
+                    done = true;
+                }
+            }
+        }
+        if (!done) throw std::runtime_error("specialize: pair schedule made no progress");
+    }
+    return S;
+}
+// hill climbing from "everything on the master" over moves of one row or one contiguous run of rows
+std::vector<int> pair_partition(const PairModel& M) {
+    std::vector<int> owner(M.N, 0);
+    auto score = [&](const std::vector<int>& ow) {
+        const PairSchedule s = pair_schedule(M, ow);
+        return (int)s.handovers.size() > kPairMaxEvents ? 1 << 30 : s.makespan();
+    };
+    int cur = score(owner);
+    for (int round = 0; round < 2 * M.N; ++round) {
+        int best = cur, bi = -1, bj = -1;
+        for (int i = 0; i < M.N; ++i)
+            for (int j = i; j < M.N; ++j) {
+                for (int t = i; t <= j; ++t) owner[t] ^= 1;
+                const int sc = score(owner);
+                if (sc < best) best = sc, bi = i, bj = j;
+                for (int t = i; t <= j; ++t) owner[t] ^= 1;
+            }
+        if (bi < 0) break;
+        for (int t = bi; t <= bj; ++t) owner[t] ^= 1;
+        cur = best;
+    }
+    return owner;
+}
+
 }  // namespace
 
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt) {
@@ -326,19 +453,91 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         for (const MosOp& m : mp.mos_ops)
             for (int t = 0; t < 3; ++t)
                 if (!prm_slot.count(m.param + t)) prm_slot[m.param + t] = alloc();
+    bool pair_mos = false;  // warp pair: the helper linearises every MOSFET ahead of the iteration, values in shared memory
     auto val = [&](int v) -> Val {  // per-iteration operand
         if (is_const[v]) return Val::K(const_val[v]);
         if (kind[v] == GMINV) return Val::E("gmin@");
         if (kind[v] == MOS)  // (gm is exactly zero while the device is off: src/element.cpp:240-247)
-            return opt.mos_in_smem ? Val::E(S(mos_slot.at(v)), kLatMos + kLatSmem, mos_gm.count(v) > 0)
+            return pair_mos        ? Val::E(S(mos_slot.at(v)), kLatSmem, mos_gm.count(v) > 0)
+                   : opt.mos_in_smem ? Val::E(S(mos_slot.at(v)), kLatMos + kLatSmem, mos_gm.count(v) > 0)
                                    : Val::E("m" + std::to_string(v) + "@", kLatMos, mos_gm.count(v) > 0);
         return Val::E(S(val_slot.at(v)));
     };
 
 
     const int R = std::max(1, opt.replicas);
+    // ---- warp pair: row ownership (0 = master, 1 = helper) and the two hand-shake slots ---------------------------------
+    const bool PAIR = opt.pair && K == 1 && !DC && R == 1 && opt.x_in_smem && !opt.opaque_park && !opt.mos_in_smem && !opt.q_in_smem;
+    std::vector<int> owner(N, 0);
+    std::vector<int> mos_of_value(mp.n_values, -1);
+    for (size_t m = 0; m < mp.mos_ops.size(); ++m)
+        for (int t = 0; t < 4; ++t) mos_of_value[mp.mos_ops[m].out + t] = (int)m;
+    std::vector<char> mos_need[2] = {std::vector<char>(mp.mos_ops.size(), 1), std::vector<char>(mp.mos_ops.size(), 0)};
+    std::map<int, int> cand_slot;  // unknown -> slot of the NEXT iterate's value at a MOSFET terminal
+    int CMD = -1, HB = -1;  // CMD, CMD + 1: the masters' command words of even / odd rounds
+    PairSchedule pair_plan;
+    if (PAIR) {
+        const Analysis& A = As[0];
+        PairModel M;
+        M.N = N;
+        M.n_mos = 0;  // (the helper linearises all MOSFETs between the iterations, below)
+        M.W = std::max(1, opt.rows_in_flight);
+        M.asm_cost.assign(N, 5);
+        M.park_cost.assign(N, 20);
+        M.steps.resize(N);
+        M.mos.resize(N);
+        for (int i = 0; i < N; ++i) {
+            std::set<int> ms;
+            for (int j = 0; j <= N; ++j)
+                for (const Term& t : A.rest[i][j]) {
+                    if (is_const[t.value]) continue;
+                    M.asm_cost[i] += 3;
+                }
+            M.mos[i].assign(ms.begin(), ms.end());
+            M.park_cost[i] += 3 * (int)A.ucols[i].size();
+            for (int k = 0; k < i; ++k)
+                if (A.pat[i][k]) M.steps[i].push_back({k, 14 + 4 * ((int)A.cols_k[k].size() + 1)});
+        }
+        if (const char* e = std::getenv("CSIM_PAIR_SYNC")) kPairSync = std::atoi(e);
+        if (const char* e = std::getenv("CSIM_PAIR_EVENTS")) kPairMaxEvents = std::min(12, std::atoi(e));
+        owner = pair_partition(M);
+        if (const char* e = std::getenv("CSIM_PAIR_ROWS")) {  // development aid: the helper's rows, comma separated
+            std::fill(owner.begin(), owner.end(), 0);
+            for (const char* c = e; *c;) {
+                const int r = std::atoi(c);
+                if (r >= 0 && r < N) owner[r] = 1;
+                while (*c && *c != ',') ++c;
+                if (*c == ',') ++c;
+            }
+        }
+        pair_plan = pair_schedule(M, owner);
+        H.pair_cost[0] = pair_schedule(M, std::vector<int>(N, 0)).t[0];
+        H.pair_cost[1] = pair_plan.t[0];
+        H.pair_cost[2] = pair_plan.t[1];
+        if (std::getenv("CSIM_PAIR_DEBUG")) {
+            std::fprintf(stderr, "pair: model single %d, master %d, helper %d, hand-overs %d; helper rows:", H.pair_cost[0], H.pair_cost[1], H.pair_cost[2], (int)pair_plan.handovers.size());
+            for (int i = 0; i < N; ++i) if (owner[i]) std::fprintf(stderr, " %d", i);
+            std::fprintf(stderr, "\n");
+        }
+        for (int r = 0; r < 2; ++r) std::fill(mos_need[r].begin(), mos_need[r].end(), 0);
+        pair_mos = true;
+        for (const MosOp& m : mp.mos_ops) {
+            for (int t = 0; t < 4; ++t) mos_slot[m.out + t] = alloc();
+            for (int node : {m.d, m.g, m.s})
+                if (node >= 0 && !cand_slot.count(node)) cand_slot[node] = alloc();
+        }
+        CMD = alloc();
+        alloc();
+        HB = alloc();
+        H.pair = true;
+    }
     std::ostringstream o;  // kernel body after the prologue, written for one replica ('@' placeholders)
-    o << "    const long long b@ = (long long)blockIdx.x * (TPB * NREP) + @R * TPB + tid;\n"
+    std::ostringstream oh_mos, oh_rows;  // warp pair: the helper's share of a Newton iteration
+    std::ostringstream* row_out = &o;    // where the row generators below write
+#define O (*row_out)
+    if (PAIR) o << "    const long long b@ = (long long)blockIdx.x * (32 * PAIRS) + (tid >> 6) * 32 + LTID;\n";
+    else o << "    const long long b@ = (long long)blockIdx.x * (LANES * NREP) + @R * LANES + LTID;\n";
+    o << ""
          "    const bool live@ = b@ < B && !(T.skip && T.skip[b@ < B ? b@ : B - 1]);\n"
          "    const long long bb@ = b@ < B ? b@ : B - 1;  // idle lanes shadow an instance and never store\n"
          "    unsigned long long h@ = (live@ && pivot_hash) ? pivot_hash[b@] : CSIM_PIVOT_HASH_INIT;\n"
@@ -346,7 +545,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
          "    int total@ = 0;\n"
          "    bool dead@ = !live@, degen@ = false;\n";
     if (K > 1) o << "    int var@ = 0;  // variant (predicted permutation) that held for this lane's last solve\n";
-    o << "";
+    if (PAIR) o << "//%HELPER%\n";
     for (int i = 0; i < N; ++i) {
         const std::string x0 = DC ? std::string("0.0")  // x.setZero(N), src/dcanalysis.cpp:110
                                   : "xio[(long long)" + std::to_string(i) + " * B + bb@]";
@@ -396,9 +595,13 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
               << ", scale);\n";
         }
     } else {
+    if (PAIR) {
+        for (const auto& kv : cand_slot) o << "    " << S(kv.second) << " = " << xrd(kv.first) << ";\n";
+        o << "    PAIR_ARRIVE(3);  // the helpers linearise the MOSFETs at the start iterate\n";
+    }
     o << "    const int r0 = T.out_begin_step / T.out_stride;\n"
          "    for (int step = T.step_begin; step < T.step_end; ++step) {\n"
-         "        if (__all_sync(0xFFFFFFFFu, ALL(dead@))) break;\n";
+      << (PAIR ? "" : "        if (__all_sync(0xFFFFFFFFu, ALL(dead@))) break;\n");  // (warp pairs of a CTA stay in step)
     // ---- per step: x_prev -> scratch, companion history terms, source values -------------------------
     for (int i = 0; i < N; ++i)
         o << "        if (live@) scratch[(long long)" << (XP0 + i) << " * B + b@] = " << xrd(i) << ";\n";
@@ -423,20 +626,46 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     o << "        int count@ = 0;\n"
          "        bool done@ = dead@;\n"
          "        for (int iter = 0; iter < " << max_iters << "; ++iter) {\n"
-         "            if (__all_sync(0xFFFFFFFFu, ALL(done@))) break;\n"
-         "            bool bad@ = degen@;\n"
+      << (PAIR ? "            // the masters of the CTA decide together (their warps share the named barriers); what they publish —\n"
+                 "            // iterate, step values, static sums — is in shared memory before the barrier releases the helpers\n"
+                 "            SMG(" + std::to_string(CMD) + " + par, tid >> 6) = __all_sync(0xFFFFFFFFu, done@) ? 2.0 : 1.0;\n"
+                 "            PAIR_SYNC(1);\n"
+                 "            if (pair_cmd(sm, " + std::to_string(CMD) + " + par, LTID) == 2.0) { par ^= 1; break; }\n"
+                 "            par ^= 1;\n"
+               : "            if (__all_sync(0xFFFFFFFFu, ALL(done@))) break;\n")
+      << "            bool bad@ = degen@;\n"
          "            unsigned int glo@ = 0xFFFFFFFFu, ghi@ = 0u, gacc@ = 0u, pmx@ = 0u, dacc@ = 0u;\n";
     // ---- MOSFET linearisation -------------------------------------------------------------------------
-    for (const MosOp& op : mp.mos_ops) {
+    // (warp pair: each warp linearises the MOSFETs the rows it owns read — both of them where both need one)
+    // (warp pair: the helper linearises every MOSFET for the NEXT iteration while the master is busy with norm and
+    // convergence test — from the damped iterate the master leaves at the MOSFET terminals — so neither warp has the
+    // linearisations on its path; see the damping block below)
+    if (PAIR)
+        for (const MosOp& op : mp.mos_ops) {
+            auto mn = [&](int t) { return "m" + std::to_string(op.out + t) + "@"; };
+            auto cand = [&](int node) { return node < 0 ? std::string("0.0") : S(cand_slot.at(node)); };
+            oh_mos << "            {\n                double " << mn(0) << ", " << mn(1) << ", " << mn(2) << ", " << mn(3) << ";\n"
+                   << "                " << (opt.mos_branchless ? "mos_eval_sel" : "mos_eval_pp") << "<" << (op.is_p ? -1 : 1) << ">(PRM("
+                   << op.param << ", bb@), PRM(" << op.param + 1 << ", bb@), PRM(" << op.param + 2 << ", bb@), " << lit(C.mos_off_gds)
+                   << ", " << cand(op.d) << ", " << cand(op.g) << ", " << cand(op.s) << ", " << mn(0) << ", " << mn(1) << ", " << mn(2)
+                   << ", " << mn(3) << ");\n";
+            for (int t = 0; t < 4; ++t) oh_mos << "                " << S(mos_slot.at(op.out + t)) << " = " << mn(t) << ";\n";
+            oh_mos << "            }\n";
+        }
+    for (size_t mi = 0; mi < mp.mos_ops.size(); ++mi)
+    for (int role = 0; role < 1; ++role) {
+        if (!mos_need[role][mi]) continue;
+        const MosOp& op = mp.mos_ops[mi];
+        std::ostringstream& om = o;
         auto prm = [&](int k) { return opt.mos_in_smem ? S(prm_slot.at(k)) : "PRM(" + std::to_string(k) + ", bb@)"; };
         auto mn = [&](int t) { return "m" + std::to_string(op.out + t) + "@"; };
-        o << "            double " << mn(0) << ", " << mn(1) << ", " << mn(2) << ", " << mn(3) << ";\n"
+        om << "            double " << mn(0) << ", " << mn(1) << ", " << mn(2) << ", " << mn(3) << ";\n"
           << "            " << (opt.mos_branchless ? "mos_eval_sel" : "mos_eval_pp") << "<" << (op.is_p ? -1 : 1) << ">("
           << prm(op.param) << ", " << prm(op.param + 1) << ", " << prm(op.param + 2) << ", " << lit(C.mos_off_gds) << ", "
           << xrd(op.d) << ", " << xrd(op.g) << ", " << xrd(op.s) << ", " << mn(0) << ", " << mn(1) << ", " << mn(2) << ", "
           << mn(3) << ");\n";
         if (opt.mos_in_smem)
-            for (int t = 0; t < 4; ++t) o << "            " << S(mos_slot[op.out + t]) << " = " << mn(t) << ";\n";
+            for (int t = 0; t < 4; ++t) om << "            " << S(mos_slot[op.out + t]) << " = " << mn(t) << ";\n";
     }
     // ---- rows: assemble, eliminate, park ----------------------------------------------------------------
     // A row is emitted in SEGMENTS — assembly, one elimination step per earlier pivot row k with a structural
@@ -519,10 +748,10 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         if (d.c && d.v == -1.0) return neg(a);
         if (a.c && d.c) return Val::K(a.v / d.v);
         if (opt.fold_guards && !a.z)
-            o << ind << "const double " << tmp << " = " << (mult && !CAND ? "tdiv_mul(" : "tdiv_nz(") << a.e << ", " << d.e
+            O << ind << "const double " << tmp << " = " << (mult && !CAND ? "tdiv_mul(" : "tdiv_nz(") << a.e << ", " << d.e
               << ", " << RDv[k].e << ", gacc@" << (mult && !CAND ? ", pmx@" : "") << ");\n";
         else
-            o << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo@, ghi@);\n";
+            O << ind << "const double " << tmp << " = tdiv(" << a.e << ", " << d.e << ", " << RDv[k].e << ", glo@, ghi@);\n";
         H.n_lu_divs++;
         return Val::E(tmp, std::max(a.t, RDv[k].t) + kLatDiv, a.z);
     };
@@ -543,13 +772,13 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
             return;
         }
         if (v.e == name) return;
-        o << ind << (R.declared.count(j) ? "" : "double ") << name << " = " << v.e << ";\n";
+        O << ind << (R.declared.count(j) ? "" : "double ") << name << " = " << v.e << ";\n";
         R.declared.insert(j);
         R.row[j] = Val::E(name, v.t, v.z);
     };
     auto emit_assembly = [&](RowGen& R) {
         const int i = R.i;
-        o << ind << "// position " << i << " = row " << perm[i] << "\n";
+        O << ind << "// position " << i << " = row " << perm[i] << "\n";
         for (int j = 0; j <= N; ++j) {
             if (j < N && !A.pat[i][j]) continue;
             Val acc = j < N ? base[i][j] : Val::K(0.0);
@@ -571,12 +800,12 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
             // judged on the quotient by tdiv_mul (|f| >= 1 on the high word: never misses, ties included)
         } else if (a.c && Dv[k].c) {
             if (std::fabs(a.v) > std::fabs(Dv[k].v) || (tie_loses && std::fabs(a.v) == std::fabs(Dv[k].v)))
-                o << ind << (CAND ? "kf@ = min(kf@, " + std::to_string(k) + ");\n" : std::string("bad@ = true;\n"));
+                O << ind << (CAND ? "kf@ = min(kf@, " + std::to_string(k) + ");\n" : std::string("bad@ = true;\n"));
         } else if (CAND) {
-            o << ind << "if (fabs(" << a.e << ") " << (tie_loses ? ">=" : ">") << " "
+            O << ind << "if (fabs(" << a.e << ") " << (tie_loses ? ">=" : ">") << " "
               << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")") << ") kf@ = min(kf@, " << k << ");\n";
         } else {
-            o << ind << "bad@ = bad@ || (fabs(" << a.e << ") " << (tie_loses ? ">=" : ">") << " "
+            O << ind << "bad@ = bad@ || (fabs(" << a.e << ") " << (tie_loses ? ">=" : ">") << " "
               << (Dv[k].c ? fabs_lit(Dv[k].v) : "fabs(" + Dv[k].e + ")") << ");\n";
         }
         std::snprintf(num, sizeof num, "f%d_%d@", i, k);
@@ -597,7 +826,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     };
     auto park = [&](int slot, const std::string& value) {
         if (opt.opaque_park) park_list.push_back({slot, value});
-        else o << ind << S(slot) << " = " << value << ";\n";
+        else O << ind << S(slot) << " = " << value << ";\n";
     };
     auto park_flush = [&](int row) {
         if (!opt.opaque_park) return;
@@ -608,12 +837,12 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
             const size_t c1 = std::min(park_list.size(), c0 + kChunk);
             const bool last = c1 >= park_list.size();
             const std::string out = last ? tok : tok + "c" + std::to_string(ci);
-            o << ind << "unsigned int " << out << ";\n" << ind << "asm volatile(\"";
-            for (size_t e = 0; e < c1 - c0; ++e) o << "st.shared.f64 [%1+%" << (2 * e + 2) << "], %" << (2 * e + 3) << "; ";
-            o << "mov.b32 %0, %1;\" : \"=r\"(" << out << ") : \"r\"(" << base << ")";
+            O << ind << "unsigned int " << out << ";\n" << ind << "asm volatile(\"";
+            for (size_t e = 0; e < c1 - c0; ++e) O << "st.shared.f64 [%1+%" << (2 * e + 2) << "], %" << (2 * e + 3) << "; ";
+            O << "mov.b32 %0, %1;\" : \"=r\"(" << out << ") : \"r\"(" << base << ")";
             for (size_t e = c0; e < c1; ++e)
-                o << ", \"n\"(SOFF(" << park_list[e].first << ", @R)), \"d\"(" << park_list[e].second << ")";
-            o << ");\n";
+                O << ", \"n\"(SOFF(" << park_list[e].first << ", @R)), \"d\"(" << park_list[e].second << ")";
+            O << ");\n";
             base = out;
             if (last) break;
         }
@@ -630,7 +859,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         } else {
             const int sd = alloc(), srd = alloc();
             const std::string dn = "r" + std::to_string(i) + "_" + std::to_string(i) + "@";
-            if (d.c) o << ind << "const double " << dn << " = " << d.e << ";\n";
+            if (d.c) O << ind << "const double " << dn << " = " << d.e << ";\n";
             // (rcp_seq needs a normal reciprocal: 2^-1021 <= |pivot| <= 2^1021; anything else is redone generically)
             if (opt.fold_guards && opt.int_pivot_guard) {
                 // on the high word, conservatively: accept 2^e_lo <= |pivot| < 2^1021 with 2^e_lo the smallest power of
@@ -643,13 +872,13 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
                 char buf[160];
                 std::snprintf(buf, sizeof buf, "dacc@ = max(dacc@, 2u * (unsigned int)__double2hiint(%s) - 0x%xu);  // <= 0x%xu\n",
                               dn.c_str(), 2u * hi_lo, 2u * (hi_hi - hi_lo) + 1u);
-                o << ind << buf;
+                O << ind << buf;
                 dacc_limit = 2u * (hi_hi - hi_lo) + 1u;
             } else {
-                o << ind << "bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(std::max(C.lu_eps, 0x1p-1021)) << " && fabs(" << dn
+                O << ind << "bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(std::max(C.lu_eps, 0x1p-1021)) << " && fabs(" << dn
                   << ") <= 0x1p+1021);\n";
             }
-            if (opt.opaque_park) o << ind << "const double rd" << i << "@ = rcp_seq(" << dn << ");\n";
+            if (opt.opaque_park) O << ind << "const double rd" << i << "@ = rcp_seq(" << dn << ");\n";
             park(sd, dn);
             park(srd, opt.opaque_park ? "rd" + std::to_string(i) + "@" : "rcp_seq(" + dn + ")");
             Dv[i] = Val::E(PK(sd, i), d.t + kLatSmem);
@@ -675,7 +904,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         park_flush(i);
         parked[i] = true;
     };
-    {
+    if (!PAIR) {
         const size_t W = (size_t)std::max(1, opt.rows_in_flight);
         std::vector<RowGen> open;
         int next_row = 0;
@@ -709,7 +938,42 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
             }
             if (!progressed) throw std::runtime_error("specialize: row schedule made no progress");
         }
+    } else {
+        // Warp pair: replay the list schedule (pair_schedule) into the two streams.  A hand-over is one named barrier,
+        // used once per Newton iteration — the iteration-start barrier lies between two uses, so an arrive can never
+        // run into the previous use of its barrier.
+        std::map<std::pair<int, int>, int> bar_of;
+        for (const auto& hp2 : pair_plan.handovers) {
+            const int id = 4 + (int)bar_of.size();
+            bar_of[hp2] = id;
+        }
+        H.pair_events = (int)bar_of.size();
+        std::map<int, RowGen> rows;
+        for (const PairAct& act : pair_plan.acts) {
+            row_out = act.role ? &oh_rows : &o;
+            if (act.kind == PairAct::WAIT) {
+                O << ind << "PAIR_SYNC(" << bar_of.at({act.row, act.k}) << ");\n";
+                continue;
+            }
+            RowGen& R = rows[act.row];
+            R.i = act.row;
+            if (act.kind == PairAct::ASM) {
+                emit_assembly(R);
+            } else if (act.kind == PairAct::STEP) {
+                if (!parked[act.k]) throw std::runtime_error("specialize: pair schedule uses a row before it is parked");
+                emit_step(R, act.k);
+            } else {
+                emit_park(R);
+                auto it = bar_of.find({act.role, act.k});
+                if (it != bar_of.end()) O << ind << "PAIR_ARRIVE(" << it->second << ");\n";
+                rows.erase(act.row);
+            }
+        }
+        row_out = &o;
     }
+    if (PAIR)
+        O << ind << "PAIR_SYNC(2);  // the helper's rows are parked\n"
+          << ind << "bad@ = bad@ || " << S(HB) << " != 0.0;\n";
     // ---- back substitution (include/solver.hpp:116-128) ---------------------------------------------------
     std::vector<Val> Q(N);
     if (K == 1)
@@ -824,14 +1088,21 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     // squares non-finite (inf/NaN propagate through every operation below), so "sum of squares finite" proves
     // all 31 entries finite with one comparison; only when it is not (overflow of a square counts too) are the
     // entries themselves inspected, in a branch no lane normally takes.
+    // (warp pair: first the unknowns at the MOSFET terminals — the helper linearises for the next iteration from them
+    // while this warp finishes damping, norm and convergence test; x stays where the lane is done)
+    for (int phase = PAIR ? 0 : 1; phase < 2; ++phase) {
     for (int i = 0; i < N; ++i) {
+        if (PAIR && (cand_slot.count(i) > 0) != (phase == 0)) continue;
         const std::string xi = xrd(i), I = std::to_string(i);
         if (opt.x_in_smem) o << "            const double xo" << I << "@ = " << xi << ";\n";
         const std::string xv = opt.x_in_smem ? "xo" + I + "@" : xi;
         o << "            const double n" << I << "@ = d_add(" << xv << ", d_mul(" << lit(DC ? C.dc_alpha : C.tran_alpha) << ", d_sub(q" << I
-          << "@, " << xv << ")));\n"
-          << "            double e" << I << "@ = d_sub(n" << I << "@, " << xv << ");\n"
+          << "@, " << xv << ")));\n";
+        if (PAIR && phase == 0) o << "            " << S(cand_slot.at(i)) << " = done@ ? xo" << I << "@ : n" << I << "@;\n";
+        o << "            double e" << I << "@ = d_sub(n" << I << "@, " << xv << ");\n"
           << "            e" << I << "@ = d_mul(e" << I << "@, e" << I << "@);\n";
+    }
+    if (PAIR && phase == 0) o << "            PAIR_ARRIVE(3);\n";
     }
     // 32-leaf pairwise tree (oracle/csim_norm2.h); leaves >= N are +0 and adding +0 to a square is exact
     {
@@ -944,7 +1215,8 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
          "            //@END\n"
          "        }\n"
          "    }\n"
-         "    //@BEGIN\n"
+      << (PAIR ? "    SMG(" + std::to_string(CMD) + " + par, tid >> 6) = 0.0;\n    PAIR_SYNC(1);  // dismiss the helpers\n" : std::string())
+      << "    //@BEGIN\n"
          "    if (live@) {\n";
     for (int i = 0; i < N; ++i) o << "        xio[(long long)" << i << " * B + b@] = " << xrd(i) << ";\n";
     o << "        if (iters_total) iters_total[b@] += total@;\n"
@@ -959,13 +1231,47 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
          "}\n";
     }  // TRAN tail
 
+#undef O
+    // ---- warp pair: hand-overs -> named barriers, helper loop ---------------------------------------------------------------
+    std::string body = o.str();
+    if (PAIR) {
+        std::ostringstream h;
+        int n_helper_rows = 0;
+        for (int i = 0; i < N; ++i) n_helper_rows += owner[i];
+        h << "    if (tid & 32) {  // helper warp: " << n_helper_rows << " of the " << N << " rows of every Newton iteration the master runs\n"
+             "        PAIR_SYNC(3);  // linearisation at the start iterate\n"
+          << oh_mos.str()
+          << "        for (int par = 0;; par ^= 1) {\n"
+             "            PAIR_SYNC(1);\n"
+             "            const double cmd = pair_cmd(sm, " << CMD << " + par, LTID);\n"
+             "            if (cmd == 0.0) break;     // kernel end\n"
+             "            if (cmd == 2.0) continue;  // every master's Newton loop has ended\n"
+             "            bool bad@ = false;\n"
+             "            unsigned int glo@ = 0xFFFFFFFFu, ghi@ = 0u, gacc@ = 0u, pmx@ = 0u, dacc@ = 0u;\n"
+          << oh_rows.str()
+          << "            " << S(HB) << " = (bad@ || (glo@ < 0x03600000u) || (ghi@ > 0x7FEFFFFFu) || (gacc@ > kTdivTMax) || (pmx@ >= kTdivTOne) || (dacc@ > DACC_LIMIT)) ? 1.0 : 0.0;\n"
+             "            PAIR_ARRIVE(2);\n"
+             "            PAIR_SYNC(3);  // the master's next iterate is there: linearise for the next iteration\n"
+          << oh_mos.str()
+          << "        }\n"
+             "        return;\n"
+             "    }\n";
+        const size_t at = body.find("//%HELPER%\n");
+        body.replace(at, std::string("//%HELPER%\n").size(), h.str());
+    }
+
     H.n_slots = n_slots;
     H.replicas = R;
     const size_t warp_bytes = (size_t)n_slots * 8 * 32 * R;
     if (warp_bytes > kMaxSmem) throw std::runtime_error("specialize: per-instance state exceeds shared memory");
-    const int kTpb = 32 * (opt.warps_per_cta > 0 ? opt.warps_per_cta : pick_warps_per_cta(warp_bytes));
+    // warp pair: the pairs of one CTA share the named barriers (they run the same two instruction streams in step,
+    // which is what lets them share instruction-cache lines)
+    int n_pairs = opt.warps_per_cta > 0 ? opt.warps_per_cta : 2;
+    while (n_pairs > 1 && warp_bytes * n_pairs > kMaxSmem) --n_pairs;
+    const int kTpb = PAIR ? 64 * n_pairs : 32 * (opt.warps_per_cta > 0 ? opt.warps_per_cta : pick_warps_per_cta(warp_bytes));
     H.threads = kTpb;
-    H.smem_bytes = warp_bytes * (kTpb / 32);
+    H.inst_per_cta = PAIR ? 32 * n_pairs : kTpb * R;
+    H.smem_bytes = PAIR ? warp_bytes * n_pairs : warp_bytes * (kTpb / 32);
     if (H.smem_bytes > kMaxSmem) throw std::runtime_error("specialize: CTA state exceeds shared memory");
     std::ostringstream pro;
     pro << "// generated by specialize_tpi.cpp — thread-per-instance transient kernel for one topology and one\n"
@@ -980,12 +1286,27 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
            "#define NSLOTS " << n_slots << "\n"
            "#define SPEC_N " << N << "\n"
            "#define SPEC_NV " << mp.n_values << "\n"
-           "#define SM(k, r) sm[((k) + (r) * NSLOTS) * TPB + tid]\n"
-           "#define SOFF(k, r) ((((k) + (r) * NSLOTS) * TPB) * 8)\n"
+           "#define LANES " << (PAIR ? "32" : "TPB") << "\n"
+           "#define LTID " << (PAIR ? "(tid & 31)" : "tid") << "\n"
+           "#define PAIRS " << (PAIR ? n_pairs : 0) << "\n"
+           "#define SM(k, r) sm[((k) + " << (PAIR ? "(tid >> 6)" : "(r)") << " * NSLOTS) * LANES + LTID]\n"
+           "#define SOFF(k, r) ((((k) + (r) * NSLOTS) * LANES) * 8)\n"
+           "#define SMG(k, g) sm[((k) + (g) * NSLOTS) * LANES + LTID]\n"
+           "#define PAIR_SYNC(id) asm volatile(\"bar.sync %0, %1;\" ::\"n\"(id), \"n\"(TPB) : \"memory\")\n"
+           "#define PAIR_ARRIVE(id) asm volatile(\"bar.arrive %0, %1;\" ::\"n\"(id), \"n\"(TPB) : \"memory\")\n"
            "#define PRM(k, bb) ld_nohoist(params + (long long)(k) * B + (bb))\n"
            "#define DACC_LIMIT 0x" << std::hex << dacc_limit << std::dec << "u\n"
         << cand_table <<
            "#define TPI_SUCC0 " << kTpiMissEntries * kTpiMissStride << "\n"
+           "// command of the round: 0 = leave as soon as one master says so, 2 = all masters' Newton loops have ended, else 1\n"
+           "__device__ __forceinline__ double pair_cmd(const double* sm, int slot, int lane) {\n"
+           "    double c = 2.0;\n"
+           "    for (int g = 0; g < PAIRS; ++g) {\n"
+           "        const double v = sm[(slot + g * NSLOTS) * 32 + lane];\n"
+           "        c = (v == 0.0 || c == 0.0) ? 0.0 : (v == 1.0 ? 1.0 : c);\n"
+           "    }\n"
+           "    return c;\n"
+           "}\n"
            "extern \"C\" __global__ void __launch_bounds__(TPB, " << std::max<size_t>(1, std::min<size_t>(16, kSmemPerSm / (H.smem_bytes + kCtaReserve)))
         << ")\n"
            "" << (DC ? "csim_dc_tpi" : "csim_tran_tpi") << "(DevPlan P, DevTran T, long long B, const double* __restrict__ params,\n"
@@ -995,12 +1316,13 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
            "              unsigned long long* __restrict__ stats) {\n"
            "    extern __shared__ double sm[];\n"
            "    const int tid = threadIdx.x;\n"
-           "    const unsigned int sbase = (unsigned int)__cvta_generic_to_shared(sm) + 8u * tid;\n"
+           "    const unsigned int sbase = (unsigned int)__cvta_generic_to_shared(sm) + 8u * LTID;\n"
 
+           "    int par = 0;  // (warp pair) parity of the command round\n"
            "    const double dt = T.dt;\n"
            "    const unsigned long long F = 0x" << std::hex << (((unsigned long long)H.hash_hi << 32) | H.hash_lo) << std::dec
         << "ull;\n";
-    H.source = pro.str() + replicate(o.str(), R);
+    H.source = pro.str() + replicate(body, R);
     return H;
 }
 }  // namespace
