@@ -535,6 +535,35 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     std::ostringstream oh_mos, oh_rows;  // warp pair: the helper's share of a Newton iteration
     std::ostringstream* row_out = &o;    // where the row generators below write
 #define O (*row_out)
+    // (warp pair) MOSFET linearisations, emitted where the comments at "MOSFET linearisation" below say
+    // The master takes the last pair_mos_master of them itself: its tail (pairwise tree, square root, votes) is a chain of
+    // dependent operations with issue slots to spare, while the helper's linearisations are what the loop waits for.
+    std::ostringstream om_start, om_iter;  // the master's linearisations: before the first step / in the tail of an iteration
+    if (PAIR) {
+        int pair_mos_master = 0;  // (B200, dbmixer headline run: 142.2 M with 0 against 139.7 M with 1, although the static timeline says 5.9 k against 6.2 k cycles)
+        if (const char* e = std::getenv("CSIM_PAIR_MOS_MASTER")) pair_mos_master = std::atoi(e);
+        const int n_mos = (int)mp.mos_ops.size();
+        for (int mi = 0; mi < n_mos; ++mi) {
+            const MosOp& op = mp.mos_ops[mi];
+            const bool by_master = mi >= n_mos - pair_mos_master;
+            auto mn = [&](int t) { return "m" + std::to_string(op.out + t) + "@"; };
+            for (int where = 0; where < (by_master ? 2 : 1); ++where) {
+                std::ostringstream& om = by_master ? (where ? om_iter : om_start) : oh_mos;
+                auto cand = [&](int node) {
+                    if (node < 0) return std::string("0.0");
+                    if (!by_master) return S(cand_slot.at(node));
+                    return where ? "c" + std::to_string(node) + "@" : xrd(node);
+                };
+                om << "            {\n                double " << mn(0) << ", " << mn(1) << ", " << mn(2) << ", " << mn(3) << ";\n"
+                   << "                " << (opt.mos_branchless ? "mos_eval_sel" : "mos_eval_pp") << "<" << (op.is_p ? -1 : 1) << ">(PRM("
+                   << op.param << ", bb@), PRM(" << op.param + 1 << ", bb@), PRM(" << op.param + 2 << ", bb@), " << lit(C.mos_off_gds)
+                   << ", " << cand(op.d) << ", " << cand(op.g) << ", " << cand(op.s) << ", " << mn(0) << ", " << mn(1) << ", " << mn(2)
+                   << ", " << mn(3) << ");\n";
+                for (int t = 0; t < 4; ++t) om << "                " << S(mos_slot.at(op.out + t)) << " = " << mn(t) << ";\n";
+                om << "            }\n";
+            }
+        }
+    }
     if (PAIR) o << "    const long long b@ = (long long)blockIdx.x * (32 * PAIRS) + (tid >> 6) * 32 + LTID;\n";
     else o << "    const long long b@ = (long long)blockIdx.x * (LANES * NREP) + @R * LANES + LTID;\n";
     o << ""
@@ -597,7 +626,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     } else {
     if (PAIR) {
         for (const auto& kv : cand_slot) o << "    " << S(kv.second) << " = " << xrd(kv.first) << ";\n";
-        o << "    PAIR_ARRIVE(3);  // the helpers linearise the MOSFETs at the start iterate\n";
+        o << "    PAIR_ARRIVE(3);  // the helpers linearise the MOSFETs at the start iterate\n" << om_start.str();
     }
     o << "    const int r0 = T.out_begin_step / T.out_stride;\n"
          "    for (int step = T.step_begin; step < T.step_end; ++step) {\n"
@@ -640,18 +669,6 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     // (warp pair: the helper linearises every MOSFET for the NEXT iteration while the master is busy with norm and
     // convergence test — from the damped iterate the master leaves at the MOSFET terminals — so neither warp has the
     // linearisations on its path; see the damping block below)
-    if (PAIR)
-        for (const MosOp& op : mp.mos_ops) {
-            auto mn = [&](int t) { return "m" + std::to_string(op.out + t) + "@"; };
-            auto cand = [&](int node) { return node < 0 ? std::string("0.0") : S(cand_slot.at(node)); };
-            oh_mos << "            {\n                double " << mn(0) << ", " << mn(1) << ", " << mn(2) << ", " << mn(3) << ";\n"
-                   << "                " << (opt.mos_branchless ? "mos_eval_sel" : "mos_eval_pp") << "<" << (op.is_p ? -1 : 1) << ">(PRM("
-                   << op.param << ", bb@), PRM(" << op.param + 1 << ", bb@), PRM(" << op.param + 2 << ", bb@), " << lit(C.mos_off_gds)
-                   << ", " << cand(op.d) << ", " << cand(op.g) << ", " << cand(op.s) << ", " << mn(0) << ", " << mn(1) << ", " << mn(2)
-                   << ", " << mn(3) << ");\n";
-            for (int t = 0; t < 4; ++t) oh_mos << "                " << S(mos_slot.at(op.out + t)) << " = " << mn(t) << ";\n";
-            oh_mos << "            }\n";
-        }
     for (size_t mi = 0; mi < mp.mos_ops.size(); ++mi)
     for (int role = 0; role < 1; ++role) {
         if (!mos_need[role][mi]) continue;
@@ -1098,11 +1115,13 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         const std::string xv = opt.x_in_smem ? "xo" + I + "@" : xi;
         o << "            const double n" << I << "@ = d_add(" << xv << ", d_mul(" << lit(DC ? C.dc_alpha : C.tran_alpha) << ", d_sub(q" << I
           << "@, " << xv << ")));\n";
-        if (PAIR && phase == 0) o << "            " << S(cand_slot.at(i)) << " = done@ ? xo" << I << "@ : n" << I << "@;\n";
+        if (PAIR && phase == 0)
+            o << "            const double c" << I << "@ = done@ ? xo" << I << "@ : n" << I << "@;\n"
+              << "            " << S(cand_slot.at(i)) << " = c" << I << "@;\n";
         o << "            double e" << I << "@ = d_sub(n" << I << "@, " << xv << ");\n"
           << "            e" << I << "@ = d_mul(e" << I << "@, e" << I << "@);\n";
     }
-    if (PAIR && phase == 0) o << "            PAIR_ARRIVE(3);\n";
+    if (PAIR && phase == 0) o << "            PAIR_ARRIVE(3);\n" << om_iter.str();
     }
     // 32-leaf pairwise tree (oracle/csim_norm2.h); leaves >= N are +0 and adding +0 to a square is exact
     {

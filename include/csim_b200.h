@@ -171,7 +171,10 @@ int csim_plan_dims(const csim_plan* plan, int32_t* n_unknowns, int32_t* n_params
  * warp-per-instance one when more than 2 % of the solves miss the predicted pivot order; 2: warp-per-instance
  * kernel (csim_tran_spec: one warp per instance, rows in registers); 3: thread-per-instance kernel
  * (csim_tran_tpi: one thread per instance, state in shared memory).  CSIM_JIT=0|2|3 in the environment
- * overrides.  All four paths give bit-identical results.                                              */
+ * overrides.  All four paths give bit-identical results.
+ * A transient batch that fits one wave of CTAs runs the thread-per-instance kernel in its warp-PAIR form (two warps
+ * per 32 instances: the second warp computes part of the matrix rows and the MOSFET linearisations of the next
+ * iteration; same operations in the same order, so the same bits).  CSIM_TPI_PAIR=0 turns that off.            */
 int csim_plan_jit_mode(csim_plan* plan, int mode);
 /* Specialise now for perm[N] (perm[i] = original row expected at pivot position i). */
 int csim_plan_specialize(csim_plan* plan, const int32_t* perm);
