@@ -394,7 +394,9 @@ bool tpi_use_pair(const csim_plan* plan, int64_t B) {
         if (B > (int64_t)tp.n_sms * 3 * 32) return false;  // cannot fit whatever the kernel needs: do not build yet
         tp.pair_tried = true;
         std::string log;
-        if (tpi_build_variant(plan, tp.host.perms, 2, tp.host_pair, tp.k_pair, tp.groups_per_sm_pair, log, false, true) == CSIM_OK &&
+        int pairs_per_cta = 2;  // (development aid: CSIM_PAIR_PER_CTA)
+        if (const char* e = std::getenv("CSIM_PAIR_PER_CTA")) pairs_per_cta = std::max(1, std::atoi(e));
+        if (tpi_build_variant(plan, tp.host.perms, pairs_per_cta, tp.host_pair, tp.k_pair, tp.groups_per_sm_pair, log, false, true) == CSIM_OK &&
             tp.host_pair.pair) {
             tp.pair_ready = true;
             tp.log += "\nwarp-pair variant: " + std::to_string(tp.host_pair.threads) + " threads per CTA for " +
