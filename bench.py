@@ -478,6 +478,8 @@ def run_ours(args):
     fused_kind = plan.spec_info().get("kind", 0)
     kname = {3: "csim_tran_tpi (NVRTC, thread per instance)", 2: "csim_tran_spec (NVRTC, warp per instance)"}.get(
         fused_kind, "tran_kernel (generic)")
+    if fused_kind == 3 and "warp-pair variant" in plan.spec_info().get("log", ""):
+        kname = "csim_tran_tpi, warp-pair variant (NVRTC, two warps per 32 instances)"
     tran_tflops = newton_total * fl["useful"] / (tran_ms / 1e3) / 1e12
     tj = None
     try:
