@@ -747,8 +747,17 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         o << "            if (__any_sync(0xFFFFFFFFu, var@ == " << v << " && need@)) {\n"
              "            if (var@ == " << v << " && need@) {  // variant " << v << "\n";
     // generator-side description of the factorisation so far
-    std::vector<Val> Dv(N), RDv(N), Yv(N);
-    std::vector<std::map<int, Val>> Uv(N);
+    // [c]: as the code of warp c refers to them (warp pair with register forwarding: the warp that parked a row reads its
+    // own registers, the other warp the shared-memory slots; otherwise both entries are the same)
+    std::vector<Val> DvA[2] = {std::vector<Val>(N), std::vector<Val>(N)}, RDvA[2] = {std::vector<Val>(N), std::vector<Val>(N)},
+                     YvA[2] = {std::vector<Val>(N), std::vector<Val>(N)};
+    std::vector<std::map<int, Val>> UvA[2] = {std::vector<std::map<int, Val>>(N), std::vector<std::map<int, Val>>(N)};
+    const bool REGFWD = PAIR && std::getenv("CSIM_PAIR_REGFWD") && std::atoi(std::getenv("CSIM_PAIR_REGFWD")) != 0;
+#define CR (row_out == &oh_rows ? 1 : 0)
+#define Dv DvA[CR]
+#define RDv RDvA[CR]
+#define Yv YvA[CR]
+#define Uv UvA[CR]
     std::vector<bool> parked(N, false);
     char num[64];
     auto fabs_lit = [&](double v) { return lit(std::fabs(v)); };
@@ -871,8 +880,12 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
         // pivot of this position: singular / non-finite pivots go to the generic path
         // (a permutation nobody's matrix can take may put a structural zero on the diagonal: constant 0 -> "bad")
         const Val d = R.row.count(i) ? R.row[i] : Val::K(0.0);
+        const int me = CR;  // the warp that parks this row
+        auto both = [&](std::vector<Val>* arr, int idx, const Val& shared, const Val& own) {
+            for (int c = 0; c < 2; ++c) arr[c][idx] = (REGFWD && c == me) ? own : shared;
+        };
         if (d.c && (d.v == 1.0 || d.v == -1.0)) {
-            Dv[i] = d;
+            both(DvA, i, d, d);
         } else {
             const int sd = alloc(), srd = alloc();
             const std::string dn = "r" + std::to_string(i) + "_" + std::to_string(i) + "@";
@@ -895,28 +908,30 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
                 O << ind << "bad@ = bad@ || !(fabs(" << dn << ") >= " << lit(std::max(C.lu_eps, 0x1p-1021)) << " && fabs(" << dn
                   << ") <= 0x1p+1021);\n";
             }
-            if (opt.opaque_park) O << ind << "const double rd" << i << "@ = rcp_seq(" << dn << ");\n";
+            if (opt.opaque_park || REGFWD) O << ind << "const double rd" << i << "@ = rcp_seq(" << dn << ");\n";
             park(sd, dn);
-            park(srd, opt.opaque_park ? "rd" + std::to_string(i) + "@" : "rcp_seq(" + dn + ")");
-            Dv[i] = Val::E(PK(sd, i), d.t + kLatSmem);
-            RDv[i] = Val::E(PK(srd, i), d.t + kLatRcp + kLatSmem);
+            park(srd, (opt.opaque_park || REGFWD) ? "rd" + std::to_string(i) + "@" : "rcp_seq(" + dn + ")");
+            both(DvA, i, Val::E(PK(sd, i), d.t + kLatSmem), Val::E(dn, d.t));
+            both(RDvA, i, Val::E(PK(srd, i), d.t + kLatRcp + kLatSmem), Val::E("rd" + std::to_string(i) + "@", d.t + kLatRcp));
             H.n_rcp++;
         }
         for (int j : A.ucols[i]) {
             const Val u = R.row[j];
             if (u.c) {
-                Uv[i][j] = u;
+                for (int c = 0; c < 2; ++c) UvA[c][i][j] = u;
             } else {
                 const int su = alloc();
                 park(su, u.e);
-                Uv[i][j] = Val::E(PK(su, i), u.t + kLatSmem, u.z);
+                for (int c = 0; c < 2; ++c)
+                    UvA[c][i][j] = (REGFWD && c == me) ? Val::E(u.e, u.t, u.z) : Val::E(PK(su, i), u.t + kLatSmem, u.z);
             }
         }
         if (R.row[N].c) {
-            Yv[i] = R.row[N];
+            both(YvA, i, R.row[N], R.row[N]);
         } else {
             park(Y0 + i, "rb" + std::to_string(i) + "@");
-            Yv[i] = Val::E(PK(Y0 + i, i), R.row[N].t + kLatSmem, R.row[N].z);
+            both(YvA, i, Val::E(PK(Y0 + i, i), R.row[N].t + kLatSmem, R.row[N].z),
+                 Val::E("rb" + std::to_string(i) + "@", R.row[N].t, R.row[N].z));
         }
         park_flush(i);
         parked[i] = true;
@@ -1251,6 +1266,11 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     }  // TRAN tail
 
 #undef O
+#undef CR
+#undef Dv
+#undef RDv
+#undef Yv
+#undef Uv
     // ---- warp pair: hand-overs -> named barriers, helper loop ---------------------------------------------------------------
     std::string body = o.str();
     if (PAIR) {
