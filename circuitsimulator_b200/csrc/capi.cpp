@@ -251,7 +251,7 @@ bool cache_load(const csim_plan* plan, bool dc, std::vector<std::vector<int32_t>
     return ok;
 }
 
-// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bit 5: folded division guards, bit 6: opaque row parking; bits 8-9: replicas - 1, bits 12-14: warps per CTA, bits 16-19: rows in flight, bit 20: warp pair per 32 instances); unset = defaults.
+// Development aid: CSIM_TPI_OPTS = bit mask of TpiOptions (bit 5: folded division guards, bit 6: opaque row parking; bits 8-9: replicas - 1, bits 12-14: warps per CTA, bits 16-19: rows in flight, bit 20: warp pair per 32 instances, bit 21: warps of a CTA in step); unset = defaults.
 TpiOptions tpi_options_from_env() {
     TpiOptions opt;
     if (const char* env = std::getenv("CSIM_TPI_OPTS")) {
@@ -270,6 +270,7 @@ TpiOptions tpi_options_from_env() {
         opt.warps_per_cta = (m >> 12) & 7;
         if ((m >> 16) & 15) opt.rows_in_flight = (m >> 16) & 15;
         opt.pair = (m >> 20) & 1;
+        opt.lockstep = (m >> 21) & 1;
     }
     return opt;
 }

@@ -81,6 +81,13 @@ struct TpiOptions {
     // operation order: bit-identical.  Why: one warp per SM sub-partition is bound by its own dependency stalls
     // (1.77 stall cycles per issue), and shared memory, not registers, caps residency at 3-4 warps per SM.
     bool pair = false;
+    // One-warp-per-32-instances kernel in CTAs of several warps: the warps vote TOGETHER on the end of every Newton
+    // loop (__syncthreads_and), so they run the straight-line body in step and share the instruction lines one of
+    // them fetched (the body is larger than the SM's instruction cache).  Costs the iterations a warp idles while
+    // another warp of its CTA still iterates, and a generic redo stalls the whole CTA.
+    // Measured on B200, dbmixer, 18,944 instances (4 warps per SM): 228.2 M (2-warp CTAs) / 227.3 M (4-warp CTAs) in step
+    // against 231.6 / 231.1 M free-running — sharing fetches does not pay where every sub-partition is busy: off.
+    bool lockstep = false;
 };
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<int32_t>& perm, const TpiOptions& opt = TpiOptions());
 TpiHost generate_tran_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>& perms,

@@ -468,6 +468,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     const int R = std::max(1, opt.replicas);
     // ---- warp pair: row ownership (0 = master, 1 = helper) and the two hand-shake slots ---------------------------------
     const bool PAIR = opt.pair && K == 1 && !DC && R == 1 && opt.x_in_smem && !opt.opaque_park && !opt.mos_in_smem && !opt.q_in_smem;
+    const bool LOCKSTEP = opt.lockstep && !PAIR && !DC;
     std::vector<int> owner(N, 0);
     std::vector<int> mos_of_value(mp.n_values, -1);
     for (size_t m = 0; m < mp.mos_ops.size(); ++m)
@@ -630,7 +631,8 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
     }
     o << "    const int r0 = T.out_begin_step / T.out_stride;\n"
          "    for (int step = T.step_begin; step < T.step_end; ++step) {\n"
-      << (PAIR ? "" : "        if (__all_sync(0xFFFFFFFFu, ALL(dead@))) break;\n");  // (warp pairs of a CTA stay in step)
+      << (PAIR ? "" : LOCKSTEP ? "        if (__syncthreads_and(ALL(dead@))) break;\n"
+                                : "        if (__all_sync(0xFFFFFFFFu, ALL(dead@))) break;\n");  // (warp pairs of a CTA stay in step)
     // ---- per step: x_prev -> scratch, companion history terms, source values -------------------------
     for (int i = 0; i < N; ++i)
         o << "        if (live@) scratch[(long long)" << (XP0 + i) << " * B + b@] = " << xrd(i) << ";\n";
@@ -661,6 +663,7 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
                  "            PAIR_SYNC(1);\n"
                  "            if (pair_cmd(sm, " + std::to_string(CMD) + " + par, LTID) == 2.0) { par ^= 1; break; }\n"
                  "            par ^= 1;\n"
+               : LOCKSTEP ? "            if (__syncthreads_and(ALL(done@))) break;  // the warps of the CTA iterate in step: they share fetched instruction lines\n"
                : "            if (__all_sync(0xFFFFFFFFu, ALL(done@))) break;\n")
       << "            bool bad@ = degen@;\n"
          "            unsigned int glo@ = 0xFFFFFFFFu, ghi@ = 0u, gacc@ = 0u, pmx@ = 0u, dacc@ = 0u;\n";
