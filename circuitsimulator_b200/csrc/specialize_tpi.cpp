@@ -185,6 +185,7 @@ int kPairSync = 40;       // (development aid: CSIM_PAIR_SYNC / CSIM_PAIR_EVENTS
 // named barriers of a CTA: 0 unused, 1 = iteration start, 2 = helper done, 3 = next iterate at the MOSFET terminals,
 // 4..15 = hand-overs
 int kPairMaxEvents = 12;
+int kPairDefer = 0, kPairMargin = 0;  // (development aids: CSIM_PAIR_DEFER, CSIM_PAIR_MARGIN)
 
 struct PairModel {
     int N = 0, W = 1;  // W: rows in flight per warp
@@ -235,9 +236,15 @@ PairSchedule pair_schedule(const PairModel& M, const std::vector<int>& owner) {
             if (!pending(r)) continue;
             std::vector<Open>& op = open[r];
             while (op.size() < (size_t)M.W && qnext[r] < queue[r].size()) op.push_back(Open{queue[r][qnext[r]++]});
+            // first a row that can go on without a new hand-over (the wait would also hold up the other rows in flight)
+            for (int avoid_wait = kPairDefer ? 1 : 0; avoid_wait >= 0 && !done; --avoid_wait)
             for (size_t n = 0; n < op.size() && !done; ++n) {
                 const size_t idx = (cursor[r] + n) % op.size();
                 Open& R = op[idx];
+                if (avoid_wait && R.assembled && R.next < M.steps[R.row].size()) {
+                    const int k = M.steps[R.row][R.next].first;
+                    if (T[k] >= 0 && owner[k] != r && pos[k] >= waited[r]) continue;
+                }
                 if (!R.assembled) {
                     S.acts.push_back({PairAct::ASM, r, R.row, -1});
                     S.t[r] += M.asm_cost[R.row];
@@ -250,7 +257,7 @@ PairSchedule pair_schedule(const PairModel& M, const std::vector<int>& owner) {
                     if (owner[k] != r && pos[k] >= waited[r]) {
                         const int o = 1 - r, ready = std::max(S.t[r], T[k] + kPairSync);
                         int q = pos[k];
-                        while (q + 1 < (int)Tpos[o].size() && Tpos[o][q + 1] + kPairSync <= ready) ++q;
+                        while (q + 1 < (int)Tpos[o].size() && Tpos[o][q + 1] + kPairSync + kPairMargin <= ready) ++q;
                         waited[r] = q + 1;
                         S.handovers.insert({o, q});
                         S.acts.push_back({PairAct::WAIT, r, o, q});
@@ -500,6 +507,8 @@ TpiHost generate_tpi(const HostPlan& hp, const std::vector<std::vector<int32_t>>
                 if (A.pat[i][k]) M.steps[i].push_back({k, 14 + 4 * ((int)A.cols_k[k].size() + 1)});
         }
         if (const char* e = std::getenv("CSIM_PAIR_SYNC")) kPairSync = std::atoi(e);
+        if (const char* e = std::getenv("CSIM_PAIR_DEFER")) kPairDefer = std::atoi(e);
+        if (const char* e = std::getenv("CSIM_PAIR_MARGIN")) kPairMargin = std::atoi(e);
         if (const char* e = std::getenv("CSIM_PAIR_EVENTS")) kPairMaxEvents = std::min(12, std::atoi(e));
         owner = pair_partition(M);
         if (const char* e = std::getenv("CSIM_PAIR_ROWS")) {  // development aid: the helper's rows, comma separated

@@ -101,3 +101,50 @@ def test_generator_rejects_non_permutations():
                      topo.elem_branch, topo.elem_param, topo.n_params, device=-1)
     with pytest.raises(capi.CsimError, match="permutation"):
         plan.generate_source(np.zeros(topo.n_unknowns, np.int32))
+
+
+@pytest.mark.parametrize("name", ["dbmixer", "buffer"])
+def test_warp_pair_source_hand_overs_are_consistent_and_compile(name, monkeypatch):
+    """The warp-pair form (CSIM_TPI_OPTS bit 20): every matrix row is emitted exactly once, in one of the two streams;
+    every hand-over barrier has exactly one arrive in one stream and one sync in the other, and a sync never precedes
+    (in the order of the master's stream interleaved by barrier) a use of a row the other warp has not parked; barrier
+    ids stay below 16; NVRTC accepts the source for sm_100a."""
+    import re
+    from circuitsimulator_b200 import capi
+    nvrtc = pytest.importorskip("cuda.bindings.nvrtc")
+    g, topo = load_golden(name)
+    plan = capi.Plan(topo.n_unknowns, topo.n_node_eq, topo.elem_type, topo.elem_flags, topo.elem_nodes,
+                     topo.elem_branch, topo.elem_param, topo.n_params, device=-1)
+    monkeypatch.setenv("CSIM_TPI_OPTS", str(1 + 2 + 32 + (2 << 12) + (1 << 20)))  # defaults + two pairs per CTA + pair
+    src = plan.generate_source(_perm(topo, g), 3)
+    monkeypatch.delenv("CSIM_TPI_OPTS")
+    N = topo.n_unknowns
+    assert "#define PAIRS 2" in src and "if (tid & 32) {  // helper warp" in src
+    lines = src.splitlines()
+    h0 = next(i for i, l in enumerate(lines) if "if (tid & 32) {" in l)
+    h1 = next(i for i in range(h0, len(lines)) if lines[i].strip() == "return;")
+    helper, master = lines[h0:h1], lines[h1:]
+    rows_h = [int(m.group(1)) for l in helper for m in [re.search(r"// position (\d+) = row", l)] if m]
+    rows_m = [int(m.group(1)) for l in master for m in [re.search(r"// position (\d+) = row", l)] if m]
+    assert sorted(rows_h + rows_m) == list(range(N)) and rows_h and rows_m
+    assert rows_h == sorted(rows_h) and rows_m == sorted(rows_m)  # each warp takes its rows in ascending order
+
+    def ops(block, loop_only):
+        out = []
+        for l in block:
+            m = re.search(r"PAIR_(SYNC|ARRIVE)\((\d+)\)", l)
+            if m and "#define" not in l:
+                out.append((m.group(1), int(m.group(2))))
+        return out
+    oh, om = ops(helper, True), ops(master, True)
+    ids = {i for _, i in oh + om}
+    assert max(ids) <= 15 and {1, 2, 3} <= ids
+    for i in sorted(ids - {1, 2, 3}):  # hand-overs: one arrive on one side, one sync on the other, once per iteration
+        a = [(w, k) for w, o in (("h", oh), ("m", om)) for k, j in o if j == i]
+        assert sorted(a) in ([("h", "ARRIVE"), ("m", "SYNC")], [("h", "SYNC"), ("m", "ARRIVE")]), (i, a)
+    assert [k for k, j in oh if j == 2] == ["ARRIVE"] and [k for k, j in om if j == 2] == ["SYNC"]
+    # barrier 3 (next iterate at the MOSFET terminals): master arrives at the start and once per iteration, helper syncs likewise
+    assert [k for k, j in om if j == 3] == ["ARRIVE", "ARRIVE"] and [k for k, j in oh if j == 3] == ["SYNC", "SYNC"]
+    # barrier 1: helper once per round; master once per iteration and once to dismiss the helpers
+    assert [k for k, j in oh if j == 1] == ["SYNC"] and [k for k, j in om if j == 1] == ["SYNC", "SYNC"]
+    assert _nvrtc_compile(nvrtc, src, b"tpi_pair.cu") > 10000
